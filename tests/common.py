@@ -1,0 +1,83 @@
+"""Shared helpers for the parity tests: golden loading, the oracle pipeline and tolerance checks."""
+import glob
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+GOLDEN_DIR = os.path.join(HERE, "golden")
+
+IMG_RTOL = 1e-5   # north_star: rendered images within 1e-5 relative in fp32
+GRAD_RTOL = 1e-4  # north_star: splat / texel gradients within 1e-4 relative
+
+FWD_KEYS = ["out_img", "out_depth", "out_reg", "out_alpha", "out_texture", "out_normal"]
+GRAD_KEYS = ["v_colors", "v_opacity", "v_means", "v_scales", "v_quats", "v_uv0", "v_umap", "v_vmap", "v_texture"]
+VOUT_KEYS = ["v_out_img", "v_out_depth", "v_out_reg", "v_out_alpha", "v_out_texture", "v_out_normal"]
+
+
+def golden_files():
+    return sorted(glob.glob(os.path.join(GOLDEN_DIR, "golden_*.npz")))
+
+
+def load_golden(path):
+    d = dict(np.load(path))
+    fx, fy, cx, cy, H, W, bw, settings, C = d["scalars"]
+    d.update(fx=float(fx), fy=float(fy), cx=float(cx), cy=float(cy), H=int(H), W=int(W), bw=int(bw),
+             settings=int(settings), C=int(C))
+    return d
+
+
+def rel_err(a, b):
+    """max |a-b| / max|b|: error relative to the tensor's scale (what 'x relative in fp32' can mean for
+    sums of signed terms; element-wise relative error is unbounded where terms cancel)."""
+    a = np.asarray(a, np.float64)
+    b = np.asarray(b, np.float64)
+    scale = float(np.abs(b).max())
+    if scale == 0.0:
+        return float(np.abs(a).max())
+    return float(np.abs(a - b).max() / scale)
+
+
+def assert_close_frac(a, b, rtol, name, max_outlier_frac=0.0, atol_scale=1.0):
+    """|a-b| <= rtol * (|b| + atol_scale * scale) element-wise for all but `max_outlier_frac` of the
+    elements (discrete decisions -- alpha < 1/255, T <= 1e-4, T > 0.5 -- may flip for a handful of
+    pixels between two fp32 implementations; those are counted, bounded and reported)."""
+    a = np.asarray(a, np.float64)
+    b = np.asarray(b, np.float64)
+    assert a.shape == b.shape, (name, a.shape, b.shape)
+    scale = float(np.abs(b).max()) if b.size else 0.0
+    bad = np.abs(a - b) > rtol * (np.abs(b) + atol_scale * scale) + 1e-30
+    frac = float(bad.mean()) if b.size else 0.0
+    assert frac <= max_outlier_frac, (
+        f"{name}: {int(bad.sum())}/{b.size} elements ({frac:.2e}) outside rtol={rtol}; "
+        f"max abs err {np.abs(a - b).max():.3e} at scale {scale:.3e}")
+    return frac
+
+
+def run_oracle_pipeline(d, v=None, settings=None):
+    """Full oracle path on a golden / scene dict of numpy arrays."""
+    import oracle
+    import oracle.raster as R
+
+    intr = (d["fx"], d["fy"], d["cx"], d["cy"])
+    H, W, bw = d["H"], d["W"], d.get("bw", 16)
+    _, depths = oracle.project_points(d["means"], d["viewmat"], intr)
+    centers, extents = oracle.get_aabb_2d(d["means"], d["scales"], 1.0, d["quats"], d["viewmat"], intr)
+    nth = oracle.get_num_tiles_hit_2d(centers, extents, H, W, bw)
+    n = d["means"].shape[0]
+    res = R.texture_gaussians_fwd_bwd((n, 1, d["C"]), d["texture_dims"], centers, extents, depths, nth, d["colors"],
+                                      d["opacities"], d["means"], d["scales"], 1.0, d["quats"], d["uv0"], d["umap"],
+                                      d["vmap"], d["texture"], d["viewmat"], d["c2w"], *intr, H, W, bw,
+                                      d["settings"] if settings is None else settings, d["background"], v)
+    res.update(centers=centers, extents=extents, depths=depths, num_tiles_hit=nth)
+    return res
+
+
+def scene_to_numpy(s):
+    import torch
+
+    out = {}
+    for k, x in s.items():
+        out[k] = x.detach().cpu().numpy() if isinstance(x, torch.Tensor) else x
+    out["bw"] = s.get("block_width", 16)
+    return out

@@ -1,0 +1,56 @@
+"""Pin the CPU oracle against golden vectors produced by the reference's own Python
+(tests/golden/make_golden.py: `_torch_impl.texture_forward` + autograd, `project_points`,
+`get_num_tiles_hit_2d`, `get_aabb_2d_torch`, `torch.sort`).  CPU only."""
+import numpy as np
+import pytest
+
+from common import GRAD_KEYS, VOUT_KEYS, assert_close_frac, golden_files, load_golden, run_oracle_pipeline
+
+FILES = golden_files()
+
+
+def test_golden_present():
+    assert len(FILES) >= 3
+
+
+@pytest.mark.parametrize("path", FILES, ids=lambda p: p.split("golden_")[-1][:-4])
+def test_binning_against_reference_python(path):
+    import oracle
+
+    d = load_golden(path)
+    intr = (d["fx"], d["fy"], d["cx"], d["cy"])
+    xys, depths = oracle.project_points(d["means"], d["viewmat"], intr)
+    # depth bits feed the sort key: must equal torch's matmul bit for bit (get_aabb_2d.py:22-32)
+    assert np.array_equal(depths.view(np.int32), d["ref_depths"].view(np.int32))
+    assert np.array_equal(xys.view(np.int32), d["ref_xys"].view(np.int32))
+    centers, extents = oracle.get_aabb_2d(d["means"], d["scales"], 1.0, d["quats"], d["viewmat"], intr)
+    assert np.array_equal(centers, d["centers"]) and np.array_equal(extents, d["extents"])
+    # get_aabb_2d_torch is the reference's (approximate, clip-free here) torch twin of the CUDA kernel
+    assert np.abs(centers - d["ref_aabb_torch_centers"]).max() < 1e-3
+    assert np.abs(extents - d["ref_aabb_torch_extents"]).max() < 1e-3
+    nth = oracle.get_num_tiles_hit_2d(centers, extents, d["H"], d["W"], d["bw"])
+    assert np.array_equal(nth, d["ref_num_tiles_hit"])
+    total, cum = oracle.compute_cumulative_intersects(nth)
+    tb = oracle.tile_bounds_of(d["H"], d["W"], d["bw"])
+    isect, gids, isect_s, gids_s, bins = oracle.bin_and_sort_gaussians(len(nth), total, centers, extents, depths, cum,
+                                                                       tb, d["bw"])
+    assert np.array_equal(isect, d["isect_ids"]) and np.array_equal(gids, d["gaussian_ids"])
+    assert np.array_equal(isect_s, d["ref_isect_ids_sorted"])  # torch.sort
+    assert np.array_equal(gids_s, d["ref_gaussian_ids_sorted"])  # torch.gather
+    assert np.array_equal(bins, d["tile_bins"])
+    # tile bins are consistent with the sorted keys
+    for t in range(bins.shape[0]):
+        lo, hi = bins[t]
+        assert np.all((isect_s[lo:hi] >> 32) == t)
+    assert int((bins[:, 1] - bins[:, 0]).sum()) == total
+
+
+@pytest.mark.parametrize("path", FILES, ids=lambda p: p.split("golden_")[-1][:-4])
+def test_raster_against_reference_torch_impl(path):
+    d = load_golden(path)
+    v = {k: d[k] for k in VOUT_KEYS}
+    res = run_oracle_pipeline(d, v)
+    for k in ["out_img", "out_depth", "out_reg", "out_texture", "out_normal", "final_Ts"]:
+        assert_close_frac(res[k], d["ref_" + k], 1e-5, k)
+    for k in GRAD_KEYS:
+        assert_close_frac(res[k], d["ref_" + k], 1e-4, k)
