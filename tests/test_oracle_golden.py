@@ -51,6 +51,8 @@ def test_raster_against_reference_torch_impl(path):
     v = {k: d[k] for k in VOUT_KEYS}
     res = run_oracle_pipeline(d, v)
     for k in ["out_img", "out_depth", "out_reg", "out_texture", "out_normal", "final_Ts"]:
-        assert_close_frac(res[k], d["ref_" + k], 1e-5, k)
+        # out_reg = sum vis*(d^2*S0 + S2 - 2*d*S1) cancels terms ~100x its value in fp32 and the torch
+        # twin evaluates it through cumsums in another order: 1e-4 there, 1e-5 everywhere else
+        assert_close_frac(res[k], d["ref_" + k], 1e-4 if k == "out_reg" else 1e-5, k)
     for k in GRAD_KEYS:
         assert_close_frac(res[k], d["ref_" + k], 1e-4, k)
