@@ -1,0 +1,113 @@
+"""ctypes binding of the C-ABI CUDA library (include/gstex_b200.h).
+
+There is NO fallback: if `lib/libgstex_b200.so` cannot be loaded (or built from csrc/ with nvcc), every
+entry point raises.  Nothing under `oracle/` is ever imported from here.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import c_float, c_int, c_size_t, c_void_p
+from typing import Optional
+
+import torch
+
+from . import build as _build
+
+_LIB: Optional[ctypes.CDLL] = None
+
+P, F, I, SZ = c_void_p, c_float, c_int, c_size_t
+
+_SIGNATURES = {
+    "gstex_abi_version": (I, []),
+    "gstex_error_string": (ctypes.c_char_p, [I]),
+    "gstex_project_points": (I, [P, P, F, F, F, F, I, P, P, P]),
+    "gstex_get_aabb_2d": (I, [P, P, F, P, P, F, F, F, F, I, P, P, P]),
+    "gstex_get_num_tiles_hit_2d": (I, [P, P, I, I, I, I, P, P]),
+    "gstex_project_bounds": (I, [P, P, F, P, P, F, F, F, F, I, I, I, I, P, P, P, P, P, P]),
+    "gstex_cumsum_workspace_bytes": (SZ, [I]),
+    "gstex_cumsum_i32": (I, [P, I, P, P, P, SZ, P]),
+    "gstex_map_gaussian_to_intersects": (I, [I, I, P, P, P, P, I, I, I, P, P, P]),
+    "gstex_sort_workspace_bytes": (SZ, [I]),
+    "gstex_sort_isects": (I, [I, P, P, P, P, I, P, SZ, P]),
+    "gstex_get_tile_bin_edges": (I, [I, P, I, P, P]),
+    "gstex_texture_workspace_bytes": (SZ, [I]),
+    "gstex_texture_forward": (I, [I, I, I, I, I, I] + [P] * 7 + [F] + [P] * 7 + [F, F, F, F, I] + [P] * 10 + [P, SZ, P]),
+    "gstex_texture_backward": (I, [I, I, I, I, I, I] + [P] * 7 + [F] + [P] * 7 + [F, F, F, F, I] + [P] * 11 + [P] * 9 +
+                               [P, SZ, I, P]),
+}
+
+EXPORTED_SYMBOLS = tuple(_SIGNATURES)
+
+
+class GstexNativeError(RuntimeError):
+    pass
+
+
+def lib_path() -> str:
+    return _build.LIB_PATH
+
+
+def load() -> ctypes.CDLL:
+    """Load (building first if stale and nvcc is present) the CUDA library; raise if impossible."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = _build.LIB_PATH
+    try:
+        if _build.sources() and _build.is_stale():
+            _build.build()
+    except Exception as exc:  # nvcc missing on a box that only has the prebuilt .so is fine
+        if not os.path.exists(path):
+            raise GstexNativeError(f"gstex_b200: CUDA library missing and cannot be built: {exc}") from exc
+    if not os.path.exists(path):
+        raise GstexNativeError(f"gstex_b200: CUDA library not found at {path}; run `python -m gstex_b200.build`")
+    lib = ctypes.CDLL(path)
+    for name, (res, args) in _SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the library does not export what the header declares
+        fn.restype = res
+        fn.argtypes = args
+    if lib.gstex_abi_version() != 1:
+        raise GstexNativeError("gstex_b200: ABI version mismatch between the Python layer and the CUDA library")
+    _LIB = lib
+    return lib
+
+
+def check(code: int, what: str) -> None:
+    if code != 0:
+        msg = load().gstex_error_string(code)
+        raise RuntimeError(f"{what} failed: {msg.decode() if msg else code} (code {code})")
+
+
+def ptr(t: Optional[torch.Tensor]):
+    if t is None:
+        return None
+    return c_void_p(t.data_ptr())
+
+
+def stream_ptr(device: torch.device):
+    return c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def require_cuda(*tensors: torch.Tensor) -> torch.device:
+    """CHECK_INPUT of the reference (bindings.h:10-15): CUDA + contiguous, else RuntimeError."""
+    dev = None
+    for t in tensors:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise RuntimeError("gstex_b200: tensor must be a CUDA tensor (there is no CPU path)")
+        if not t.is_contiguous():
+            raise RuntimeError("gstex_b200: tensor must be contiguous")
+        if dev is None:
+            dev = t.device
+        elif t.device != dev:
+            raise RuntimeError("gstex_b200: all tensors must be on the same device")
+    if dev is None:
+        raise RuntimeError("gstex_b200: no tensor given")
+    return dev
+
+
+def require_dtype(t: torch.Tensor, dtype: torch.dtype, name: str) -> None:
+    if t.dtype != dtype:
+        raise RuntimeError(f"gstex_b200: {name} must be {dtype}, got {t.dtype}")

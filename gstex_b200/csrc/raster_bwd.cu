@@ -1,0 +1,309 @@
+// raster_bwd.cu -- stage (d): back-to-front backward re-traversal.
+// Replaces texture_backward (gstex_cuda/cuda/csrc/texture.cu:331-760, wrapper :903-1053).  sm_100a.
+//
+// Differences in HOW from the reference kernel:
+//   * per-splat invariants come from the packed records (see raster_fwd.cu), staged back to front;
+//   * batches behind every pixel's last contributor are never loaded (block max of final_index);
+//   * the per-splat gradients of a warp are reduced with a transposing butterfly (16 shuffles for the
+//     13 values of the training configuration instead of 22 five-step reductions = 110 shuffles), after
+//     which lane 2s holds the total of value s, so ONE red instruction issues all of the warp's
+//     atomics for that splat instead of 22 serial ones from lane 0;
+//   * texel gradients skip zero contributions (the reference issues all 4*C atomics unconditionally).
+#include "raster_common.cuh"
+
+namespace gstex {
+
+// Transposing butterfly: on entry every lane holds K partial values; on exit v[0] of lane L holds the
+// warp total of value (L * K / 32).  K = 32: 31 shuffles; K = 16: 16 shuffles.
+template <int K>
+__device__ __forceinline__ void butterfly_reduce(float (&v)[K], const int lane) {
+    static_assert(K == 16 || K == 32, "K must be 16 or 32");
+    int off = 16;
+#pragma unroll
+    for (int half = K / 2; half >= 1; half >>= 1, off >>= 1) {
+        const bool hi = lane & off;
+#pragma unroll
+        for (int i = 0; i < half; ++i) {
+            const float keep = hi ? v[i + half] : v[i];
+            const float send = hi ? v[i] : v[i + half];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
+    }
+    if (K == 16) v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
+}
+
+struct BwdParams {
+    RasterGeom g;
+    int C;
+    const SplatRec* recs;
+    const SplatRecBwd* recs_bwd;
+    const int32_t* ids;
+    const int2* tile_bins;
+    const float* texture;
+    const float *viewmat, *c2w, *background;
+    float fx, fy, cx, cy;
+    int settings;
+    const float *final_Ts, *final_s;
+    const int32_t *final_idx, *depth_idx;
+    const float *v_output, *v_output_depth, *v_output_reg, *v_output_alpha, *v_output_texture, *v_output_normal;
+    float *v_colors, *v_opacity, *v_means, *v_scales, *v_quats, *v_uv0, *v_umap, *v_vmap, *v_texture;
+};
+
+// slot layout of the per-splat gradient vector
+//  0-2 v_colors | 3 v_opacity | 4-6 v_means | 7-8 v_scales.xy | 9-12 v_quats | (UV) 13-14 v_uv0 | 15-17 v_umap | 18-20 v_vmap
+template <bool UV>
+__device__ __forceinline__ void slot_target(const BwdParams& p, int slot, float*& base, int& stride) {
+    base = nullptr; stride = 0;
+    if (slot < 3) { base = p.v_colors + slot; stride = 3; }
+    else if (slot == 3) { base = p.v_opacity; stride = 1; }
+    else if (slot < 7) { base = p.v_means + (slot - 4); stride = 3; }
+    else if (slot < 9) { base = p.v_scales + (slot - 7); stride = 3; }
+    else if (slot < 13) { base = p.v_quats + (slot - 9); stride = 4; }
+    else if (UV) {
+        if (slot < 15) { base = p.v_uv0 + (slot - 13); stride = 2; }
+        else if (slot < 18) { base = p.v_umap + (slot - 15); stride = 3; }
+        else if (slot < 21) { base = p.v_vmap + (slot - 18); stride = 3; }
+    }
+}
+
+template <int CMAX, bool UV>
+__global__ void __launch_bounds__(kMaxTileThreads) texture_backward_kernel(const BwdParams p) {
+    constexpr int K = UV ? 32 : 16;
+    __shared__ SplatRec s_recs[kBatch];
+    __shared__ SplatRecBwd s_bwd[kBatch];
+    __shared__ int s_ids[kBatch];
+    __shared__ Camera s_cam;
+    __shared__ int s_block_final;
+    const RasterGeom g = p.g;
+    const int nthreads = blockDim.x;
+    const int lane = threadIdx.x & 31;
+    load_camera(s_cam, p.viewmat, p.c2w, p.fx, p.fy, p.cx, p.cy);
+    if (threadIdx.x == 0) s_block_final = -1;
+    __syncthreads();
+    const int tile_id = blockIdx.y * g.tiles_x + blockIdx.x;
+    const Pixel pix = make_pixel(s_cam, g, blockIdx.x, blockIdx.y);
+    const bool use_blur = p.settings & GSTEX_SET_BLUR;
+    const bool use_ndc = p.settings & GSTEX_SET_NDC_REG;
+    const bool bilinear = !(p.settings & GSTEX_SET_NEAREST);
+    const int C = p.C;
+    const int2 range = p.tile_bins[tile_id];
+
+    const int id = pix.pix_id;
+    float T = p.final_Ts[id];
+    const float3 ts_final = make_float3(p.final_s[3 * id], p.final_s[3 * id + 1], p.final_s[3 * id + 2]);
+    const int depth_final = p.depth_idx[id];
+    const int bin_final = pix.inside ? p.final_idx[id] : -1;
+    const float3 v_out = make_float3(p.v_output[3 * id], p.v_output[3 * id + 1], p.v_output[3 * id + 2]);
+    const float v_out_depth = p.v_output_depth[id], v_out_reg = p.v_output_reg[id];
+    const float3 v_out_normal =
+        make_float3(p.v_output_normal[3 * id], p.v_output_normal[3 * id + 1], p.v_output_normal[3 * id + 2]);
+    float v_tex[CMAX];
+#pragma unroll
+    for (int k = 0; k < CMAX; ++k) v_tex[k] = (k < C) ? p.v_output_texture[(size_t)C * id + k] : 0.f;
+    float v_T_running = __ldg(p.background) * v_out.x + __ldg(p.background + 1) * v_out.y +
+                        __ldg(p.background + 2) * v_out.z - p.v_output_alpha[id];
+
+    // where this lane's reduced slot goes
+    float* slot_base;
+    int slot_stride;
+    slot_target<UV>(p, (K == 16) ? (lane >> 1) : lane, slot_base, slot_stride);
+    if (K == 16 && (lane & 1)) slot_base = nullptr;
+
+    int warp_final = bin_final;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) warp_final = max(warp_final, __shfl_xor_sync(0xffffffffu, warp_final, o));
+    if (lane == 0) atomicMax(&s_block_final, warp_final);
+    __syncthreads();
+    const int block_final = min(s_block_final, range.y - 1);
+    // walk idx = block_final, block_final-1, ..., range.x in batches of kBatch
+    for (int batch_end = block_final; batch_end >= range.x; batch_end -= kBatch) {
+        __syncthreads();  // previous batch fully consumed
+        const int count = min(kBatch, batch_end + 1 - range.x);
+        stage_records(s_recs, p.recs, p.ids, batch_end, count, true, nthreads);
+        for (int j = threadIdx.x; j < count; j += nthreads) {
+            const int gid = __ldg(p.ids + batch_end - j);
+            s_ids[j] = gid;
+            s_bwd[j] = p.recs_bwd[gid];
+        }
+        __syncthreads();
+        for (int j = max(0, batch_end - warp_final); j < count; ++j) {
+            const int idx = batch_end - j;
+            const SplatRec& r = s_recs[j];
+            const float4 r0 = r.q[0], r1 = r.q[1], r2 = r.q[2], r3 = r.q[3], r4 = r.q[4];
+            const PairEval e = eval_pair(pix, r0, r1, r2, r3, r4, use_blur);
+            const bool valid = (idx <= bin_final) && !e.skip;
+            if (!__any_sync(0xffffffffu, valid)) continue;
+            float v[K];
+#pragma unroll
+            for (int k = 0; k < K; ++k) v[k] = 0.f;
+            if (valid) {
+                const float4 r5 = r.q[5], r6 = r.q[6], r7 = r.q[7];
+                const SplatRecBwd rb = s_bwd[j];
+                const float alpha = e.alpha;
+                const float ra = 1.f / (1.f - alpha);
+                T *= ra;
+                const float vis = alpha * T;
+                v[0] = vis * v_out.x; v[1] = vis * v_out.y; v[2] = vis * v_out.z;
+                const float3 v_normal_local = make_float3(vis * v_out_normal.x, vis * v_out_normal.y, vis * v_out_normal.z);
+                float v_vis = r5.x * v_out.x + r5.y * v_out.y + r5.z * v_out.z;
+                v_vis += r1.x * v_out_normal.x + r1.y * v_out_normal.y + r1.z * v_out_normal.z;
+                float3 v_diff = make_float3(0.f, 0.f, 0.f);
+                {
+                    const int th = __float_as_int(r4.z), tw = __float_as_int(r4.w);
+                    const float u = clamp01(r6.w + (r6.x * e.delta.x + r6.y * e.delta.y + r6.z * e.delta.z));
+                    const float vv = clamp01(r7.w + (r7.x * e.delta.x + r7.y * e.delta.y + r7.z * e.delta.z));
+                    const TexQuery q = tex_query(th, tw, __float_as_int(r5.w), u, vv, bilinear);
+                    const size_t o00 = (size_t)q.b00 * C, o01 = (size_t)q.b01 * C, o10 = (size_t)q.b10 * C, o11 = (size_t)q.b11 * C;
+                    float v_u = 0.f, v_v = 0.f;
+#pragma unroll
+                    for (int k = 0; k < CMAX; ++k) {
+                        if (k < C) {
+                            const float t00 = __ldg(p.texture + o00 + k), t01 = __ldg(p.texture + o01 + k);
+                            const float t10 = __ldg(p.texture + o10 + k), t11 = __ldg(p.texture + o11 + k);
+                            const float val = q.w00 * t00 + q.w01 * t01 + q.w10 * t10 + q.w11 * t11;
+                            const float v_val = vis * v_tex[k];
+                            // query_jagged_chart_vjp, texture_helpers.cuh:252-260
+                            const float g00 = q.w00 * v_val, g01 = q.w01 * v_val, g10 = q.w10 * v_val, g11 = q.w11 * v_val;
+                            if (g00 != 0.f) atomicAdd(p.v_texture + o00 + k, g00);
+                            if (g01 != 0.f) atomicAdd(p.v_texture + o01 + k, g01);
+                            if (g10 != 0.f) atomicAdd(p.v_texture + o10 + k, g10);
+                            if (g11 != 0.f) atomicAdd(p.v_texture + o11 + k, g11);
+                            if (UV && bilinear) {  // texture_helpers.cuh:262-299
+                                v_u += (float)th * (v_val * (-(1.f - q.fy) * t00 - q.fy * t01 + (1.f - q.fy) * t10 + q.fy * t11));
+                                v_v += (float)tw * (v_val * (-(1.f - q.fx) * t00 + (1.f - q.fx) * t01 - q.fx * t10 + q.fx * t11));
+                            }
+                            v_vis += val * v_tex[k];
+                        }
+                    }
+                    if (UV) {  // get_uv_vjp, texture_helpers.cuh:62-80 (the clamp is not differentiated)
+                        v[13] = v_u; v[14] = v_v;
+                        v[15] = e.delta.x * v_u; v[16] = e.delta.y * v_u; v[17] = e.delta.z * v_u;
+                        v[18] = e.delta.x * v_v; v[19] = e.delta.y * v_v; v[20] = e.delta.z * v_v;
+                        v_diff = make_float3(r6.x * v_u + r7.x * v_v, r6.y * v_u + r7.y * v_v, r6.z * v_u + r7.z * v_v);
+                    }
+                }
+                // texture.cu:650-670
+                float v_alpha = T * v_vis - T * v_T_running;
+                float v_T_cur = alpha * v_vis + (1.f - alpha) * v_T_running;
+                const float t_view = e.t * pix.view_depth;
+                float v_t = 0.f, v_t_view = 0.f;
+                {
+                    const float d = use_ndc ? (kFar * t_view - kFar * kNear) / ((kFar - kNear) * t_view) : e.t;
+                    // distortion_vjp, helpers.cuh:266-269, with the FINAL sums
+                    const float v_d = 2.f * (vis * d * ts_final.x - vis * ts_final.y) * v_out_reg;
+                    const float v_weight = (d * d * ts_final.x - 2.f * d * ts_final.y + ts_final.z) * v_out_reg;
+                    if (use_ndc) v_t_view += (kFar * kNear) / ((kFar - kNear) * t_view * t_view) * v_d;
+                    else v_t += v_d;
+                    v_alpha += v_weight * T;
+                    v_T_cur += v_weight * alpha;
+                }
+                v_T_running = v_T_cur;
+                // texture.cu:672-707
+                const float v_sigma = e.blur ? 0.f : -r1.w * e.ex * v_alpha;
+                const float v_sigma_blur = e.blur ? -r1.w * e.ex * v_alpha : 0.f;
+                const float v_l1 = r2.w * e.l1 * v_sigma, v_l2 = r3.w * e.l2 * v_sigma;
+                v[7] = -(r2.w * e.l1 * e.l1) * v_sigma * rb.aux.x;
+                v[8] = -(r3.w * e.l2 * e.l2) * v_sigma * rb.aux.y;
+                v_t += v_l1 * (pix.ray.x * r2.x + pix.ray.y * r2.y + pix.ray.z * r2.z) +
+                       v_l2 * (pix.ray.x * r3.x + pix.ray.y * r3.y + pix.ray.z * r3.z);
+                v_t += pix.ray.x * v_diff.x + pix.ray.y * v_diff.y + pix.ray.z * v_diff.z;
+                if (idx == depth_final && depth_final != -1) v_t_view += v_out_depth;
+                v_t += pix.view_depth * v_t_view;
+                float3 v_mean_extra = make_float3(0.f, 0.f, 0.f);
+                if (e.blur) {  // project_pix_vjp + transform_4x3_rot_only_transposed, texture.cu:685-692
+                    const float vxp = s_cam.fx * (2.0f * v_sigma_blur * (r4.x - pix.px));
+                    const float vyp = s_cam.fy * (2.0f * v_sigma_blur * (r4.y - pix.py));
+                    const float rw = rb.aux.z;
+                    const float nx = (r4.x - s_cam.cx) / s_cam.fx, ny = (r4.y - s_cam.cy) / s_cam.fy;  // p_view.xy * rw
+                    const float wx = vxp * rw, wy = vyp * rw, wz = -(vxp * nx + vyp * ny) * rw;
+                    v_mean_extra = make_float3(s_cam.vm[0] * wx + s_cam.vm[4] * wy + s_cam.vm[8] * wz,
+                                               s_cam.vm[1] * wx + s_cam.vm[5] * wy + s_cam.vm[9] * wz,
+                                               s_cam.vm[2] * wx + s_cam.vm[6] * wy + s_cam.vm[10] * wz);
+                }
+                // compute_tt_vjp, texture_helpers.cuh:315-334
+                const float den = clamp_tt_denom(r1.x * pix.ray.x + r1.y * pix.ray.y + r1.z * pix.ray.z);
+                const float vt_den = v_t / den;
+                const float3 v_normal_tt = make_float3((r0.x - pix.origin.x - pix.ray.x * e.t) * vt_den,
+                                                       (r0.y - pix.origin.y - pix.ray.y * e.t) * vt_den,
+                                                       (r0.z - pix.origin.z - pix.ray.z * e.t) * vt_den);
+                v[4] = -(r2.x * v_l1 + r3.x * v_l2) + r1.x * vt_den + v_mean_extra.x - v_diff.x;
+                v[5] = -(r2.y * v_l1 + r3.y * v_l2) + r1.y * vt_den + v_mean_extra.y - v_diff.y;
+                v[6] = -(r2.z * v_l1 + r3.z * v_l2) + r1.z * vt_den + v_mean_extra.z - v_diff.z;
+                {  // quat_to_rotmat_vjp, helpers.cuh:187-228; R columns: c0 = delta*v_l1, c1 = delta*v_l2, c2
+                    const float qw = rb.quat.x, qx = rb.quat.y, qy = rb.quat.z, qz = rb.quat.w;
+                    const float c00 = e.delta.x * v_l1, c01 = e.delta.y * v_l1, c02 = e.delta.z * v_l1;
+                    const float c10 = e.delta.x * v_l2, c11 = e.delta.y * v_l2, c12 = e.delta.z * v_l2;
+                    const float c20 = v_normal_tt.x + v_normal_local.x, c21 = v_normal_tt.y + v_normal_local.y,
+                                c22 = v_normal_tt.z + v_normal_local.z;
+                    v[9] = 2.f * (qx * (c12 - c21) + qy * (c20 - c02) + qz * (c01 - c10));
+                    v[10] = 2.f * (-2.f * qx * (c11 + c22) + qy * (c01 + c10) + qz * (c02 + c20) + qw * (c12 - c21));
+                    v[11] = 2.f * (qx * (c01 + c10) - 2.f * qy * (c00 + c22) + qz * (c12 + c21) + qw * (c20 - c02));
+                    v[12] = 2.f * (qx * (c02 + c20) + qy * (c12 + c21) - 2.f * qz * (c00 + c11) + qw * (c01 - c10));
+                }
+                v[3] = e.ex * v_alpha;
+            }
+            butterfly_reduce<K>(v, lane);
+            if (slot_base != nullptr && v[0] != 0.f) atomicAdd(slot_base + (size_t)s_ids[j] * slot_stride, v[0]);
+        }
+    }
+}
+
+}  // namespace gstex
+
+using namespace gstex;
+
+template <int CMAX>
+static void launch_bwd(const BwdParams& p, bool uv, cudaStream_t st) {
+    const dim3 grid(p.g.tiles_x, p.g.tiles_y);
+    if (uv) texture_backward_kernel<CMAX, true><<<grid, p.g.threads, 0, st>>>(p);
+    else texture_backward_kernel<CMAX, false><<<grid, p.g.threads, 0, st>>>(p);
+}
+
+extern "C" int gstex_texture_backward(
+    int img_height, int img_width, int block_width, int channels, int n, int num_intersects,
+    const int32_t* texture_dims, const int32_t* gaussian_ids_sorted, const int32_t* tile_bins, const float* colors,
+    const float* opacities, const float* means, const float* scales, float glob_scale, const float* quats,
+    const float* uv0, const float* umap, const float* vmap, const float* texture, const float* viewmat,
+    const float* c2w, float fx, float fy, float cx, float cy, int settings, const float* background,
+    const float* final_Ts, const int32_t* final_idx, const int32_t* depth_idx, const float* final_s,
+    const float* v_output, const float* v_output_depth, const float* v_output_reg, const float* v_output_alpha,
+    const float* v_output_texture, const float* v_output_normal, float* v_colors, float* v_opacity, float* v_means,
+    float* v_scales, float* v_quats, float* v_uv0, float* v_umap, float* v_vmap, float* v_texture, void* workspace,
+    size_t workspace_bytes, int records_valid, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (img_height <= 0 || img_width <= 0 || block_width < 2 || block_width > 16 || n < 0 || num_intersects < 0)
+        return GSTEX_E_BADARG;
+    if (settings & ~GSTEX_SETTINGS_SUPPORTED) return GSTEX_E_UNSUPPORTED;
+    if (channels < 1 || channels > GSTEX_MAX_CHANNELS) return GSTEX_E_UNSUPPORTED;
+    if (n == 0 || num_intersects == 0) return GSTEX_OK;  // gradients stay zero (texture.py:331-340)
+    if (!texture_dims || !gaussian_ids_sorted || !tile_bins || !colors || !opacities || !means || !scales || !quats ||
+        !uv0 || !umap || !vmap || !texture || !viewmat || !c2w || !background || !final_Ts || !final_idx ||
+        !depth_idx || !final_s || !v_output || !v_output_depth || !v_output_reg || !v_output_alpha ||
+        !v_output_texture || !v_output_normal || !v_colors || !v_opacity || !v_means || !v_scales || !v_quats ||
+        !v_uv0 || !v_umap || !v_vmap || !v_texture || !workspace)
+        return GSTEX_E_BADARG;
+    if (workspace_bytes < gstex_texture_workspace_bytes(n)) return GSTEX_E_WORKSPACE;
+    SplatRec* recs = ws_recs(workspace);
+    SplatRecBwd* recs_bwd = ws_recs_bwd(workspace, n);
+    if (!records_valid) {
+        const int rc = launch_pack_records(n, texture_dims, colors, opacities, means, scales, glob_scale, quats, uv0, umap,
+                                           vmap, viewmat, c2w, fx, fy, cx, cy, recs, recs_bwd, st);
+        if (rc != GSTEX_OK) return rc;
+    }
+    BwdParams p;
+    p.g = make_raster_geom(img_height, img_width, block_width);
+    p.C = channels; p.recs = recs; p.recs_bwd = recs_bwd; p.ids = gaussian_ids_sorted;
+    p.tile_bins = reinterpret_cast<const int2*>(tile_bins); p.texture = texture; p.viewmat = viewmat; p.c2w = c2w;
+    p.background = background; p.fx = fx; p.fy = fy; p.cx = cx; p.cy = cy; p.settings = settings;
+    p.final_Ts = final_Ts; p.final_s = final_s; p.final_idx = final_idx; p.depth_idx = depth_idx;
+    p.v_output = v_output; p.v_output_depth = v_output_depth; p.v_output_reg = v_output_reg;
+    p.v_output_alpha = v_output_alpha; p.v_output_texture = v_output_texture; p.v_output_normal = v_output_normal;
+    p.v_colors = v_colors; p.v_opacity = v_opacity; p.v_means = v_means; p.v_scales = v_scales; p.v_quats = v_quats;
+    p.v_uv0 = v_uv0; p.v_umap = v_umap; p.v_vmap = v_vmap; p.v_texture = v_texture;
+    const bool uv = (settings & GSTEX_SET_UV_GRAD) != 0;
+    if (channels <= 3) launch_bwd<3>(p, uv, st);
+    else if (channels <= 6) launch_bwd<6>(p, uv, st);
+    else launch_bwd<GSTEX_MAX_CHANNELS>(p, uv, st);
+    GSTEX_LAUNCH_CHECK();
+    return GSTEX_OK;
+}

@@ -1,0 +1,200 @@
+"""Stages (c)+(d): `texture_gaussians`, the drop-in for the reference's `gstex_cuda/texture.py`.
+
+Same positional signature (27 arguments), the same six outputs
+`(out_img, out_depth, out_reg, out_alpha, out_texture, out_normal)` and the same autograd contract
+(gradients for colors, opacity, means, scales, quats, uv0, umap, vmap, texture; `None` elsewhere) as
+/root/reference/submodules/GStex_cuda/gstex_cuda/texture.py:14-408.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+from torch import Tensor
+from torch.autograd import Function
+
+from . import _lib
+from .utils import bin_and_sort_gaussians, compute_cumulative_intersects
+
+SUPPORTED_SETTINGS = (1 << 2) | (1 << 8) | (1 << 9) | (1 << 10)
+
+
+def texture_gaussians(
+    texture_info: Tuple[int, int, int],
+    texture_dims: Tensor,
+    centers: Tensor,
+    extents: Tensor,
+    depths: Tensor,
+    num_tiles_hit: Tensor,
+    colors: Tensor,
+    opacity: Tensor,
+    means: Tensor,
+    scales: Tensor,
+    glob_scale,
+    quats: Tensor,
+    uv0: Tensor,
+    umap: Tensor,
+    vmap: Tensor,
+    texture: Tensor,
+    viewmat: Tensor,
+    c2w: Tensor,
+    fx: float,
+    fy: float,
+    cx: float,
+    cy: float,
+    img_height: int,
+    img_width: int,
+    block_width: int,
+    settings: int,
+    background: Optional[Tensor] = None,
+    use_torch_impl: bool = False,
+):
+    """Rasterizes textured 2D gaussians (ref: texture.py:14-150)."""
+    assert block_width > 1 and block_width <= 16, "block_width must be between 2 and 16"
+    if use_torch_impl:
+        raise NotImplementedError("gstex_b200 has no PyTorch/CPU rasterizer: the CUDA kernels are the only path")
+    if colors.dtype == torch.uint8:
+        colors = colors.float() / 255
+    if background is not None:
+        assert background.shape[0] == colors.shape[-1], (
+            f"incorrect shape of background color tensor, expected shape {colors.shape[-1]}")
+    else:
+        background = torch.ones(colors.shape[-1], dtype=torch.float32, device=colors.device)
+    if colors.ndimension() != 2:
+        raise ValueError("colors must have dimensions (N, D)")
+    if colors.shape[-1] != 3:
+        raise ValueError("colors must have 3 channels (the reference kernels read float3, texture.cu:18)")
+    if int(settings) & ~SUPPORTED_SETTINGS:
+        raise NotImplementedError(
+            f"settings {int(settings):#x}: only bits 2, 8, 9, 10 are implemented (15-29 are viewer visualisation)")
+    return _TextureGaussians.apply(
+        texture_info, texture_dims.contiguous(), centers.contiguous(), extents.contiguous(), depths.contiguous(),
+        num_tiles_hit.contiguous(), colors.contiguous(), opacity.contiguous(), means.contiguous(),
+        scales.contiguous(), glob_scale, quats.contiguous(), uv0.contiguous(), umap.contiguous(), vmap.contiguous(),
+        texture.contiguous(), viewmat.contiguous(), c2w.contiguous(), fx, fy, cx, cy, img_height, img_width,
+        block_width, settings, background.contiguous())
+
+
+def _raster_forward(texture_info, texture_dims, gaussian_ids_sorted, tile_bins, colors, opacity, means, scales,
+                    glob_scale, quats, uv0, umap, vmap, texture, viewmat, c2w, fx, fy, cx, cy, img_height, img_width,
+                    block_width, settings, background, num_intersects):
+    """ref: `_C.texture_forward` (cuda/csrc/texture.cu:762-901).  Returns the 9 tensors + the workspace
+    holding the per-view packed records (re-used by the backward)."""
+    dev = _lib.require_cuda(texture_dims, colors, opacity, means, scales, quats, uv0, umap, vmap, texture, viewmat,
+                            c2w, background, tile_bins)
+    _lib.require_dtype(texture_dims, torch.int32, "texture_dims")
+    for t, nm in ((colors, "colors"), (opacity, "opacity"), (means, "means"), (scales, "scales"), (quats, "quats"),
+                  (uv0, "uv0"), (umap, "umap"), (vmap, "vmap"), (texture, "texture"), (viewmat, "viewmat"),
+                  (c2w, "c2w"), (background, "background")):
+        _lib.require_dtype(t, torch.float32, nm)
+    H, W, C = int(img_height), int(img_width), int(texture_info[2])
+    n = means.shape[0]
+    f32 = dict(dtype=torch.float32, device=dev)
+    i32 = dict(dtype=torch.int32, device=dev)
+    out_img = torch.empty((H, W, 3), **f32)
+    out_depth = torch.empty((H, W), **f32)
+    out_reg = torch.empty((H, W), **f32)
+    out_texture = torch.empty((H, W, C), **f32)
+    out_normal = torch.empty((H, W, 3), **f32)
+    final_Ts = torch.empty((H, W), **f32)
+    final_idx = torch.empty((H, W), **i32)
+    depth_idx = torch.empty((H, W), **i32)
+    out_reg_s = torch.empty((H, W, 3), **f32)
+    lib = _lib.load()
+    ws = torch.empty((lib.gstex_texture_workspace_bytes(n),), dtype=torch.uint8, device=dev)
+    p = _lib.ptr
+    with torch.cuda.device(dev):
+        rc = lib.gstex_texture_forward(
+            H, W, int(block_width), C, n, int(num_intersects), p(texture_dims), p(gaussian_ids_sorted), p(tile_bins),
+            p(colors), p(opacity), p(means), p(scales), float(glob_scale), p(quats), p(uv0), p(umap), p(vmap),
+            p(texture), p(viewmat), p(c2w), float(fx), float(fy), float(cx), float(cy), int(settings), p(background),
+            p(out_img), p(out_depth), p(out_reg), p(out_texture), p(out_normal), p(final_Ts), p(final_idx),
+            p(depth_idx), p(out_reg_s), p(ws), ws.numel(), _lib.stream_ptr(dev))
+    _lib.check(rc, "gstex_texture_forward")
+    return (out_img, out_depth, out_reg, out_texture, out_normal, final_Ts, final_idx, depth_idx, out_reg_s), ws
+
+
+class _TextureGaussians(Function):
+    """ref: texture.py:152-408."""
+
+    @staticmethod
+    def forward(ctx, texture_info, texture_dims, centers, extents, depths, num_tiles_hit, colors, opacity, means,
+                scales, glob_scale, quats, uv0, umap, vmap, texture, viewmat, c2w, fx, fy, cx, cy, img_height,
+                img_width, block_width, settings, background=None):
+        num_points = centers.size(0)
+        tile_bounds = ((img_width + block_width - 1) // block_width, (img_height + block_width - 1) // block_width, 1)
+        dev = centers.device
+        num_intersects, cum_tiles_hit = compute_cumulative_intersects(num_tiles_hit)
+        if num_intersects < 1:
+            # The reference leaves most outputs undefined here (texture.py:197-205, a latent NameError guarded
+            # by the model at NS/models/gstex.py:1127); we return a well-formed empty render instead.
+            gaussian_ids_sorted = torch.zeros((0,), dtype=torch.int32, device=dev)
+            tile_bins = torch.zeros((tile_bounds[0] * tile_bounds[1], 2), dtype=torch.int32, device=dev)
+        else:
+            (_, _, _, gaussian_ids_sorted, tile_bins) = bin_and_sort_gaussians(
+                num_points, num_intersects, centers, extents, depths, cum_tiles_hit, tile_bounds, block_width)
+        outputs, ws = _raster_forward(texture_info, texture_dims, gaussian_ids_sorted, tile_bins, colors, opacity,
+                                      means, scales, glob_scale, quats, uv0, umap, vmap, texture, viewmat, c2w, fx, fy,
+                                      cx, cy, img_height, img_width, block_width, settings, background,
+                                      max(num_intersects, 0))
+        out_img, out_depth, out_reg, out_texture, out_normal, final_Ts, final_idx, depth_idx, out_reg_s = outputs
+        ctx.img_width, ctx.img_height = img_width, img_height
+        ctx.texture_info = texture_info
+        ctx.fx, ctx.fy, ctx.cx, ctx.cy = fx, fy, cx, cy
+        ctx.glob_scale = glob_scale
+        ctx.num_intersects = num_intersects
+        ctx.block_width = block_width
+        ctx.settings = settings
+        ctx.workspace = ws  # packed per-view records, valid as long as the inputs are unchanged
+        ctx.save_for_backward(texture_dims, gaussian_ids_sorted, tile_bins, colors, opacity, means, scales, quats,
+                              uv0, umap, vmap, texture, viewmat, c2w, background, final_Ts, final_idx, depth_idx,
+                              out_reg_s)
+        out_alpha = 1 - final_Ts
+        return out_img, out_depth, out_reg, out_alpha, out_texture, out_normal
+
+    @staticmethod
+    def backward(ctx, v_out_img, v_out_depth, v_out_reg, v_out_alpha, v_out_texture, v_out_normal):
+        (texture_dims, gaussian_ids_sorted, tile_bins, colors, opacity, means, scales, quats, uv0, umap, vmap,
+         texture, viewmat, c2w, background, final_Ts, final_idx, depth_idx, out_reg_s) = ctx.saved_tensors
+        H, W = ctx.img_height, ctx.img_width
+        C = int(ctx.texture_info[2])
+        dev = means.device
+
+        def grad_or_zero(g, shape):
+            if g is None:
+                return torch.zeros(shape, dtype=torch.float32, device=dev)
+            return g.contiguous().float()
+
+        v_out_img = grad_or_zero(v_out_img, (H, W, 3))
+        v_out_depth = grad_or_zero(v_out_depth, (H, W))
+        v_out_reg = grad_or_zero(v_out_reg, (H, W))
+        v_out_alpha = grad_or_zero(v_out_alpha, (H, W))  # ref: texture.py:306-307
+        v_out_texture = grad_or_zero(v_out_texture, (H, W, C))
+        v_out_normal = grad_or_zero(v_out_normal, (H, W, 3))
+
+        v_colors = torch.zeros_like(colors)
+        v_opacity = torch.zeros_like(opacity)
+        v_means = torch.zeros_like(means)
+        v_scales = torch.zeros_like(scales)
+        v_quats = torch.zeros_like(quats)
+        v_uv0 = torch.zeros_like(uv0)
+        v_umap = torch.zeros_like(umap)
+        v_vmap = torch.zeros_like(vmap)
+        v_texture = torch.zeros_like(texture)
+        if ctx.num_intersects >= 1:
+            lib = _lib.load()
+            ws = ctx.workspace
+            p = _lib.ptr
+            with torch.cuda.device(dev):
+                rc = lib.gstex_texture_backward(
+                    int(H), int(W), int(ctx.block_width), C, means.shape[0], int(ctx.num_intersects),
+                    p(texture_dims), p(gaussian_ids_sorted), p(tile_bins), p(colors), p(opacity), p(means), p(scales),
+                    float(ctx.glob_scale), p(quats), p(uv0), p(umap), p(vmap), p(texture), p(viewmat), p(c2w),
+                    float(ctx.fx), float(ctx.fy), float(ctx.cx), float(ctx.cy), int(ctx.settings), p(background),
+                    p(final_Ts), p(final_idx), p(depth_idx), p(out_reg_s), p(v_out_img), p(v_out_depth), p(v_out_reg),
+                    p(v_out_alpha), p(v_out_texture), p(v_out_normal), p(v_colors), p(v_opacity), p(v_means),
+                    p(v_scales), p(v_quats), p(v_uv0), p(v_umap), p(v_vmap), p(v_texture), p(ws), ws.numel(), 1,
+                    _lib.stream_ptr(dev))
+            _lib.check(rc, "gstex_texture_backward")
+        return (None, None, None, None, None, None, v_colors, v_opacity, v_means, v_scales, None, v_quats, v_uv0,
+                v_umap, v_vmap, v_texture, None, None, None, None, None, None, None, None, None, None, None)

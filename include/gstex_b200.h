@@ -1,0 +1,141 @@
+/*
+ * gstex_b200.h -- C ABI of the B200-native GStex rasterizer hot path (libgstex_b200.so).
+ *
+ * One entry point per native function the reference's Python binds for this path (the pybind11
+ * module `_C` of nvnhat95/GStex, submodules/GStex_cuda/gstex_cuda/cuda/csrc/ext.cpp:8-24) plus the
+ * three torch library calls the reference makes in between (cumsum, sort, gather).  Conventions:
+ *   - every pointer is a DEVICE pointer into memory owned by the caller (PyTorch's caching
+ *     allocator in the shipped host layer); nothing is allocated or freed behind the caller's back,
+ *     scratch space is passed in as `workspace` and sized by the matching *_workspace_bytes();
+ *   - tensors are contiguous row-major, fp32 / int32 / int64 exactly as in the reference;
+ *   - every call enqueues work on `stream` (a cudaStream_t passed as void*) and returns without
+ *     synchronising; the return value is 0 on success, a negative GSTEX_E_* argument error, or a
+ *     positive cudaError_t from the launch (the reference checks neither: csrc/config.h:6-17 is
+ *     never used);
+ *   - re-entrant, no global state.
+ * "ref:" comments name the reference interface each function replaces; paths are relative to
+ * /root/reference/submodules/GStex_cuda/gstex_cuda/.
+ */
+#ifndef GSTEX_B200_H
+#define GSTEX_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSTEX_B200_ABI_VERSION 1
+
+#define GSTEX_OK 0
+#define GSTEX_E_BADARG (-1)      /* null pointer, negative size, block_width outside [2,16] ... */
+#define GSTEX_E_UNSUPPORTED (-2) /* settings bits 15-29 (viewer visualisation), channels > 16 */
+#define GSTEX_E_WORKSPACE (-3)   /* workspace too small */
+
+/* settings bit-field, ref: cuda/csrc/texture.cu:54-65,381-387 */
+#define GSTEX_SET_NEAREST (1 << 2)
+#define GSTEX_SET_UV_GRAD (1 << 8)
+#define GSTEX_SET_BLUR (1 << 9)
+#define GSTEX_SET_NDC_REG (1 << 10)
+#define GSTEX_SETTINGS_SUPPORTED (GSTEX_SET_NEAREST | GSTEX_SET_UV_GRAD | GSTEX_SET_BLUR | GSTEX_SET_NDC_REG)
+#define GSTEX_MAX_CHANNELS 16
+
+int gstex_abi_version(void);
+/* Human-readable text for a return code of this library (static storage). */
+const char* gstex_error_string(int code);
+
+/* ---- stage (a): per-splat projection, bounds, tile count ------------------------------------- */
+
+/* ref: get_aabb_2d.py:22-32 project_points(points, viewmat, intrins, clip=False).
+ * viewmat: 12 floats, row-major [R|t].  xys (N,2) and/or depths (N) may be NULL. */
+int gstex_project_points(const float* means, const float* viewmat, float fx, float fy, float cx, float cy, int n,
+                         float* xys, float* depths, void* stream);
+
+/* ref: cuda/csrc/get_aabb_2d.cu:91-126 get_aabb_2d_tensor -> kernel :11-89.  centers, extents: (N,2). */
+int gstex_get_aabb_2d(const float* means, const float* scales, float glob_scale, const float* quats,
+                      const float* viewmat, float fx, float fy, float cx, float cy, int n, float* centers,
+                      float* extents, void* stream);
+
+/* ref: get_aabb_2d.py:70-91 get_num_tiles_hit_2d(centers, extents, H, W, block_width) -> (N,) int32. */
+int gstex_get_num_tiles_hit_2d(const float* centers, const float* extents, int n, int img_height, int img_width,
+                               int block_width, int32_t* num_tiles_hit, void* stream);
+
+/* The three calls above fused into one kernel (what NS/models/gstex.py:1077-1080 asks for every step).
+ * Any output pointer may be NULL. */
+int gstex_project_bounds(const float* means, const float* scales, float glob_scale, const float* quats,
+                         const float* viewmat, float fx, float fy, float cx, float cy, int n, int img_height,
+                         int img_width, int block_width, float* xys, float* depths, float* centers, float* extents,
+                         int32_t* num_tiles_hit, void* stream);
+
+/* ---- stage (b): prefix sum, key emit, radix sort, tile ranges --------------------------------- */
+
+/* ref: utils.py:57 torch.cumsum(num_tiles_hit, dim=0, dtype=int32): inclusive scan.  `total`, if not
+ * NULL, receives out[n-1] (device int32; 0 when n == 0).  workspace: gstex_cumsum_workspace_bytes(n). */
+size_t gstex_cumsum_workspace_bytes(int n);
+int gstex_cumsum_i32(const int32_t* in, int n, int32_t* out, int32_t* total, void* workspace, size_t workspace_bytes,
+                     void* stream);
+
+/* ref: cuda/csrc/bindings.cu:77-121 map_gaussian_to_intersects_tensor -> kernel forward.cu:13-71
+ * (wrapped=false).  Zero-fills isect_ids (I int64) and gaussian_ids (I int32) first, as the reference's
+ * torch::zeros does, so the reserved-but-unwritten slots of clipped splats keep key 0 / id 0. */
+int gstex_map_gaussian_to_intersects(int n, int num_intersects, const float* centers, const float* extents,
+                                     const float* depths, const int32_t* cum_tiles_hit, int tiles_x, int tiles_y,
+                                     int block_width, int64_t* isect_ids, int32_t* gaussian_ids, void* stream);
+
+/* ref: utils.py:159-160 torch.sort(isect_ids) + torch.gather(gaussian_ids, 0, idx): stable ascending
+ * LSD radix sort of the (tile<<32 | depth bits) keys carrying the splat id as payload.  Only key bits
+ * [0, key_bits) are examined (32 + bits needed for tiles_x*tiles_y - 1; pass 64 to sort on everything);
+ * keys must be non-negative.  Inputs are not modified. */
+size_t gstex_sort_workspace_bytes(int num_intersects);
+int gstex_sort_isects(int num_intersects, const int64_t* isect_ids, const int32_t* gaussian_ids,
+                      int64_t* isect_ids_sorted, int32_t* gaussian_ids_sorted, int key_bits, void* workspace,
+                      size_t workspace_bytes, void* stream);
+
+/* ref: cuda/csrc/bindings.cu:123-141 get_tile_bin_edges_tensor -> kernel forward.cu:76-98.
+ * Zero-fills tile_bins (num_tiles,2) int32 first. */
+int gstex_get_tile_bin_edges(int num_intersects, const int64_t* isect_ids_sorted, int num_tiles, int32_t* tile_bins,
+                             void* stream);
+
+/* ---- stages (c), (d): textured forward compositing and backward -------------------------------- */
+
+/* ref: cuda/csrc/texture.cu:762-901 texture_forward_tensor -> kernel :11-329.
+ * Inputs as in the reference (texture_dims (N,3) int32 {h,w,start}; uv0 (N,1,2); umap, vmap (N,1,3);
+ * texture (T,C); viewmat >= 12 floats; c2w >= 12 floats; background 3 floats).  All nine outputs are
+ * written for every pixel (no zero-fill needed):
+ *   out_img (H,W,3) out_depth (H,W) out_reg (H,W) out_texture (H,W,C) out_normal (H,W,3)
+ *   final_Ts (H,W) final_idx (H,W) int32 depth_idx (H,W) int32 out_reg_s (H,W,3).
+ * workspace: gstex_texture_forward_workspace_bytes(n) (per-view packed splat records). */
+size_t gstex_texture_workspace_bytes(int n);
+int gstex_texture_forward(int img_height, int img_width, int block_width, int channels, int n, int num_intersects,
+                          const int32_t* texture_dims, const int32_t* gaussian_ids_sorted, const int32_t* tile_bins,
+                          const float* colors, const float* opacities, const float* means, const float* scales,
+                          float glob_scale, const float* quats, const float* uv0, const float* umap,
+                          const float* vmap, const float* texture, const float* viewmat, const float* c2w, float fx,
+                          float fy, float cx, float cy, int settings, const float* background, float* out_img,
+                          float* out_depth, float* out_reg, float* out_texture, float* out_normal, float* final_Ts,
+                          int32_t* final_idx, int32_t* depth_idx, float* out_reg_s, void* workspace,
+                          size_t workspace_bytes, void* stream);
+
+/* ref: cuda/csrc/texture.cu:903-1053 texture_backward_tensor -> kernel :331-760.
+ * The nine gradient outputs (shapes of the inputs they belong to) must be ZERO-FILLED by the caller
+ * (the reference allocates them with torch::zeros); gradients are accumulated into them.
+ * `workspace` may be the one the forward of the same view filled (records_valid != 0 skips re-packing). */
+int gstex_texture_backward(int img_height, int img_width, int block_width, int channels, int n, int num_intersects,
+                           const int32_t* texture_dims, const int32_t* gaussian_ids_sorted, const int32_t* tile_bins,
+                           const float* colors, const float* opacities, const float* means, const float* scales,
+                           float glob_scale, const float* quats, const float* uv0, const float* umap,
+                           const float* vmap, const float* texture, const float* viewmat, const float* c2w, float fx,
+                           float fy, float cx, float cy, int settings, const float* background,
+                           const float* final_Ts, const int32_t* final_idx, const int32_t* depth_idx,
+                           const float* final_s, const float* v_output, const float* v_output_depth,
+                           const float* v_output_reg, const float* v_output_alpha, const float* v_output_texture,
+                           const float* v_output_normal, float* v_colors, float* v_opacity, float* v_means,
+                           float* v_scales, float* v_quats, float* v_uv0, float* v_umap, float* v_vmap,
+                           float* v_texture, void* workspace, size_t workspace_bytes, int records_valid,
+                           void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSTEX_B200_H */

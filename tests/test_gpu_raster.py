@@ -1,0 +1,167 @@
+"""GPU parity, stages (c)+(d): forward compositing and backward, through the public
+`texture_gaussians` (-> C ABI).  Checked against the CPU oracle, the golden vectors of the reference's
+torch rasterizer, and the reference's own CUDA extension when oracle/_ref holds it.
+Tolerances (north_star): images 1e-5 relative, gradients 1e-4 relative, indices exact."""
+import numpy as np
+import pytest
+import torch
+
+from common import (FWD_KEYS, GRAD_KEYS, GRAD_RTOL, IMG_RTOL, VOUT_KEYS, assert_close_frac, golden_files, load_golden,
+                    run_oracle_pipeline, scene_to_numpy)
+
+pytestmark = pytest.mark.gpu
+
+# discrete decisions (alpha < 1/255, T <= 1e-4, T > 0.5, blur floor) can flip for isolated pixels between two
+# fp32 implementations; such pixels are counted and bounded, everything else must meet the tolerance
+MAX_FLIP_FRAC = 2e-4
+
+SCENES = [
+    dict(name="cfg1", n=400, width=72, height=56, texels=400 * 16, settings=1 << 8, C=3),
+    dict(name="cfg1", n=400, width=72, height=56, texels=400 * 16, settings=0, C=3),
+    dict(name="cfg2", n=6000, width=160, height=160, texels=60000, settings=(1 << 9) | (1 << 10), C=3),
+    dict(name="cfg2", n=6000, width=160, height=160, texels=0, settings=(1 << 9) | (1 << 10), C=3),  # 2DGS 1x1 charts
+    dict(name="cfg2", n=3000, width=96, height=128, texels=30000, settings=(1 << 8) | (1 << 9) | (1 << 10), C=6),
+    dict(name="cfg2", n=3000, width=96, height=128, texels=30000, settings=(1 << 2) | (1 << 9), C=3),  # nearest
+    dict(name="cfg4", n=20000, width=240, height=136, texels=200000, settings=(1 << 9) | (1 << 10), C=3),
+    dict(name="cfg1", n=300, width=40, height=40, texels=300 * 9, settings=1 << 9, C=10),
+]
+
+
+def _id(c):
+    return f"{c['name']}-n{c['n']}-{c['width']}x{c['height']}-s{c['settings']}-C{c['C']}-T{c['texels']}"
+
+
+def run_ours(s, v=None, block_width=16):
+    """The reference's call sequence (example.py:145-184 / NS/models/gstex.py:1075-1170) on our package."""
+    import gstex_b200 as G
+
+    sd = {k: (x.cuda() if isinstance(x, torch.Tensor) else x) for k, x in s.items()}
+    intr = (s["fx"], s["fy"], s["cx"], s["cy"])
+    H, W = s["H"], s["W"]
+    leaves = {}
+    for k in ["colors", "opacities", "means", "scales", "quats", "uv0", "umap", "vmap", "texture"]:
+        leaves[k] = sd[k].clone().requires_grad_(v is not None)
+    _, depths = G.project_points(leaves["means"].detach(), sd["viewmat"][:3, :], intr)
+    centers, extents = G.get_aabb_2d(leaves["means"].detach(), leaves["scales"].detach(), 1, leaves["quats"].detach(),
+                                     sd["viewmat"][:3, :], intr)
+    nth = G.get_num_tiles_hit_2d(centers, extents, H, W, block_width)
+    outs = G.texture_gaussians(s["texture_info"], sd["texture_dims"], centers, extents, depths, nth, leaves["colors"],
+                               leaves["opacities"], leaves["means"], leaves["scales"], 1, leaves["quats"],
+                               leaves["uv0"], leaves["umap"], leaves["vmap"], leaves["texture"], sd["viewmat"],
+                               sd["c2w"], *intr, H, W, block_width, s["settings"], sd["background"])
+    res = dict(zip(FWD_KEYS, outs))
+    if v is not None:
+        vd = {k: x.cuda() for k, x in v.items()}
+        loss = sum((res[k] * vd["v_" + k]).sum() for k in FWD_KEYS)
+        loss.backward()
+        for k, gk in zip(["colors", "opacities", "means", "scales", "quats", "uv0", "umap", "vmap", "texture"], GRAD_KEYS):
+            res[gk] = leaves[k].grad
+    res.update(centers=centers, extents=extents, depths=depths, num_tiles_hit=nth)
+    return {k: (x.detach().cpu().numpy() if isinstance(x, torch.Tensor) else x) for k, x in res.items()}, sd
+
+
+def compare(ours, ref, fwd_rtol=IMG_RTOL, grad_rtol=GRAD_RTOL, what=""):
+    flips = {}
+    for k in FWD_KEYS:
+        rt = 1e-4 if k == "out_reg" else fwd_rtol  # out_reg cancels terms ~100x its size (see test_oracle_golden)
+        flips[k] = assert_close_frac(ours[k], ref[k], rt, f"{what}{k}", MAX_FLIP_FRAC)
+    for k in GRAD_KEYS:
+        if k in ref:
+            flips[k] = assert_close_frac(ours[k], ref[k], grad_rtol, f"{what}{k}", MAX_FLIP_FRAC * 10)
+    return flips
+
+
+@pytest.mark.parametrize("cfg", SCENES, ids=_id)
+def test_forward_backward_matches_oracle(cfg):
+    from gstex_b200.synthetic import make_scene, make_upstream_grads
+
+    s = make_scene(cfg["name"], n=cfg["n"], width=cfg["width"], height=cfg["height"], texels=cfg["texels"],
+                   settings=cfg["settings"], channels=cfg["C"])
+    v = make_upstream_grads(s)
+    ours, _ = run_ours(s, v)
+    d = scene_to_numpy(s)
+    ref = run_oracle_pipeline(d, {k: x.numpy() for k, x in v.items()})
+    compare(ours, ref, what="oracle:")
+
+
+@pytest.mark.parametrize("cfg", SCENES[:7], ids=_id)
+def test_forward_backward_matches_reference_extension(cfg):
+    from oracle import ref_ext
+
+    C = ref_ext.load()
+    if C is None:
+        pytest.skip("oracle/_ref/gstex_ref_C.so not built (python oracle/build_ref.py)")
+    from gstex_b200.synthetic import make_scene, make_upstream_grads
+
+    s = make_scene(cfg["name"], n=cfg["n"], width=cfg["width"], height=cfg["height"], texels=cfg["texels"],
+                   settings=cfg["settings"], channels=cfg["C"])
+    v = make_upstream_grads(s)
+    ours, sd = run_ours(s, v)
+    vd = {k: x.cuda() for k, x in v.items()}
+    t = lambda k: torch.from_numpy(ours[k]).cuda()  # noqa: E731
+    ref = ref_ext.ref_forward_backward(C, sd, t("centers"), t("extents"), t("depths"), t("num_tiles_hit"), vd)
+    ref = {k: (x.detach().cpu().numpy() if isinstance(x, torch.Tensor) else x) for k, x in ref.items()}
+    compare(ours, ref, what="refext:")
+
+
+@pytest.mark.parametrize("path", golden_files(), ids=lambda p: p.split("golden_")[-1][:-4])
+def test_matches_golden_of_reference_torch_rasterizer(path):
+    d = load_golden(path)
+    s = {k: torch.from_numpy(d[k]) for k in ["means", "scales", "quats", "opacities", "colors", "texture_dims",
+                                             "texture", "uv0", "umap", "vmap", "viewmat", "c2w", "background"]}
+    s.update(fx=d["fx"], fy=d["fy"], cx=d["cx"], cy=d["cy"], H=d["H"], W=d["W"], settings=d["settings"], C=d["C"],
+             texture_info=(len(d["means"]), 1, d["C"]))
+    v = {k: torch.from_numpy(d[k]) for k in VOUT_KEYS}
+    ours, _ = run_ours(s, v)
+    for k in ["out_img", "out_depth", "out_reg", "out_texture", "out_normal"]:
+        assert_close_frac(ours[k], d["ref_" + k], 1e-4 if k == "out_reg" else 1e-5, k, MAX_FLIP_FRAC)
+    assert_close_frac(1.0 - ours["out_alpha"], d["ref_final_Ts"], 1e-5, "final_Ts", MAX_FLIP_FRAC)
+    for k in GRAD_KEYS:
+        assert_close_frac(ours[k], d["ref_" + k], 1e-4, k, MAX_FLIP_FRAC * 10)
+
+
+@pytest.mark.parametrize("bw", [2, 5, 8, 13])
+def test_block_widths(bw):
+    from gstex_b200.synthetic import make_scene, make_upstream_grads
+
+    s = make_scene("cfg2", n=1500, width=50, height=38, texels=15000, settings=(1 << 9) | (1 << 10))
+    s["block_width"] = bw
+    v = make_upstream_grads(s)
+    ours, _ = run_ours(s, v, block_width=bw)
+    d = scene_to_numpy(s)
+    d["bw"] = bw
+    ref = run_oracle_pipeline(d, {k: x.numpy() for k, x in v.items()})
+    compare(ours, ref, what=f"bw{bw}:")
+
+
+def test_no_intersections_is_well_formed():
+    """The reference is ill-formed here (texture.py:197-205); we return background and zero gradients."""
+    from gstex_b200.synthetic import make_scene, make_upstream_grads
+
+    s = make_scene("cfg2", n=64, width=48, height=48, texels=640)
+    s["means"] = s["means"] + torch.tensor([1000.0, 0.0, 0.0])  # everything off-screen
+    s["background"] = torch.tensor([0.2, 0.4, 0.6])
+    ours, _ = run_ours(s, make_upstream_grads(s))
+    assert np.allclose(ours["out_img"], np.array([0.2, 0.4, 0.6], np.float32)[None, None, :])
+    assert np.all(ours["out_alpha"] == 0) and np.all(ours["v_means"] == 0) and np.all(ours["v_texture"] == 0)
+
+
+def test_errors_are_loud():
+    import gstex_b200 as G
+    from gstex_b200.synthetic import make_scene
+
+    s = make_scene("cfg2", n=32, width=32, height=32, texels=320)
+    intr = (s["fx"], s["fy"], s["cx"], s["cy"])
+    with pytest.raises(RuntimeError):  # CPU tensors: there is no CPU path
+        G.get_aabb_2d(s["means"], s["scales"], 1, s["quats"], s["viewmat"], intr)
+    sd = {k: (x.cuda() if isinstance(x, torch.Tensor) else x) for k, x in s.items()}
+    c, e = G.get_aabb_2d(sd["means"], sd["scales"], 1, sd["quats"], sd["viewmat"], intr)
+    _, dep = G.project_points(sd["means"], sd["viewmat"], intr)
+    nth = G.get_num_tiles_hit_2d(c, e, 32, 32, 16)
+    args = [s["texture_info"], sd["texture_dims"], c, e, dep, nth, sd["colors"], sd["opacities"], sd["means"],
+            sd["scales"], 1, sd["quats"], sd["uv0"], sd["umap"], sd["vmap"], sd["texture"], sd["viewmat"], sd["c2w"],
+            *intr, 32, 32]
+    with pytest.raises(AssertionError):
+        G.texture_gaussians(*args, 32, 0, sd["background"])  # block_width > 16
+    with pytest.raises(NotImplementedError):
+        G.texture_gaussians(*args, 16, 1 << 16, sd["background"])  # viewer visualisation bit
