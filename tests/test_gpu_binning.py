@@ -156,7 +156,7 @@ def test_radix_sort_stable(n, bits):
     import gstex_b200 as G
 
     g = torch.Generator().manual_seed(n)
-    hi = torch.randint(0, 1 << max(bits - 32, 1), (n,), generator=g, dtype=torch.int64) if bits > 32 else torch.zeros(n, dtype=torch.int64)
+    hi = torch.randint(0, 1 << min(max(bits - 32, 1), 31), (n,), generator=g, dtype=torch.int64) if bits > 32 else torch.zeros(n, dtype=torch.int64)
     lo = torch.randint(0, 1 << 20, (n,), generator=g, dtype=torch.int64) * 37  # many duplicate keys
     keys = ((hi << 32) | (lo & 0x7FFFFFFF)).cuda()
     vals = torch.arange(n, dtype=torch.int32).cuda()
