@@ -1,0 +1,443 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the GStex hot path on B200 (contract: see the task brief).
+
+    python bench.py --gpus 1 --steps K --warmup W            # our CUDA path
+    python bench.py --impl reference --steps K --warmup W    # the reference algorithm on the host cores
+
+Workload (BASELINE.json: "fwd+bwd ms/iter & Mpix/s, 1M textured splats @800^2"): the cfg5 synthetic scene --
+1M textured 2D Gaussians, 1e7 texels (C=3), 800x800 views, settings (1<<9)|(1<<10) as in training.  One
+"step" = one multi-view training step of the hot path: for each of `views_per_gpu` camera views
+project/bounds/tile-count -> scan -> key emit -> radix sort -> tile ranges -> textured forward -> backward
+with fixed upstream gradients, parameter gradients accumulated over the views; with N>1 GPUs every rank
+renders its own views (weak scaling) and the splat+texel gradients are summed with one NCCL all-reduce.
+`value` = Mpix/s = views x 800 x 800 / time over all ranks, inputs resident in HBM.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "fwd+bwd Mpix/s, 1M textured splats @800x800 (project+bin+sort+forward+backward)"
+UNIT = "Mpix/s"
+PARAM_KEYS = ["colors", "opacities", "means", "scales", "quats", "uv0", "umap", "vmap", "texture"]
+VOUT_KEYS = ["v_out_img", "v_out_depth", "v_out_reg", "v_out_alpha", "v_out_texture", "v_out_normal"]
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="cfg5")
+    ap.add_argument("--views-per-gpu", type=int, default=8)
+    ap.add_argument("--n", type=int, default=None, help="override splat count (debug)")
+    ap.add_argument("--size", type=int, default=None, help="override image size (debug)")
+    ap.add_argument("--no-ref-cuda", action="store_true", help="skip timing the reference CUDA extension")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def build_scene(args, views):
+    from gstex_b200.synthetic import make_scene, make_upstream_grads
+
+    kw = {}
+    if args.n:
+        kw["n"] = args.n
+    if args.size:
+        kw["width"] = kw["height"] = args.size
+    s = make_scene(args.config, views=views, **kw)
+    v = make_upstream_grads(s)
+    return s, v
+
+
+def alg_bytes(N, I, T, C, P, tiles):
+    """Algorithmic bytes per view: every datum counted once per stage that must touch it."""
+    b = {
+        "project_bounds": 64 * N,
+        "scan_emit": 24 * N + 12 * I,
+        "sort": 24 * I,
+        "tile_bins": 8 * I + 8 * tiles,
+        "forward": 4 * I + 100 * N + 4 * T * C + P * (56 + 4 * C),
+        "backward": 4 * I + 100 * N + 4 * T * C + P * (60 + 4 * C) + 88 * N + 8 * T * C,
+    }
+    b["total"] = sum(b.values())
+    return b
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
+                                          str(self.idx), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return None
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, val in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return None
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+class Workload:
+    """Parameters resident on the device (they are the model state, like weights), a list of local camera
+    views, fixed upstream gradients; `step()` runs the whole hot path forward+backward over the views."""
+
+    def __init__(self, s, v, dev, local_view_ids):
+        import torch
+
+        self.torch = torch
+        self.s, self.dev = s, dev
+        self.params = {k: s[k].to(dev).detach().clone().requires_grad_(True) for k in PARAM_KEYS}
+        self.texture_dims = s["texture_dims"].to(dev)
+        self.background = s["background"].to(dev)
+        self.viewmats = [s["viewmats"][i].contiguous().to(dev) for i in local_view_ids]
+        self.c2ws = [s["c2ws"][i].contiguous().to(dev) for i in local_view_ids]
+        self.v = {k: x.to(dev) for k, x in v.items()}
+        self.intr = (s["fx"], s["fy"], s["cx"], s["cy"])
+        self.H, self.W, self.bw = s["H"], s["W"], 16
+        self.last_I = 0
+
+    def render_view(self, viewmat, c2w, v):
+        """One view through the public API (the reference's call sequence, NS/models/gstex.py:1075-1170)."""
+        import gstex_b200 as G
+
+        p, s = self.params, self.s
+        _, depths, centers, extents, nth = G.project_bounds(p["means"], p["scales"], 1, p["quats"], viewmat, self.intr,
+                                                            self.H, self.W, self.bw)
+        outs = G.texture_gaussians(s["texture_info"], self.texture_dims, centers, extents, depths, nth, p["colors"],
+                                   p["opacities"], p["means"], p["scales"], 1, p["quats"], p["uv0"], p["umap"],
+                                   p["vmap"], p["texture"], viewmat, c2w, *self.intr, self.H, self.W, self.bw,
+                                   s["settings"], self.background)
+        self.torch.autograd.backward(list(outs), [v["v_out_img"], v["v_out_depth"], v["v_out_reg"], v["v_out_alpha"],
+                                                  v["v_out_texture"], v["v_out_normal"]])
+        return outs
+
+    def zero_grad(self):
+        for p in self.params.values():
+            p.grad = None
+
+    def step(self, world):
+        self.zero_grad()
+        for vm, c2w in zip(self.viewmats, self.c2ws):
+            self.render_view(vm, c2w, self.v)
+        if world > 1:
+            import torch.distributed as dist
+
+            for p in self.params.values():
+                dist.all_reduce(p.grad)
+
+    def step_e2e(self, world, host):
+        """Same step, but every view's inputs (camera, upstream-gradient images) come from pinned HOST memory
+        and its result (rendered image + a scalar) goes back to the host inside the timed region."""
+        torch = self.torch
+        self.zero_grad()
+        for i in range(len(self.viewmats)):
+            vm = host["viewmats"][i].to(self.dev, non_blocking=True)
+            c2w = host["c2ws"][i].to(self.dev, non_blocking=True)
+            v = {k: x.to(self.dev, non_blocking=True) for k, x in host["v"].items()}
+            outs = self.render_view(vm, c2w, v)
+            host["out_img"][i].copy_(outs[0].detach(), non_blocking=True)
+            host["scalar"][i].copy_(outs[3].detach().sum(), non_blocking=True)
+        if world > 1:
+            import torch.distributed as dist
+
+            for p in self.params.values():
+                dist.all_reduce(p.grad)
+        torch.cuda.current_stream().synchronize()  # the host consumes the result every step
+
+    def make_host(self):
+        torch = self.torch
+        nv = len(self.viewmats)
+        host = {
+            "viewmats": [m.cpu().pin_memory() for m in self.viewmats],
+            "c2ws": [m.cpu().pin_memory() for m in self.c2ws],
+            "v": {k: x.cpu().pin_memory() for k, x in self.v.items()},
+            "out_img": [torch.empty(self.H, self.W, 3).pin_memory() for _ in range(nv)],
+            "scalar": [torch.empty(()).pin_memory() for _ in range(nv)],
+        }
+        h2d = nv * (2 * 16 * 4 + sum(x.numel() * 4 for x in host["v"].values()))
+        d2h = nv * (self.H * self.W * 3 * 4 + 4)
+        return host, h2d, d2h
+
+    def stats(self):
+        """Intersections and depth complexity of view 0 (data dependent; reported with every number)."""
+        import gstex_b200 as G
+
+        p = self.params
+        with self.torch.no_grad():
+            _, _, c, e, nth = G.project_bounds(p["means"], p["scales"], 1, p["quats"], self.viewmats[0], self.intr, self.H,
+                                               self.W, self.bw)
+        return int(nth.sum().item())
+
+
+def cpu_reference_view(s, v, threads=None):
+    """One view (view 0) fwd+bwd of the same scene through the CPU restatement of the reference algorithm
+    (oracle/, OpenMP over tiles).  Returns (seconds, num_intersects, threads)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle
+    from common import run_oracle_pipeline, scene_to_numpy
+
+    if threads:
+        oracle.set_num_threads(threads)
+    d = scene_to_numpy(s)
+    vn = {k: x.numpy() for k, x in v.items()}
+    t0 = time.perf_counter()
+    r = run_oracle_pipeline(d, vn)
+    return time.perf_counter() - t0, int(r["num_intersects"]), oracle.num_threads()
+
+
+def run_reference_arm(args):
+    """--impl reference: the reference algorithm on the host cores (the reference's own CPU path is Python
+    that cannot travel to the GPU box and its CUDA path is the thing being replaced, so this is the C port
+    of it in oracle/ -- kind "port"), all host threads, one view per step as the bounded sample."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    s, v = build_scene(args, 1)
+    P = s["H"] * s["W"]
+    times, I, threads = [], 0, 0
+    for i in range(args.warmup + args.steps):
+        dt, I, threads = cpu_reference_view(s, v)
+        if i >= args.warmup:
+            times.append(dt)
+    t = sum(times) / len(times)
+    val = P / t / 1e6
+    sample = f"1 view ({s['W']}x{s['H']}) of the {s['N']}-splat scene per step, fwd+bwd incl. binning+sort, I={I}"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.config}: {s['N']} splats, {s['T']} texels, {s['W']}x{s['H']}, 1 view/step on CPU"},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def time_reference_cuda(wl, s):
+    """The reference's own CUDA kernels (oracle/_ref, built unmodified for sm_100) on the same inputs and the
+    same GPU: fwd+bwd of view 0, median of 5.  Reported beside our numbers; None if the .so is absent."""
+    import torch
+
+    from oracle import ref_ext
+
+    C = ref_ext.load()
+    if C is None:
+        return None
+    import gstex_b200 as G
+
+    sd = {k: (x.to(wl.dev) if isinstance(x, torch.Tensor) else x) for k, x in s.items()}
+    sd["viewmat"], sd["c2w"] = wl.viewmats[0], wl.c2ws[0]
+    vm3 = wl.viewmats[0][:3, :].contiguous()
+    times = []
+    for it in range(7):
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        _, depths = ref_ext.ref_project_points(sd["means"], vm3, wl.intr)
+        c, e = C.get_aabb_2d(sd["means"], sd["scales"], 1.0, sd["quats"], vm3, *wl.intr)
+        nth = ref_ext.ref_get_num_tiles_hit_2d(c, e, wl.H, wl.W, 16).to(torch.int32)
+        ref_ext.ref_forward_backward(C, sd, c, e, depths.contiguous(), nth, wl.v)
+        e1.record()
+        torch.cuda.synchronize()
+        if it >= 2:
+            times.append(e0.elapsed_time(e1))
+    return statistics.median(times)
+
+
+def measured_peak_gbs():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, STREAM-style copy)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic(kernel_key):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu capture (profiles/traffic.json)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f).get(kernel_key)
+    except Exception:
+        return None
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+        return
+    import torch
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU path in the product)"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    from gstex_b200 import _lib
+
+    lib = _lib.load()
+    total_views = args.views_per_gpu * world
+    s, v = build_scene(args, total_views)
+    wl = Workload(s, v, dev, list(range(rank, total_views, world)))
+    N, T, C, H, W = s["N"], s["T"], s["C"], s["H"], s["W"]
+    P = H * W
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+
+    for _ in range(max(args.warmup, 1)):
+        wl.step(world)
+    barrier()
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    launches0 = lib.gstex_launch_count()
+    _lib.Timing.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        wl.step(world)
+    e1.record()
+    barrier()
+    per_call = _lib.Timing.stop()
+    launches = lib.gstex_launch_count() - launches0
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    clk = clocks.stop() if rank == 0 else None
+    ms_per_step = ms_total / args.steps
+    value = total_views * P / (ms_per_step * 1e-3) / 1e6
+
+    # ---- end to end through the public API with host buffers
+    host, h2d, d2h = wl.make_host()
+    wl.step_e2e(world, host)
+    barrier()
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(args.steps):
+        wl.step_e2e(world, host)
+    e1.record()
+    barrier()
+    wall = time.perf_counter() - t0
+    e2e_ms = max_over_ranks(max(e0.elapsed_time(e1), 0.0)) / args.steps
+    e2e_value = total_views * P / (e2e_ms * 1e-3) / 1e6
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (live CUDA-event durations of the timed region)
+    I = wl.stats()
+    ab = alg_bytes(N, I, T, C, P, tiles)
+    entry_ms = {k: (sum(x) / len(x), len(x), sum(x)) for k, x in per_call.items() if x}
+    dom = max(entry_ms, key=lambda k: entry_ms[k][2])
+    key = {"gstex_texture_backward": "backward", "gstex_texture_forward": "forward", "gstex_sort_isects": "sort"}.get(dom, "total")
+    peak, peak_src = measured_peak_gbs()
+    achieved = ab[key] / (entry_ms[dom][0] * 1e-3) / 1e9
+    step_ms_kernels = sum(x[2] for x in entry_ms.values()) / args.steps
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": ncu_traffic(dom), "peak_source": peak_src, "alg_bytes_per_launch": ab[key],
+                "avg_launch_ms": entry_ms[dom][0],
+                "share_of_step": entry_ms[dom][2] / args.steps / ms_per_step,
+                "whole_path": {"alg_bytes_per_view": ab["total"],
+                               "achieved_gbs": ab["total"] * args.views_per_gpu / (ms_per_step * 1e-3) / 1e9,
+                               "frac": ab["total"] * args.views_per_gpu / (ms_per_step * 1e-3) / 1e9 / peak},
+                "per_entry_ms_per_view": {k: x[2] / args.steps / args.views_per_gpu for k, x in entry_ms.items()}}
+
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": f"{args.config}: {N} splats, {T} texels (C={C}), {W}x{H}, {args.views_per_gpu} views/GPU/step, "
+                               f"fwd+bwd, settings {s['settings']}", "views_per_gpu": args.views_per_gpu,
+                   "intersections_view0": I, "mean_tile_list": I / tiles, "ms_per_view": ms_per_step / args.views_per_gpu,
+                   "l2": "working set (texture+texel grads+records ~400 MB) exceeds the 126 MB L2; no explicit flush",
+                   "parallelism": f"views sharded over {world} GPU(s), NCCL all-reduce of 9 gradient tensors" if world > 1
+                   else "single GPU"},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": e2e_ms, "wall_ms_per_step": wall * 1e3 / args.steps,
+                "what": "per view: camera + upstream-gradient images from pinned host memory, rendered image + scalar "
+                        "back to the host; splat/texture parameters are model state resident in HBM"},
+        "gpu_launches": int(launches),
+        "kernel_ms_per_step": step_ms_kernels,
+        "roofline": roofline,
+        "clocks": clk,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        dt, Icpu, threads = cpu_reference_view(s, v)
+        out["cpu_baseline"] = {"value": P / dt / 1e6, "unit": UNIT, "cores": threads, "kind": "port",
+                               "sample": f"1 view of the same scene, fwd+bwd incl. binning+sort, {dt:.1f} s, I={Icpu}"}
+    if world == 1 and not args.no_ref_cuda:
+        try:
+            ms = time_reference_cuda(wl, s)
+            if ms is not None:
+                out["reference_cuda_same_gpu"] = {"ms_per_view": ms, "value": P / (ms * 1e-3) / 1e6, "unit": UNIT,
+                                                  "what": "reference CUDA kernels + torch cumsum/sort, unmodified, sm_100 build"}
+        except Exception as exc:  # the checker must never break the bench
+            out["reference_cuda_same_gpu"] = {"error": str(exc)[:200]}
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -21,6 +21,7 @@ P, F, I, SZ = c_void_p, c_float, c_int, c_size_t
 _SIGNATURES = {
     "gstex_abi_version": (I, []),
     "gstex_error_string": (ctypes.c_char_p, [I]),
+    "gstex_launch_count": (ctypes.c_longlong, []),
     "gstex_project_points": (I, [P, P, F, F, F, F, I, P, P, P]),
     "gstex_get_aabb_2d": (I, [P, P, F, P, P, F, F, F, F, I, P, P, P]),
     "gstex_get_num_tiles_hit_2d": (I, [P, P, I, I, I, I, P, P]),
@@ -42,6 +43,52 @@ EXPORTED_SYMBOLS = tuple(_SIGNATURES)
 
 class GstexNativeError(RuntimeError):
     pass
+
+
+class Timing:
+    """Optional per-entry-point device timing (CUDA events on the launching stream around each C-ABI call).
+    Used by bench.py for the live roofline numbers; off by default (zero overhead on the hot path)."""
+    enabled = False
+    records = {}
+
+    @classmethod
+    def start(cls):
+        cls.records = {}
+        cls.enabled = True
+
+    @classmethod
+    def stop(cls):
+        """Returns {entry point: [ms per call, ...]} (synchronises)."""
+        cls.enabled = False
+        torch.cuda.synchronize()
+        out = {k: [a.elapsed_time(b) for a, b in v] for k, v in cls.records.items()}
+        cls.records = {}
+        return out
+
+
+class _TimedLib:
+    """Thin proxy over the ctypes library: identical calls, optionally bracketed by CUDA events."""
+
+    def __init__(self, cdll):
+        object.__setattr__(self, "_cdll", cdll)
+
+    def __getattr__(self, name):
+        fn = getattr(self._cdll, name)
+        if not name.startswith("gstex_") or name.endswith("_bytes") or name in ("gstex_abi_version", "gstex_error_string",
+                                                                               "gstex_launch_count"):
+            return fn
+
+        def call(*args):
+            if not Timing.enabled:
+                return fn(*args)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            rc = fn(*args)
+            e1.record()
+            Timing.records.setdefault(name, []).append((e0, e1))
+            return rc
+
+        return call
 
 
 def lib_path() -> str:
@@ -69,8 +116,8 @@ def load() -> ctypes.CDLL:
         fn.argtypes = args
     if lib.gstex_abi_version() != 1:
         raise GstexNativeError("gstex_b200: ABI version mismatch between the Python layer and the CUDA library")
-    _LIB = lib
-    return lib
+    _LIB = _TimedLib(lib)
+    return _LIB
 
 
 def check(code: int, what: str) -> None:

@@ -7,7 +7,12 @@
 // from its SASS; the same form is restated for the CPU in oracle/gstex_oracle.c).
 #include "common.cuh"
 
+#include <atomic>
+
 namespace gstex {
+
+static std::atomic<long long> g_launches{0};
+void note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
 // ---------------------------------------------------------------------------------------------
 // projection helpers
@@ -215,6 +220,8 @@ extern "C" int gstex_get_num_tiles_hit_2d(const float* centers, const float* ext
 }
 
 extern "C" int gstex_abi_version(void) { return GSTEX_B200_ABI_VERSION; }
+
+extern "C" long long gstex_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 extern "C" const char* gstex_error_string(int code) {
     if (code == GSTEX_OK) return "ok";

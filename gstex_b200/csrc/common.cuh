@@ -5,8 +5,10 @@
 
 #include "../../include/gstex_b200.h"
 
+// after every <<<>>>: count the launch (statistics) and surface launch errors (the reference checks none)
 #define GSTEX_LAUNCH_CHECK()                         \
     do {                                             \
+        gstex::note_launch();                        \
         cudaError_t _e = cudaGetLastError();         \
         if (_e != cudaSuccess) return (int)_e;       \
     } while (0)
@@ -18,6 +20,8 @@
     } while (0)
 
 namespace gstex {
+
+void note_launch();  // binning.cu
 
 constexpr int kThreads1D = 256;  // per-splat / per-intersection kernels
 constexpr float kNear = 0.01f;   // ref: t_near in get_aabb_2d.cu:25, texture.cu:213,294

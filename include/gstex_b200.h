@@ -44,6 +44,8 @@ extern "C" {
 int gstex_abi_version(void);
 /* Human-readable text for a return code of this library (static storage). */
 const char* gstex_error_string(int code);
+/* Number of CUDA kernels this library has launched in this process so far (statistics only). */
+long long gstex_launch_count(void);
 
 /* ---- stage (a): per-splat projection, bounds, tile count ------------------------------------- */
 
