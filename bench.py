@@ -27,6 +27,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+from gstex_b200.multiview import allreduce_gradients, shard_views  # noqa: E402
+
 METRIC = "fwd+bwd Mpix/s, 1M textured splats @800x800 (project+bin+sort+forward+backward)"
 UNIT = "Mpix/s"
 PARAM_KEYS = ["colors", "opacities", "means", "scales", "quats", "uv0", "umap", "vmap", "texture"]
@@ -164,11 +166,7 @@ class Workload:
         self.zero_grad()
         for vm, c2w in zip(self.viewmats, self.c2ws):
             self.render_view(vm, c2w, self.v)
-        if world > 1:
-            import torch.distributed as dist
-
-            for p in self.params.values():
-                dist.all_reduce(p.grad)
+        allreduce_gradients([p.grad for p in self.params.values()], world)
 
     def step_e2e(self, world, host):
         """Same step, but every view's inputs (camera, upstream-gradient images) come from pinned HOST memory
@@ -182,11 +180,7 @@ class Workload:
             outs = self.render_view(vm, c2w, v)
             host["out_img"][i].copy_(outs[0].detach(), non_blocking=True)
             host["scalar"][i].copy_(outs[3].detach().sum(), non_blocking=True)
-        if world > 1:
-            import torch.distributed as dist
-
-            for p in self.params.values():
-                dist.all_reduce(p.grad)
+        allreduce_gradients([p.grad for p in self.params.values()], world)
         torch.cuda.current_stream().synchronize()  # the host consumes the result every step
 
     def make_host(self):
@@ -340,7 +334,7 @@ def main():
     lib = _lib.load()
     total_views = args.views_per_gpu * world
     s, v = build_scene(args, total_views)
-    wl = Workload(s, v, dev, list(range(rank, total_views, world)))
+    wl = Workload(s, v, dev, shard_views(total_views, rank, world))
     N, T, C, H, W = s["N"], s["T"], s["C"], s["H"], s["W"]
     P = H * W
     tiles = ((W + 15) // 16) * ((H + 15) // 16)

@@ -5,8 +5,8 @@
 // i.e. 6 passes instead of 8), 4-byte payload carried through (no gather), stable so that equal keys
 // keep emission order = ascending splat index, exactly what the reference produces.  sm_100a.
 //
-// Per pass: (1) per-block digit histograms over a contiguous chunk of tiles, (2) one-block exclusive
-// scan of the digit-major histogram matrix, (3) stable scatter with warp-level match-any ranking.
+// Per pass: (1) per-block digit histograms over a contiguous chunk of tiles, (2) per-digit row scans of
+// the digit-major histogram matrix, (3) stable scatter with warp-level match-any ranking.
 // The grid is persistent-sized (a multiple of the SM count), so the histogram matrix stays small.
 #include "common.cuh"
 
@@ -49,40 +49,41 @@ radix_hist_kernel(const int64_t* __restrict__ keys, SortGeom g, int shift, int m
     block_hist[threadIdx.x * g.num_blocks + blockIdx.x] = hist[threadIdx.x];
 }
 
-// (2) exclusive scan of `len` ints in place order (digit-major), one block of 1024 threads
-__global__ void __launch_bounds__(1024) radix_scan_kernel(const int32_t* __restrict__ in, int len, int32_t* __restrict__ out) {
-    __shared__ int warp_sums[32];
-    const int chunk = (len + 1023) / 1024;
-    const int b = threadIdx.x * chunk;
-    const int e = min(b + chunk, len);
-    int s = 0;
-    for (int i = b; i < e; ++i) s += in[i];
-    // block exclusive scan of s
+// (2) row scan: block d turns row d of the digit-major histogram matrix (num_blocks counts of digit d, in
+// block order) into exclusive offsets within the digit and publishes the digit's total.  256 blocks of
+// 256 threads, coalesced; the cross-digit offset is added by the scatter kernel itself (a 256-entry scan).
+__global__ void __launch_bounds__(kSortThreads)
+radix_scan_rows_kernel(const int32_t* __restrict__ block_hist, int num_blocks, int32_t* __restrict__ block_off,
+                       int32_t* __restrict__ digit_total) {
+    __shared__ int warp_sums[kSortWarps];
+    const int d = blockIdx.x;
+    const int32_t* row = block_hist + (size_t)d * num_blocks;
+    int32_t* orow = block_off + (size_t)d * num_blocks;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    int v = s;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const int t = __shfl_up_sync(0xffffffffu, v, o);
-        if (lane >= o) v += t;
-    }
-    if (lane == 31) warp_sums[warp] = v;
-    __syncthreads();
-    if (warp == 0) {
-        int w = warp_sums[lane];
+    int carry = 0;
+    for (int base = 0; base < num_blocks; base += kSortThreads) {
+        const int i = base + threadIdx.x;
+        const int c = (i < num_blocks) ? row[i] : 0;
+        int v = c;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            const int t = __shfl_up_sync(0xffffffffu, w, o);
-            if (lane >= o) w += t;
+            const int t = __shfl_up_sync(0xffffffffu, v, o);
+            if (lane >= o) v += t;
         }
-        warp_sums[lane] = w;
+        if (lane == 31) warp_sums[warp] = v;
+        __syncthreads();
+        int wprefix = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < kSortWarps; ++w) {
+            const int sw = warp_sums[w];
+            if (w < warp) wprefix += sw;
+            total += sw;
+        }
+        if (i < num_blocks) orow[i] = carry + wprefix + v - c;
+        carry += total;
+        __syncthreads();
     }
-    __syncthreads();
-    int run = v - s + (warp > 0 ? warp_sums[warp - 1] : 0);
-    for (int i = b; i < e; ++i) {
-        const int c = in[i];
-        out[i] = run;
-        run += c;
-    }
+    if (threadIdx.x == 0) digit_total[d] = carry;
 }
 
 // (3) stable scatter.  Within a tile, warp w owns keys [w*512, (w+1)*512) and lane l's k-th key is
@@ -90,12 +91,28 @@ __global__ void __launch_bounds__(1024) radix_scan_kernel(const int32_t* __restr
 __global__ void __launch_bounds__(kSortThreads)
 radix_scatter_kernel(const int64_t* __restrict__ keys_in, const int32_t* __restrict__ vals_in,
                      int64_t* __restrict__ keys_out, int32_t* __restrict__ vals_out, SortGeom g, int shift, int mask,
-                     const int32_t* __restrict__ block_off) {
+                     const int32_t* __restrict__ block_off, const int32_t* __restrict__ digit_total) {
     __shared__ int warp_hist[kSortWarps][kRadix];
     __shared__ int digit_base[kRadix];  // running global offset of each digit for this block
+    __shared__ int scan_tmp[kSortWarps];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned lt_mask = (1u << lane) - 1u;
-    digit_base[threadIdx.x] = block_off[threadIdx.x * g.num_blocks + blockIdx.x];
+    {  // exclusive scan of the 256 digit totals (thread d <-> digit d) + this block's offset within the digit
+        const int c = digit_total[threadIdx.x];
+        int v = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, v, o);
+            if (lane >= o) v += t;
+        }
+        if (lane == 31) scan_tmp[warp] = v;
+        __syncthreads();
+        int wprefix = 0;
+#pragma unroll
+        for (int w = 0; w < kSortWarps; ++w)
+            if (w < warp) wprefix += scan_tmp[w];
+        digit_base[threadIdx.x] = wprefix + v - c + block_off[threadIdx.x * g.num_blocks + blockIdx.x];
+    }
 
     const int first_tile = blockIdx.x * g.tiles_per_block;
     const int last_tile = min(first_tile + g.tiles_per_block, g.num_tiles);
@@ -177,7 +194,7 @@ extern "C" size_t gstex_sort_workspace_bytes(int num_intersects) {
     if (num_intersects <= 0) return 256;
     const SortGeom g = make_geom(num_intersects);
     return align256((size_t)num_intersects * 8) + align256((size_t)num_intersects * 4) +
-           2 * align256((size_t)kRadix * g.num_blocks * 4) + 256;
+           2 * align256((size_t)kRadix * g.num_blocks * 4) + align256(kRadix * 4) + 256;
 }
 
 extern "C" int gstex_sort_isects(int num_intersects, const int64_t* isect_ids, const int32_t* gaussian_ids,
@@ -198,6 +215,8 @@ extern "C" int gstex_sort_isects(int num_intersects, const int64_t* isect_ids, c
     int32_t* block_hist = reinterpret_cast<int32_t*>(ws);
     ws += align256((size_t)kRadix * g.num_blocks * 4);
     int32_t* block_off = reinterpret_cast<int32_t*>(ws);
+    ws += align256((size_t)kRadix * g.num_blocks * 4);
+    int32_t* digit_total = reinterpret_cast<int32_t*>(ws);
 
     const int passes = (key_bits + 7) / 8;
     const int64_t* src_k = isect_ids;
@@ -211,9 +230,10 @@ extern "C" int gstex_sort_isects(int num_intersects, const int64_t* isect_ids, c
         const int mask = (1 << bits) - 1;
         radix_hist_kernel<<<g.num_blocks, kSortThreads, 0, st>>>(src_k, g, shift, mask, block_hist);
         GSTEX_LAUNCH_CHECK();
-        radix_scan_kernel<<<1, 1024, 0, st>>>(block_hist, kRadix * g.num_blocks, block_off);
+        radix_scan_rows_kernel<<<kRadix, kSortThreads, 0, st>>>(block_hist, g.num_blocks, block_off, digit_total);
         GSTEX_LAUNCH_CHECK();
-        radix_scatter_kernel<<<g.num_blocks, kSortThreads, 0, st>>>(src_k, src_v, dst_k, dst_v, g, shift, mask, block_off);
+        radix_scatter_kernel<<<g.num_blocks, kSortThreads, 0, st>>>(src_k, src_v, dst_k, dst_v, g, shift, mask, block_off,
+                                                                    digit_total);
         GSTEX_LAUNCH_CHECK();
         src_k = dst_k;
         src_v = dst_v;
