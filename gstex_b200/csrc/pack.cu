@@ -1,0 +1,144 @@
+// pack.cu -- per-(view, splat) record packer shared by the forward and backward compositing kernels.
+// One thread per splat writes
+//   * SplatRec     (128 B): everything the per-(pixel,splat) loop needs that does not depend on the pixel;
+//   * SplatRecBwd  ( 32 B): quaternion, 1/scale, 1/(z_view+1e-6) for the backward-only VJPs;
+//   * a support box (16 B): a CONSERVATIVE pixel-space bounding box of the pixel centres at which the splat can
+//     reach alpha >= 1/255.  The compositing kernels use it to skip, per warp, splats that cannot touch the
+//     warp's pixel rows.  Culling never changes a result: a culled pair has alpha < 1/255 (it is `skip`ped by
+//     the reference too, texture.cu:213) and the kernels fall back to evaluating everything whenever a pixel's
+//     transmittance is so close to the 1e-4 termination threshold that even such a pair could end it.
+#include "raster_common.cuh"
+
+namespace gstex {
+
+struct PackParams {
+    int n;
+    const int32_t* texture_dims;
+    const float *colors, *opacities, *means, *scales, *quats, *uv0, *umap, *vmap, *viewmat, *c2w;
+    float glob_scale, fx, fy, cx, cy;
+    int use_blur;
+    SplatRec* recs;
+    SplatRecBwd* recs_bwd;
+    float4* boxes;
+};
+
+// Support box.  alpha = opac*exp(-sigma) >= 1/255  <=>  sigma <= smax = ln(255*opac), sigma = (u^2+v^2)/2 in
+// units of the splat's standard deviations, so the support is the disc u^2+v^2 <= r^2 = 2*smax of the splat
+// plane.  A point of the plane is mean + u*sx*ax1 + v*sy*ax2; in camera coordinates (X,Y,Z) = a*u + b*v + c.
+// The screen bounding box of the projected disc has the closed form used for 2D Gaussian splatting (bounding
+// box of a conic under a homography): with f = (r^2, r^2, -1) and rows T0,T1,T2 of [a b c],
+//   d = sum f*T2*T2,  centre_x = sum f*T0*T2 / d,  half_x^2 = centre_x^2 - sum f*T0*T0 / d   (same for y),
+// valid when the disc lies entirely in front of the camera (d < 0, c.z > 0).  Everything in double, r^2
+// inflated by 2 % + 0.02 and the box by 0.05 px so that fp32 noise of the exact per-pixel evaluation (relative
+// ~1e-4..1e-3 after the cancellation in pos - mean) can never put a contributing pixel outside it.  With the
+// blur floor (settings bit 9) alpha uses min(sigma, |xy - pix|^2): the box is unioned with the disc of radius
+// sqrt(smax) around the projected mean.  Anything doubtful (disc crossing the camera plane, splat behind the
+// camera, non-finite numbers) gets the infinite box = never culled.
+__device__ __forceinline__ float4 support_box(const double a[3], const double b[3], const double c[3], double opac,
+                                              double fx, double fy, double cx, double cy, bool use_blur, double mean_px,
+                                              double mean_py) {
+    const float inf = __int_as_float(0x7f800000);
+    const float4 everything = make_float4(-inf, -inf, inf, inf);
+    const float4 nothing = make_float4(inf, inf, -inf, -inf);
+    if (!(opac > 0.0)) return (opac == opac) ? nothing : everything;  // alpha <= 0 < 1/255 always; NaN: no culling
+    const double smax = log(255.0 * opac) * 1.02 + 0.02;
+    if (smax <= 0.0) return nothing;  // opac*exp(-sigma) < 1/255 for every sigma >= 0
+    const double r2 = 2.0 * smax;
+    const double d = r2 * (a[2] * a[2] + b[2] * b[2]) - c[2] * c[2];
+    if (!(c[2] > 0.0) || !(d < -1e-12 * c[2] * c[2])) return everything;
+    const double ccx = (r2 * (a[0] * a[2] + b[0] * b[2]) - c[0] * c[2]) / d;
+    const double ccy = (r2 * (a[1] * a[2] + b[1] * b[2]) - c[1] * c[2]) / d;
+    double hx2 = ccx * ccx - (r2 * (a[0] * a[0] + b[0] * b[0]) - c[0] * c[0]) / d;
+    double hy2 = ccy * ccy - (r2 * (a[1] * a[1] + b[1] * b[1]) - c[1] * c[1]) / d;
+    if (!(hx2 == hx2) || !(hy2 == hy2)) return everything;
+    const double hx = sqrt(fmax(hx2, 0.0)), hy = sqrt(fmax(hy2, 0.0));
+    double x0 = fx * (ccx - hx) + cx, x1 = fx * (ccx + hx) + cx;
+    double y0 = fy * (ccy - hy) + cy, y1 = fy * (ccy + hy) + cy;
+    if (x0 > x1) { const double t = x0; x0 = x1; x1 = t; }
+    if (y0 > y1) { const double t = y0; y0 = y1; y1 = t; }
+    if (use_blur) {
+        const double rb = sqrt(smax);
+        x0 = fmin(x0, mean_px - rb); x1 = fmax(x1, mean_px + rb);
+        y0 = fmin(y0, mean_py - rb); y1 = fmax(y1, mean_py + rb);
+    }
+    const double m = 0.05;
+    const float4 box = make_float4(__double2float_rd(x0 - m), __double2float_rd(y0 - m), __double2float_ru(x1 + m),
+                                   __double2float_ru(y1 + m));
+    if (!(box.x == box.x) || !(box.y == box.y) || !(box.z == box.z) || !(box.w == box.w)) return everything;
+    return box;
+}
+
+__global__ void __launch_bounds__(kThreads1D) pack_records_kernel(const PackParams p) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= p.n) return;
+    const float mx = p.means[3 * i], my = p.means[3 * i + 1], mz = p.means[3 * i + 2];
+    const float4 qt = reinterpret_cast<const float4*>(p.quats)[i];
+    const float w = qt.x, x = qt.y, y = qt.z, z = qt.w;
+    // columns of R(quat), helpers.cuh:166-185
+    const float a1x = 1.f - 2.f * (y * y + z * z), a1y = 2.f * (x * y + w * z), a1z = 2.f * (x * z - w * y);
+    const float a2x = 2.f * (x * y - w * z), a2y = 1.f - 2.f * (x * x + z * z), a2z = 2.f * (y * z + w * x);
+    const float a3x = 2.f * (x * z + w * y), a3y = 2.f * (y * z - w * x), a3z = 1.f - 2.f * (x * x + y * y);
+    const float ox = __ldg(p.c2w + 3), oy = __ldg(p.c2w + 7), oz = __ldg(p.c2w + 11);
+    const float dx = mx - ox, dy = my - oy, dz = mz - oz;
+    const float tnum = a3x * dx + a3y * dy + a3z * dz;  // compute_tt numerator, texture_helpers.cuh:303,312
+    const float sx = p.scales[3 * i], sy = p.scales[3 * i + 1];
+    const float is1 = 1.f / (sx * p.glob_scale), is2 = 1.f / (sy * p.glob_scale);
+    // projected mean (texture.cu:184-185): transform_4x3 + project_pix
+    float vm[12];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) vm[k] = __ldg(p.viewmat + k);
+    const float vx = vm[0] * mx + vm[1] * my + vm[2] * mz + vm[3];
+    const float vy = vm[4] * mx + vm[5] * my + vm[6] * mz + vm[7];
+    const float vz = vm[8] * mx + vm[9] * my + vm[10] * mz + vm[11];
+    const float rw = 1.f / (vz + 1e-6f);
+    const float xy_x = vx * rw * p.fx + p.cx, xy_y = vy * rw * p.fy + p.cy;
+    const int h = p.texture_dims[3 * i], wd = p.texture_dims[3 * i + 1], st = p.texture_dims[3 * i + 2];
+    const float opac = p.opacities[i];
+    SplatRec r;
+    r.q[0] = make_float4(mx, my, mz, tnum);
+    r.q[1] = make_float4(a3x, a3y, a3z, opac);
+    r.q[2] = make_float4(a1x, a1y, a1z, is1 * is1);
+    r.q[3] = make_float4(a2x, a2y, a2z, is2 * is2);
+    r.q[4] = make_float4(xy_x, xy_y, __int_as_float(h), __int_as_float(wd));
+    r.q[5] = make_float4(p.colors[3 * i], p.colors[3 * i + 1], p.colors[3 * i + 2], __int_as_float(st));
+    r.q[6] = make_float4(p.umap[3 * i], p.umap[3 * i + 1], p.umap[3 * i + 2], p.uv0[2 * i]);
+    r.q[7] = make_float4(p.vmap[3 * i], p.vmap[3 * i + 1], p.vmap[3 * i + 2], p.uv0[2 * i + 1]);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) p.recs[i].q[k] = r.q[k];
+    p.recs_bwd[i].quat = qt;
+    p.recs_bwd[i].aux = make_float4(1.f / sx, 1.f / sy, rw, 0.f);
+
+    // support box, in double
+    const double gsx = (double)sx * (double)p.glob_scale, gsy = (double)sy * (double)p.glob_scale;
+    const double A1[3] = {(double)a1x * gsx, (double)a1y * gsx, (double)a1z * gsx};
+    const double A2[3] = {(double)a2x * gsy, (double)a2y * gsy, (double)a2z * gsy};
+    double a[3], b[3], c[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        a[k] = (double)vm[4 * k] * A1[0] + (double)vm[4 * k + 1] * A1[1] + (double)vm[4 * k + 2] * A1[2];
+        b[k] = (double)vm[4 * k] * A2[0] + (double)vm[4 * k + 1] * A2[1] + (double)vm[4 * k + 2] * A2[2];
+        c[k] = (double)vm[4 * k] * mx + (double)vm[4 * k + 1] * my + (double)vm[4 * k + 2] * mz + (double)vm[4 * k + 3];
+    }
+    p.boxes[i] = support_box(a, b, c, (double)opac, p.fx, p.fy, p.cx, p.cy, p.use_blur != 0, xy_x, xy_y);
+}
+
+int launch_pack_records(int n, const int32_t* texture_dims, const float* colors, const float* opacities,
+                        const float* means, const float* scales, float glob_scale, const float* quats,
+                        const float* uv0, const float* umap, const float* vmap, const float* viewmat,
+                        const float* c2w, float fx, float fy, float cx, float cy, int settings, void* workspace,
+                        cudaStream_t st) {
+    if (n <= 0) return GSTEX_OK;
+    PackParams p;
+    p.n = n; p.texture_dims = texture_dims; p.colors = colors; p.opacities = opacities; p.means = means;
+    p.scales = scales; p.quats = quats; p.uv0 = uv0; p.umap = umap; p.vmap = vmap; p.viewmat = viewmat; p.c2w = c2w;
+    p.glob_scale = glob_scale; p.fx = fx; p.fy = fy; p.cx = cx; p.cy = cy;
+    p.use_blur = (settings & GSTEX_SET_BLUR) ? 1 : 0;
+    p.recs = ws_recs(workspace); p.recs_bwd = ws_recs_bwd(workspace, n); p.boxes = ws_boxes(workspace, n);
+    pack_records_kernel<<<div_up(n, kThreads1D), kThreads1D, 0, st>>>(p);
+    GSTEX_LAUNCH_CHECK();
+    return GSTEX_OK;
+}
+
+}  // namespace gstex
+
+extern "C" size_t gstex_texture_workspace_bytes(int n) { return gstex::ws_bytes(n); }

@@ -2,14 +2,16 @@
 // Replaces texture_backward (gstex_cuda/cuda/csrc/texture.cu:331-760, wrapper :903-1053).  sm_100a.
 //
 // Differences in HOW from the reference kernel:
-//   * per-splat invariants come from the packed records (see raster_fwd.cu), staged back to front;
-//   * batches behind every pixel's last contributor are never loaded (block max of final_index);
-//   * the per-splat gradients of a warp are reduced with a transposing butterfly (16 shuffles for the
-//     13 values of the training configuration instead of 22 five-step reductions = 110 shuffles), after
-//     which lane 2s holds the total of value s, so ONE red instruction issues all of the warp's
-//     atomics for that splat instead of 22 serial ones from lane 0;
-//   * texel gradients skip zero contributions (the reference issues all 4*C atomics unconditionally).
-#include "raster_common.cuh"
+//   * same warp-specialised TMA/mbarrier ring and per-warp support-box culling as the forward
+//     (raster_fwd.cu, pipeline.cuh), walking the tile's list back to front from the block's last contributor;
+//     records behind every pixel's last contributor are never loaded, and a warp only evaluates splats
+//     that are not beyond its own last contributor and can reach its pixel rows;
+//   * the per-splat gradients of a warp are reduced with a transposing butterfly (16 shuffles for the 13
+//     values of the training configuration instead of 22 five-step reductions = 110 shuffles), after which
+//     lane 2s holds the total of value s, so ONE red instruction issues all of the warp's atomics for that
+//     splat instead of 22 serial ones from lane 0;
+//   * the bilinear index/weight computation is done once per pair, not once per channel.
+#include "pipeline.cuh"
 
 namespace gstex {
 
@@ -37,6 +39,7 @@ struct BwdParams {
     int C;
     const SplatRec* recs;
     const SplatRecBwd* recs_bwd;
+    const float4* boxes;
     const int32_t* ids;
     const int2* tile_bins;
     const float* texture;
@@ -47,6 +50,18 @@ struct BwdParams {
     const int32_t *final_idx, *depth_idx;
     const float *v_output, *v_output_depth, *v_output_reg, *v_output_alpha, *v_output_texture, *v_output_normal;
     float *v_colors, *v_opacity, *v_means, *v_scales, *v_quats, *v_uv0, *v_umap, *v_vmap, *v_texture;
+};
+
+struct BwdShared {
+    SplatRec recs[kStages][kStageRecs];     // 32 KB
+    SplatRecBwd bwd[kStages][kStageRecs];   // 8 KB
+    int ids[kStages][kStageRecs];           // 1 KB
+    uint64_t full[kStages];
+    uint64_t empty[kStages];
+    unsigned bits[kStages][8];
+    Camera cam;
+    int warp_final[8];
+    int block_final;
 };
 
 // slot layout of the per-splat gradient vector
@@ -67,32 +82,88 @@ __device__ __forceinline__ void slot_target(const BwdParams& p, int slot, float*
 }
 
 template <int CMAX, bool UV>
-__global__ void __launch_bounds__(kMaxTileThreads) texture_backward_kernel(const BwdParams p) {
+__global__ void __launch_bounds__(kMaxTileThreads + 32) texture_backward_kernel(const BwdParams p) {
     constexpr int K = UV ? 32 : 16;
-    __shared__ SplatRec s_recs[kBatch];
-    __shared__ SplatRecBwd s_bwd[kBatch];
-    __shared__ int s_ids[kBatch];
-    __shared__ Camera s_cam;
-    __shared__ int s_block_final;
+    __shared__ __align__(128) BwdShared sm;
     const RasterGeom g = p.g;
-    const int nthreads = blockDim.x;
-    const int lane = threadIdx.x & 31;
-    load_camera(s_cam, p.viewmat, p.c2w, p.fx, p.fy, p.cx, p.cy);
-    if (threadIdx.x == 0) s_block_final = -1;
+    const int n_pix_warps = g.threads >> 5;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool is_producer = warp == n_pix_warps;
+    load_camera(sm.cam, p.viewmat, p.c2w, p.fx, p.fy, p.cx, p.cy);
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(&sm.full[s], 1);
+            mbar_init(&sm.empty[s], n_pix_warps);
+        }
+        sm.block_final = -1;
+        mbar_fence_init();
+    }
     __syncthreads();
     const int tile_id = blockIdx.y * g.tiles_x + blockIdx.x;
-    const Pixel pix = make_pixel(s_cam, g, blockIdx.x, blockIdx.y);
+    const int2 range = p.tile_bins[tile_id];
+
+    // per-pixel state (pixel warps only; the producer computes a dummy pixel it never uses)
+    Pixel pix;
+    int bin_final = -1;
+    if (!is_producer) {
+        pix = make_pixel(sm.cam, g, blockIdx.x, blockIdx.y);
+        bin_final = pix.inside ? p.final_idx[pix.pix_id] : -1;
+        int wf = bin_final;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) wf = max(wf, __shfl_xor_sync(0xffffffffu, wf, o));
+        if (lane == 0) {
+            sm.warp_final[warp] = wf;
+            atomicMax(&sm.block_final, wf);
+        }
+    }
+    __syncthreads();
+    // walk idx = block_final, block_final-1, ..., range.x; stage n covers [batch_end-31, batch_end]
+    const int block_final = min(sm.block_final, range.y - 1);
+    const int n_stages = (block_final >= range.x) ? (block_final - range.x) / kStageRecs + 1 : 0;
+
+    if (is_producer) {
+        const float tx0 = (float)(blockIdx.x * g.bw) + 0.5f, tx1 = (float)(blockIdx.x * g.bw + g.bw - 1) + 0.5f;
+        const float ty = (float)(blockIdx.y * g.bw) + 0.5f;
+        int g_next = (block_final - lane >= range.x && n_stages > 0) ? __ldg(p.ids + block_final - lane) : -1;
+        for (int n = 0; n < n_stages; ++n) {
+            const int s = n % kStages;
+            const int idx = block_final - n * kStageRecs - lane;
+            const int gid = g_next;
+            const int nxt = idx - kStageRecs;
+            g_next = (nxt >= range.x) ? __ldg(p.ids + nxt) : -1;
+            const float4 box = (gid >= 0) ? __ldg(p.boxes + gid) : make_float4(1.f, 1.f, 0.f, 0.f);
+            if (n >= kStages) mbar_wait(&sm.empty[s], ((n / kStages) - 1) & 1);
+            unsigned mine = 0, any = 0;
+            for (int w = 0; w < n_pix_warps; ++w) {
+                int r0, r1;
+                warp_rows(w, g.bw, r0, r1);
+                const bool hit = gid >= 0 && idx <= sm.warp_final[w] &&
+                                 box_overlaps(box, tx0, tx1, ty + (float)r0, ty + (float)r1);
+                const unsigned b = __ballot_sync(0xffffffffu, hit);
+                if (lane == w) mine = b;
+                any |= b;
+            }
+            if (lane < n_pix_warps) sm.bits[s][lane] = mine;
+            if (gid >= 0) sm.ids[s][lane] = gid;
+            __syncwarp();
+            if (lane == 0)
+                mbar_arrive_expect_tx(&sm.full[s], (uint32_t)__popc(any) * (uint32_t)(sizeof(SplatRec) + sizeof(SplatRecBwd)));
+            if ((any >> lane) & 1u) {
+                bulk_copy_g2s(&sm.recs[s][lane], p.recs + gid, sizeof(SplatRec), &sm.full[s]);
+                bulk_copy_g2s(&sm.bwd[s][lane], p.recs_bwd + gid, sizeof(SplatRecBwd), &sm.full[s]);
+            }
+        }
+        return;
+    }
+    // =============================== pixel warps: back to front ===============================
     const bool use_blur = p.settings & GSTEX_SET_BLUR;
     const bool use_ndc = p.settings & GSTEX_SET_NDC_REG;
     const bool bilinear = !(p.settings & GSTEX_SET_NEAREST);
     const int C = p.C;
-    const int2 range = p.tile_bins[tile_id];
-
     const int id = pix.pix_id;
     float T = p.final_Ts[id];
     const float3 ts_final = make_float3(p.final_s[3 * id], p.final_s[3 * id + 1], p.final_s[3 * id + 2]);
     const int depth_final = p.depth_idx[id];
-    const int bin_final = pix.inside ? p.final_idx[id] : -1;
     const float3 v_out = make_float3(p.v_output[3 * id], p.v_output[3 * id + 1], p.v_output[3 * id + 2]);
     const float v_out_depth = p.v_output_depth[id], v_out_reg = p.v_output_reg[id];
     const float3 v_out_normal =
@@ -109,26 +180,16 @@ __global__ void __launch_bounds__(kMaxTileThreads) texture_backward_kernel(const
     slot_target<UV>(p, (K == 16) ? (lane >> 1) : lane, slot_base, slot_stride);
     if (K == 16 && (lane & 1)) slot_base = nullptr;
 
-    int warp_final = bin_final;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) warp_final = max(warp_final, __shfl_xor_sync(0xffffffffu, warp_final, o));
-    if (lane == 0) atomicMax(&s_block_final, warp_final);
-    __syncthreads();
-    const int block_final = min(s_block_final, range.y - 1);
-    // walk idx = block_final, block_final-1, ..., range.x in batches of kBatch
-    for (int batch_end = block_final; batch_end >= range.x; batch_end -= kBatch) {
-        __syncthreads();  // previous batch fully consumed
-        const int count = min(kBatch, batch_end + 1 - range.x);
-        stage_records(s_recs, p.recs, p.ids, batch_end, count, true, nthreads);
-        for (int j = threadIdx.x; j < count; j += nthreads) {
-            const int gid = __ldg(p.ids + batch_end - j);
-            s_ids[j] = gid;
-            s_bwd[j] = p.recs_bwd[gid];
-        }
-        __syncthreads();
-        for (int j = max(0, batch_end - warp_final); j < count; ++j) {
+    for (int n = 0; n < n_stages; ++n) {
+        const int s = n % kStages;
+        mbar_wait(&sm.full[s], (n / kStages) & 1);
+        const int batch_end = block_final - n * kStageRecs;
+        unsigned todo = sm.bits[s][warp];
+        while (todo) {
+            const int j = __ffs(todo) - 1;
+            todo &= todo - 1;
             const int idx = batch_end - j;
-            const SplatRec& r = s_recs[j];
+            const SplatRec& r = sm.recs[s][j];
             const float4 r0 = r.q[0], r1 = r.q[1], r2 = r.q[2], r3 = r.q[3], r4 = r.q[4];
             const PairEval e = eval_pair(pix, r0, r1, r2, r3, r4, use_blur);
             const bool valid = (idx <= bin_final) && !e.skip;
@@ -138,7 +199,7 @@ __global__ void __launch_bounds__(kMaxTileThreads) texture_backward_kernel(const
             for (int k = 0; k < K; ++k) v[k] = 0.f;
             if (valid) {
                 const float4 r5 = r.q[5], r6 = r.q[6], r7 = r.q[7];
-                const SplatRecBwd rb = s_bwd[j];
+                const SplatRecBwd rb = sm.bwd[s][j];
                 const float alpha = e.alpha;
                 const float ra = 1.f / (1.f - alpha);
                 T *= ra;
@@ -163,11 +224,10 @@ __global__ void __launch_bounds__(kMaxTileThreads) texture_backward_kernel(const
                             const float val = q.w00 * t00 + q.w01 * t01 + q.w10 * t10 + q.w11 * t11;
                             const float v_val = vis * v_tex[k];
                             // query_jagged_chart_vjp, texture_helpers.cuh:252-260
-                            const float g00 = q.w00 * v_val, g01 = q.w01 * v_val, g10 = q.w10 * v_val, g11 = q.w11 * v_val;
-                            if (g00 != 0.f) atomicAdd(p.v_texture + o00 + k, g00);
-                            if (g01 != 0.f) atomicAdd(p.v_texture + o01 + k, g01);
-                            if (g10 != 0.f) atomicAdd(p.v_texture + o10 + k, g10);
-                            if (g11 != 0.f) atomicAdd(p.v_texture + o11 + k, g11);
+                            atomicAdd(p.v_texture + o00 + k, q.w00 * v_val);
+                            atomicAdd(p.v_texture + o01 + k, q.w01 * v_val);
+                            atomicAdd(p.v_texture + o10 + k, q.w10 * v_val);
+                            atomicAdd(p.v_texture + o11 + k, q.w11 * v_val);
                             if (UV && bilinear) {  // texture_helpers.cuh:262-299
                                 v_u += (float)th * (v_val * (-(1.f - q.fy) * t00 - q.fy * t01 + (1.f - q.fy) * t10 + q.fy * t11));
                                 v_v += (float)tw * (v_val * (-(1.f - q.fx) * t00 + (1.f - q.fx) * t01 - q.fx * t10 + q.fx * t11));
@@ -211,14 +271,14 @@ __global__ void __launch_bounds__(kMaxTileThreads) texture_backward_kernel(const
                 v_t += pix.view_depth * v_t_view;
                 float3 v_mean_extra = make_float3(0.f, 0.f, 0.f);
                 if (e.blur) {  // project_pix_vjp + transform_4x3_rot_only_transposed, texture.cu:685-692
-                    const float vxp = s_cam.fx * (2.0f * v_sigma_blur * (r4.x - pix.px));
-                    const float vyp = s_cam.fy * (2.0f * v_sigma_blur * (r4.y - pix.py));
+                    const float vxp = sm.cam.fx * (2.0f * v_sigma_blur * (r4.x - pix.px));
+                    const float vyp = sm.cam.fy * (2.0f * v_sigma_blur * (r4.y - pix.py));
                     const float rw = rb.aux.z;
-                    const float nx = (r4.x - s_cam.cx) / s_cam.fx, ny = (r4.y - s_cam.cy) / s_cam.fy;  // p_view.xy * rw
+                    const float nx = (r4.x - sm.cam.cx) / sm.cam.fx, ny = (r4.y - sm.cam.cy) / sm.cam.fy;  // p_view.xy * rw
                     const float wx = vxp * rw, wy = vyp * rw, wz = -(vxp * nx + vyp * ny) * rw;
-                    v_mean_extra = make_float3(s_cam.vm[0] * wx + s_cam.vm[4] * wy + s_cam.vm[8] * wz,
-                                               s_cam.vm[1] * wx + s_cam.vm[5] * wy + s_cam.vm[9] * wz,
-                                               s_cam.vm[2] * wx + s_cam.vm[6] * wy + s_cam.vm[10] * wz);
+                    v_mean_extra = make_float3(sm.cam.vm[0] * wx + sm.cam.vm[4] * wy + sm.cam.vm[8] * wz,
+                                               sm.cam.vm[1] * wx + sm.cam.vm[5] * wy + sm.cam.vm[9] * wz,
+                                               sm.cam.vm[2] * wx + sm.cam.vm[6] * wy + sm.cam.vm[10] * wz);
                 }
                 // compute_tt_vjp, texture_helpers.cuh:315-334
                 const float den = clamp_tt_denom(r1.x * pix.ray.x + r1.y * pix.ray.y + r1.z * pix.ray.z);
@@ -243,8 +303,10 @@ __global__ void __launch_bounds__(kMaxTileThreads) texture_backward_kernel(const
                 v[3] = e.ex * v_alpha;
             }
             butterfly_reduce<K>(v, lane);
-            if (slot_base != nullptr && v[0] != 0.f) atomicAdd(slot_base + (size_t)s_ids[j] * slot_stride, v[0]);
+            if (slot_base != nullptr && v[0] != 0.f) atomicAdd(slot_base + (size_t)sm.ids[s][j] * slot_stride, v[0]);
         }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.empty[s]);
     }
 }
 
@@ -255,8 +317,9 @@ using namespace gstex;
 template <int CMAX>
 static void launch_bwd(const BwdParams& p, bool uv, cudaStream_t st) {
     const dim3 grid(p.g.tiles_x, p.g.tiles_y);
-    if (uv) texture_backward_kernel<CMAX, true><<<grid, p.g.threads, 0, st>>>(p);
-    else texture_backward_kernel<CMAX, false><<<grid, p.g.threads, 0, st>>>(p);
+    const int threads = p.g.threads + 32;  // + the producer warp
+    if (uv) texture_backward_kernel<CMAX, true><<<grid, threads, 0, st>>>(p);
+    else texture_backward_kernel<CMAX, false><<<grid, threads, 0, st>>>(p);
 }
 
 extern "C" int gstex_texture_backward(
@@ -282,17 +345,16 @@ extern "C" int gstex_texture_backward(
         !v_output_texture || !v_output_normal || !v_colors || !v_opacity || !v_means || !v_scales || !v_quats ||
         !v_uv0 || !v_umap || !v_vmap || !v_texture || !workspace)
         return GSTEX_E_BADARG;
-    if (workspace_bytes < gstex_texture_workspace_bytes(n)) return GSTEX_E_WORKSPACE;
-    SplatRec* recs = ws_recs(workspace);
-    SplatRecBwd* recs_bwd = ws_recs_bwd(workspace, n);
+    if (workspace_bytes < ws_bytes(n)) return GSTEX_E_WORKSPACE;
     if (!records_valid) {
         const int rc = launch_pack_records(n, texture_dims, colors, opacities, means, scales, glob_scale, quats, uv0, umap,
-                                           vmap, viewmat, c2w, fx, fy, cx, cy, recs, recs_bwd, st);
+                                           vmap, viewmat, c2w, fx, fy, cx, cy, settings, workspace, st);
         if (rc != GSTEX_OK) return rc;
     }
     BwdParams p;
     p.g = make_raster_geom(img_height, img_width, block_width);
-    p.C = channels; p.recs = recs; p.recs_bwd = recs_bwd; p.ids = gaussian_ids_sorted;
+    p.C = channels; p.recs = ws_recs(workspace); p.recs_bwd = ws_recs_bwd(workspace, n); p.boxes = ws_boxes(workspace, n);
+    p.ids = gaussian_ids_sorted;
     p.tile_bins = reinterpret_cast<const int2*>(tile_bins); p.texture = texture; p.viewmat = viewmat; p.c2w = c2w;
     p.background = background; p.fx = fx; p.fy = fy; p.cx = cx; p.cy = cy; p.settings = settings;
     p.final_Ts = final_Ts; p.final_s = final_s; p.final_idx = final_idx; p.depth_idx = depth_idx;

@@ -1,88 +1,27 @@
-// raster_fwd.cu -- stage (c): per-tile textured forward compositing, plus the per-view record packer.
+// raster_fwd.cu -- stage (c): per-tile textured forward compositing.
 // Replaces texture_forward (gstex_cuda/cuda/csrc/texture.cu:11-329, wrapper :762-901).  sm_100a.
 //
 // Differences in HOW (not WHAT) from the reference kernel:
-//   * per-splat invariants (rotation axes, inverse-scale squares, ray/plane numerator, projected mean)
-//     come from a 128-byte packed record computed once per (view, splat) instead of once per pixel;
-//   * records are staged cooperatively (8 lanes x 16 B per record = whole lines) instead of ten scattered
-//     4-16 B gathers per splat;
+//   * per-splat invariants (rotation axes, inverse-scale squares, ray/plane numerator, projected mean) come
+//     from a 128-byte packed record computed once per (view, splat) (pack.cu) instead of once per pixel;
+//   * warp-specialised: one producer warp gathers the tile's records by sorted id with TMA bulk copies
+//     (cp.async.bulk -> UBLKCP, 128 B each) into an 8-stage shared-memory ring guarded by full/empty
+//     mbarriers; the eight pixel warps consume stages independently -- no block-wide barrier per batch;
+//   * per stage the producer also tests each record's conservative support box against the pixel rows of
+//     every warp and hands each warp a 32-bit "worth evaluating" mask, so a warp never touches splats that
+//     cannot reach alpha >= 1/255 on its rows (exact: see pack.cu and the `danger` fallback below);
 //   * the bilinear index/weight computation is done once per pair, not once per channel; texture
 //     accumulators live in registers (channel count is a template bound), not in a float[64] local array;
-//   * a warp stops as soon as all its 32 pixels are done (ballot), the block when all warps are.
-#include "raster_common.cuh"
+//   * a warp stops as soon as all its 32 pixels are done (ballot), the producer when all warps are.
+#include "pipeline.cuh"
 
 namespace gstex {
 
-// ------------------------------------------------------------------------------------------------
-// record packer: one thread per splat
-// ------------------------------------------------------------------------------------------------
-struct PackParams {
-    int n;
-    const int32_t* texture_dims;
-    const float *colors, *opacities, *means, *scales, *quats, *uv0, *umap, *vmap, *viewmat, *c2w;
-    float glob_scale, fx, fy, cx, cy;
-    SplatRec* recs;
-    SplatRecBwd* recs_bwd;
-};
-
-__global__ void __launch_bounds__(kThreads1D) pack_records_kernel(const PackParams p) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= p.n) return;
-    const float mx = p.means[3 * i], my = p.means[3 * i + 1], mz = p.means[3 * i + 2];
-    const float4 qt = reinterpret_cast<const float4*>(p.quats)[i];
-    const float w = qt.x, x = qt.y, y = qt.z, z = qt.w;
-    // columns of R(quat), helpers.cuh:166-185
-    const float a1x = 1.f - 2.f * (y * y + z * z), a1y = 2.f * (x * y + w * z), a1z = 2.f * (x * z - w * y);
-    const float a2x = 2.f * (x * y - w * z), a2y = 1.f - 2.f * (x * x + z * z), a2z = 2.f * (y * z + w * x);
-    const float a3x = 2.f * (x * z + w * y), a3y = 2.f * (y * z - w * x), a3z = 1.f - 2.f * (x * x + y * y);
-    const float ox = __ldg(p.c2w + 3), oy = __ldg(p.c2w + 7), oz = __ldg(p.c2w + 11);
-    const float dx = mx - ox, dy = my - oy, dz = mz - oz;
-    const float tnum = a3x * dx + a3y * dy + a3z * dz;  // compute_tt numerator, texture_helpers.cuh:303,312
-    const float is1 = 1.f / (p.scales[3 * i] * p.glob_scale), is2 = 1.f / (p.scales[3 * i + 1] * p.glob_scale);
-    // projected mean (texture.cu:184-185): transform_4x3 + project_pix
-    const float* vm = p.viewmat;
-    const float vx = __ldg(vm + 0) * mx + __ldg(vm + 1) * my + __ldg(vm + 2) * mz + __ldg(vm + 3);
-    const float vy = __ldg(vm + 4) * mx + __ldg(vm + 5) * my + __ldg(vm + 6) * mz + __ldg(vm + 7);
-    const float vz = __ldg(vm + 8) * mx + __ldg(vm + 9) * my + __ldg(vm + 10) * mz + __ldg(vm + 11);
-    const float rw = 1.f / (vz + 1e-6f);
-    const float xy_x = vx * rw * p.fx + p.cx, xy_y = vy * rw * p.fy + p.cy;
-    const int h = p.texture_dims[3 * i], wd = p.texture_dims[3 * i + 1], st = p.texture_dims[3 * i + 2];
-    SplatRec r;
-    r.q[0] = make_float4(mx, my, mz, tnum);
-    r.q[1] = make_float4(a3x, a3y, a3z, p.opacities[i]);
-    r.q[2] = make_float4(a1x, a1y, a1z, is1 * is1);
-    r.q[3] = make_float4(a2x, a2y, a2z, is2 * is2);
-    r.q[4] = make_float4(xy_x, xy_y, __int_as_float(h), __int_as_float(wd));
-    r.q[5] = make_float4(p.colors[3 * i], p.colors[3 * i + 1], p.colors[3 * i + 2], __int_as_float(st));
-    r.q[6] = make_float4(p.umap[3 * i], p.umap[3 * i + 1], p.umap[3 * i + 2], p.uv0[2 * i]);
-    r.q[7] = make_float4(p.vmap[3 * i], p.vmap[3 * i + 1], p.vmap[3 * i + 2], p.uv0[2 * i + 1]);
-#pragma unroll
-    for (int k = 0; k < 8; ++k) p.recs[i].q[k] = r.q[k];
-    p.recs_bwd[i].quat = qt;
-    p.recs_bwd[i].aux = make_float4(1.f / p.scales[3 * i], 1.f / p.scales[3 * i + 1], rw, 0.f);
-}
-
-int launch_pack_records(int n, const int32_t* texture_dims, const float* colors, const float* opacities,
-                        const float* means, const float* scales, float glob_scale, const float* quats,
-                        const float* uv0, const float* umap, const float* vmap, const float* viewmat,
-                        const float* c2w, float fx, float fy, float cx, float cy, SplatRec* recs, SplatRecBwd* recs_bwd,
-                        cudaStream_t st) {
-    PackParams p;
-    p.n = n; p.texture_dims = texture_dims; p.colors = colors; p.opacities = opacities; p.means = means;
-    p.scales = scales; p.quats = quats; p.uv0 = uv0; p.umap = umap; p.vmap = vmap; p.viewmat = viewmat; p.c2w = c2w;
-    p.glob_scale = glob_scale; p.fx = fx; p.fy = fy; p.cx = cx; p.cy = cy; p.recs = recs; p.recs_bwd = recs_bwd;
-    pack_records_kernel<<<div_up(n, kThreads1D), kThreads1D, 0, st>>>(p);
-    GSTEX_LAUNCH_CHECK();
-    return GSTEX_OK;
-}
-
-// ------------------------------------------------------------------------------------------------
-// forward compositing
-// ------------------------------------------------------------------------------------------------
 struct FwdParams {
     RasterGeom g;
     int C;
     const SplatRec* recs;
+    const float4* boxes;
     const int32_t* ids;
     const int2* tile_bins;
     const float* texture;
@@ -93,23 +32,77 @@ struct FwdParams {
     int32_t *final_idx, *depth_idx;
 };
 
+struct FwdShared {
+    SplatRec recs[kStages][kStageRecs];  // 32 KB
+    uint64_t full[kStages];
+    uint64_t empty[kStages];
+    unsigned bits[kStages][8];  // per stage, per pixel warp: records worth evaluating
+    Camera cam;
+    int warps_done;
+    volatile int stop_at;
+};
+
 template <int CMAX>
-__global__ void __launch_bounds__(kMaxTileThreads) texture_forward_kernel(const FwdParams p) {
-    __shared__ SplatRec s_recs[kBatch];
-    __shared__ Camera s_cam;
+__global__ void __launch_bounds__(kMaxTileThreads + 32) texture_forward_kernel(const FwdParams p) {
+    __shared__ __align__(128) FwdShared sm;
     const RasterGeom g = p.g;
-    const int nthreads = blockDim.x;
-    load_camera(s_cam, p.viewmat, p.c2w, p.fx, p.fy, p.cx, p.cy);
+    const int n_pix_warps = g.threads >> 5;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool is_producer = warp == n_pix_warps;
+    load_camera(sm.cam, p.viewmat, p.c2w, p.fx, p.fy, p.cx, p.cy);
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages; ++s) {
+            mbar_init(&sm.full[s], 1);
+            mbar_init(&sm.empty[s], n_pix_warps);
+        }
+        sm.warps_done = 0;
+        sm.stop_at = 0x7fffffff;
+        mbar_fence_init();
+    }
     __syncthreads();
     const int tile_id = blockIdx.y * g.tiles_x + blockIdx.x;
-    const Pixel pix = make_pixel(s_cam, g, blockIdx.x, blockIdx.y);
+    const int2 range = p.tile_bins[tile_id];
+    const int n_stages = (range.y - range.x + kStageRecs - 1) / kStageRecs;
+
+    if (is_producer) {
+        // ===================== producer warp: gather records, build per-warp masks =====================
+        const float tx0 = (float)(blockIdx.x * g.bw) + 0.5f, tx1 = (float)(blockIdx.x * g.bw + g.bw - 1) + 0.5f;
+        const float ty = (float)(blockIdx.y * g.bw) + 0.5f;
+        int g_next = (range.x + lane < range.y) ? __ldg(p.ids + range.x + lane) : -1;
+        for (int n = 0; n < n_stages; ++n) {
+            const int s = n % kStages;
+            const int gid = g_next;
+            const int nxt = range.x + (n + 1) * kStageRecs + lane;
+            g_next = (nxt < range.y) ? __ldg(p.ids + nxt) : -1;  // prefetch the next stage's ids
+            const float4 box = (gid >= 0) ? __ldg(p.boxes + gid) : make_float4(1.f, 1.f, 0.f, 0.f);
+            if (n >= kStages) mbar_wait(&sm.empty[s], ((n / kStages) - 1) & 1);
+            if (*(volatile int*)&sm.warps_done >= n_pix_warps) {  // every pixel of the tile is finished
+                if (lane == 0) sm.stop_at = n;
+                break;
+            }
+            unsigned mine = 0, any = 0;
+            for (int w = 0; w < n_pix_warps; ++w) {
+                int r0, r1;
+                warp_rows(w, g.bw, r0, r1);
+                const bool hit = gid >= 0 && box_overlaps(box, tx0, tx1, ty + (float)r0, ty + (float)r1);
+                const unsigned b = __ballot_sync(0xffffffffu, hit);
+                if (lane == w) mine = b;
+                any |= b;
+            }
+            if (lane < n_pix_warps) sm.bits[s][lane] = mine;
+            __syncwarp();
+            if (lane == 0) mbar_arrive_expect_tx(&sm.full[s], (uint32_t)__popc(any) * (uint32_t)sizeof(SplatRec));
+            if ((any >> lane) & 1u) bulk_copy_g2s(&sm.recs[s][lane], p.recs + gid, sizeof(SplatRec), &sm.full[s]);
+        }
+        return;
+    }
+
+    // =============================== pixel warps: composite front to back ===============================
+    const Pixel pix = make_pixel(sm.cam, g, blockIdx.x, blockIdx.y);
     const bool use_blur = p.settings & GSTEX_SET_BLUR;
     const bool use_ndc = p.settings & GSTEX_SET_NDC_REG;
     const bool bilinear = !(p.settings & GSTEX_SET_NEAREST);
     const int C = p.C;
-
-    const int2 range = p.tile_bins[tile_id];
-    const int num_batches = (range.y - range.x + kBatch - 1) / kBatch;
 
     bool done = !pix.inside;
     float T = 1.f;
@@ -120,57 +113,81 @@ __global__ void __launch_bounds__(kMaxTileThreads) texture_forward_kernel(const 
 #pragma unroll
     for (int k = 0; k < CMAX; ++k) tex[k] = 0.f;
 
-    for (int b = 0; b < num_batches; ++b) {
-        // block-wide early exit (texture.cu:132); also protects s_recs against the previous batch's readers
-        if (__syncthreads_count(done) >= nthreads) break;
-        const int batch_start = range.x + kBatch * b;
-        const int count = min(kBatch, range.y - batch_start);
-        stage_records(s_recs, p.recs, p.ids, batch_start, count, false, nthreads);
-        __syncthreads();
-        for (int i = 0; i < count; ++i) {
-            if (__all_sync(0xffffffffu, done)) break;  // this warp's 32 pixels are finished
-            const SplatRec& r = s_recs[i];
-            const float4 r0 = r.q[0], r1 = r.q[1], r2 = r.q[2], r3 = r.q[3], r4 = r.q[4];
-            const PairEval e = eval_pair(pix, r0, r1, r2, r3, r4, use_blur);
-            const float next_T = T * (1.f - e.alpha);
-            if (!done) {
-                if (next_T <= 1e-4f) {
-                    done = true;  // tested before `skip`, texture.cu:216-221; this splat is not composited
-                } else if (!e.skip) {
-                    const float vis = e.alpha * T;
-                    const float4 r5 = r.q[5], r6 = r.q[6], r7 = r.q[7];
-                    rgb.x += r5.x * vis; rgb.y += r5.y * vis; rgb.z += r5.z * vis;
-                    nrm.x += vis * r1.x; nrm.y += vis * r1.y; nrm.z += vis * r1.z;
-                    const float t_view = e.t * pix.view_depth;
-                    const float u = clamp01(r6.w + (r6.x * e.delta.x + r6.y * e.delta.y + r6.z * e.delta.z));
-                    const float v = clamp01(r7.w + (r7.x * e.delta.x + r7.y * e.delta.y + r7.z * e.delta.z));
-                    const TexQuery q = tex_query(__float_as_int(r4.z), __float_as_int(r4.w), __float_as_int(r5.w), u, v, bilinear);
-                    const float* t00 = p.texture + (size_t)q.b00 * C;
-                    const float* t01 = p.texture + (size_t)q.b01 * C;
-                    const float* t10 = p.texture + (size_t)q.b10 * C;
-                    const float* t11 = p.texture + (size_t)q.b11 * C;
+    bool warp_done = __all_sync(0xffffffffu, done);
+    if (warp_done && lane == 0) atomicAdd(&sm.warps_done, 1);
+
+    for (int n = 0; n < n_stages; ++n) {
+        const int s = n % kStages;
+        const uint32_t parity = (n / kStages) & 1;
+        bool stopped = false;
+        while (!mbar_try_wait(&sm.full[s], parity)) {
+            if (sm.stop_at <= n) { stopped = true; break; }
+        }
+        if (stopped) break;
+        if (!warp_done) {
+            const int batch_start = range.x + n * kStageRecs;
+            const int count = min(kStageRecs, range.y - batch_start);
+            unsigned remaining = (count >= 32) ? 0xffffffffu : ((1u << count) - 1u);  // records not yet passed
+            unsigned todo = sm.bits[s][warp] & remaining;
+            while (true) {
+                // A pixel whose transmittance sits in (1e-4, 1e-4/(1-1/255)] can be terminated even by a pair
+                // with alpha < 1/255 (next_T <= 1e-4 is tested before `skip`, texture.cu:216-221): then nothing
+                // may be culled for this warp.
+                if (__any_sync(0xffffffffu, !done && T <= 1.0041e-4f)) todo = remaining;
+                if (todo == 0) break;
+                const int i = __ffs(todo) - 1;
+                remaining &= ~((2u << i) - 1u);
+                todo &= remaining;
+                const SplatRec& r = sm.recs[s][i];
+                const float4 r0 = r.q[0], r1 = r.q[1], r2 = r.q[2], r3 = r.q[3], r4 = r.q[4];
+                const PairEval e = eval_pair(pix, r0, r1, r2, r3, r4, use_blur);
+                const float next_T = T * (1.f - e.alpha);
+                if (!done) {
+                    if (next_T <= 1e-4f) {
+                        done = true;  // this splat is not composited
+                    } else if (!e.skip) {
+                        const float vis = e.alpha * T;
+                        const float4 r5 = r.q[5], r6 = r.q[6], r7 = r.q[7];
+                        rgb.x += r5.x * vis; rgb.y += r5.y * vis; rgb.z += r5.z * vis;
+                        nrm.x += vis * r1.x; nrm.y += vis * r1.y; nrm.z += vis * r1.z;
+                        const float t_view = e.t * pix.view_depth;
+                        const float u = clamp01(r6.w + (r6.x * e.delta.x + r6.y * e.delta.y + r6.z * e.delta.z));
+                        const float v = clamp01(r7.w + (r7.x * e.delta.x + r7.y * e.delta.y + r7.z * e.delta.z));
+                        const TexQuery q =
+                            tex_query(__float_as_int(r4.z), __float_as_int(r4.w), __float_as_int(r5.w), u, v, bilinear);
+                        const float* t00 = p.texture + (size_t)q.b00 * C;
+                        const float* t01 = p.texture + (size_t)q.b01 * C;
+                        const float* t10 = p.texture + (size_t)q.b10 * C;
+                        const float* t11 = p.texture + (size_t)q.b11 * C;
 #pragma unroll
-                    for (int k = 0; k < CMAX; ++k) {
-                        if (k < C) {
-                            const float val = q.w00 * __ldg(t00 + k) + q.w01 * __ldg(t01 + k) + q.w10 * __ldg(t10 + k) +
-                                              q.w11 * __ldg(t11 + k);
-                            tex[k] += vis * val;
+                        for (int k = 0; k < CMAX; ++k) {
+                            if (k < C) {
+                                const float val = q.w00 * __ldg(t00 + k) + q.w01 * __ldg(t01 + k) +
+                                                  q.w10 * __ldg(t10 + k) + q.w11 * __ldg(t11 + k);
+                                tex[k] += vis * val;
+                            }
                         }
+                        if (T > 0.5f) {  // median depth, texture.cu:286-291
+                            pix_depth = t_view;
+                            pix_depth_index = batch_start + i;
+                        }
+                        float d = e.t;
+                        if (use_ndc) d = (kFar * t_view - kFar * kNear) / ((kFar - kNear) * t_view);
+                        pix_reg += vis * (d * d * ts.x + ts.z - 2.f * d * ts.y);  // distortion(), helpers.cuh:259-264
+                        ts.x += vis; ts.y += vis * d; ts.z += vis * d * d;
+                        T = next_T;
+                        cur_idx = batch_start + i;
                     }
-                    if (T > 0.5f) {  // median depth, texture.cu:286-291
-                        pix_depth = t_view;
-                        pix_depth_index = batch_start + i;
-                    }
-                    float d = e.t;
-                    if (use_ndc) d = (kFar * t_view - kFar * kNear) / ((kFar - kNear) * t_view);
-                    // distortion(), helpers.cuh:259-264
-                    pix_reg += vis * (d * d * ts.x + ts.z - 2.f * d * ts.y);
-                    ts.x += vis; ts.y += vis * d; ts.z += vis * d * d;
-                    T = next_T;
-                    cur_idx = batch_start + i;
+                }
+                if (__all_sync(0xffffffffu, done)) {
+                    warp_done = true;
+                    if (lane == 0) atomicAdd(&sm.warps_done, 1);
+                    break;
                 }
             }
         }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.empty[s]);
     }
 
     if (pix.inside) {
@@ -196,8 +213,6 @@ __global__ void __launch_bounds__(kMaxTileThreads) texture_forward_kernel(const 
 
 using namespace gstex;
 
-extern "C" size_t gstex_texture_workspace_bytes(int n) { return (size_t)(n > 0 ? n : 1) * (sizeof(SplatRec) + sizeof(SplatRecBwd)) + 256; }
-
 extern "C" int gstex_texture_forward(int img_height, int img_width, int block_width, int channels, int n,
                                      int num_intersects, const int32_t* texture_dims,
                                      const int32_t* gaussian_ids_sorted, const int32_t* tile_bins, const float* colors,
@@ -220,25 +235,28 @@ extern "C" int gstex_texture_forward(int img_height, int img_width, int block_wi
                   !texture || !workspace))
         return GSTEX_E_BADARG;
     if (num_intersects > 0 && !gaussian_ids_sorted) return GSTEX_E_BADARG;
-    if (workspace_bytes < gstex_texture_workspace_bytes(n)) return GSTEX_E_WORKSPACE;
-    SplatRec* recs = ws_recs(workspace);
+    if (n > 0 && workspace_bytes < ws_bytes(n)) return GSTEX_E_WORKSPACE;
     if (n > 0) {
         const int rc = launch_pack_records(n, texture_dims, colors, opacities, means, scales, glob_scale, quats, uv0, umap,
-                                           vmap, viewmat, c2w, fx, fy, cx, cy, recs, ws_recs_bwd(workspace, n), st);
+                                           vmap, viewmat, c2w, fx, fy, cx, cy, settings, workspace, st);
         if (rc != GSTEX_OK) return rc;
     }
     FwdParams p;
     p.g = make_raster_geom(img_height, img_width, block_width);
-    p.C = channels; p.recs = recs; p.ids = gaussian_ids_sorted; p.tile_bins = reinterpret_cast<const int2*>(tile_bins);
+    p.C = channels;
+    p.recs = n > 0 ? ws_recs(workspace) : nullptr;
+    p.boxes = n > 0 ? ws_boxes(workspace, n) : nullptr;
+    p.ids = gaussian_ids_sorted; p.tile_bins = reinterpret_cast<const int2*>(tile_bins);
     p.texture = texture; p.viewmat = viewmat; p.c2w = c2w; p.background = background;
     p.fx = fx; p.fy = fy; p.cx = cx; p.cy = cy; p.settings = settings;
     p.out_img = out_img; p.out_depth = out_depth; p.out_reg = out_reg; p.out_texture = out_texture;
     p.out_normal = out_normal; p.final_Ts = final_Ts; p.out_reg_s = out_reg_s; p.final_idx = final_idx;
     p.depth_idx = depth_idx;
     const dim3 grid(p.g.tiles_x, p.g.tiles_y);
-    if (channels <= 3) texture_forward_kernel<3><<<grid, p.g.threads, 0, st>>>(p);
-    else if (channels <= 6) texture_forward_kernel<6><<<grid, p.g.threads, 0, st>>>(p);
-    else texture_forward_kernel<GSTEX_MAX_CHANNELS><<<grid, p.g.threads, 0, st>>>(p);
+    const int threads = p.g.threads + 32;  // + the producer warp
+    if (channels <= 3) texture_forward_kernel<3><<<grid, threads, 0, st>>>(p);
+    else if (channels <= 6) texture_forward_kernel<6><<<grid, threads, 0, st>>>(p);
+    else texture_forward_kernel<GSTEX_MAX_CHANNELS><<<grid, threads, 0, st>>>(p);
     GSTEX_LAUNCH_CHECK();
     return GSTEX_OK;
 }
