@@ -82,7 +82,7 @@ __device__ __forceinline__ void slot_target(const BwdParams& p, int slot, float*
 }
 
 template <int CMAX, bool UV>
-__global__ void __launch_bounds__(kMaxTileThreads + 32) texture_backward_kernel(const BwdParams p) {
+__global__ void __launch_bounds__(kMaxTileThreads + 32, 2) texture_backward_kernel(const BwdParams p) {
     constexpr int K = UV ? 32 : 16;
     __shared__ __align__(128) BwdShared sm;
     const RasterGeom g = p.g;

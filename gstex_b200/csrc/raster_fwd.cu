@@ -43,7 +43,7 @@ struct FwdShared {
 };
 
 template <int CMAX>
-__global__ void __launch_bounds__(kMaxTileThreads + 32) texture_forward_kernel(const FwdParams p) {
+__global__ void __launch_bounds__(kMaxTileThreads + 32, 3) texture_forward_kernel(const FwdParams p) {
     __shared__ __align__(128) FwdShared sm;
     const RasterGeom g = p.g;
     const int n_pix_warps = g.threads >> 5;
@@ -91,8 +91,12 @@ __global__ void __launch_bounds__(kMaxTileThreads + 32) texture_forward_kernel(c
             }
             if (lane < n_pix_warps) sm.bits[s][lane] = mine;
             __syncwarp();
-            if (lane == 0) mbar_arrive_expect_tx(&sm.full[s], (uint32_t)__popc(any) * (uint32_t)sizeof(SplatRec));
-            if ((any >> lane) & 1u) bulk_copy_g2s(&sm.recs[s][lane], p.recs + gid, sizeof(SplatRec), &sm.full[s]);
+            // every record of the stage is copied, also those no warp asked for: a warp in `danger` mode (below)
+            // evaluates all of them
+            (void)any;
+            const unsigned present = __ballot_sync(0xffffffffu, gid >= 0);
+            if (lane == 0) mbar_arrive_expect_tx(&sm.full[s], (uint32_t)__popc(present) * (uint32_t)sizeof(SplatRec));
+            if (gid >= 0) bulk_copy_g2s(&sm.recs[s][lane], p.recs + gid, sizeof(SplatRec), &sm.full[s]);
         }
         return;
     }
