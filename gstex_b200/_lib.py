@@ -33,9 +33,13 @@ _SIGNATURES = {
     "gstex_sort_isects": (I, [I, P, P, P, P, I, P, SZ, P]),
     "gstex_get_tile_bin_edges": (I, [I, P, I, P, P]),
     "gstex_texture_workspace_bytes": (SZ, [I]),
-    "gstex_texture_forward": (I, [I, I, I, I, I, I] + [P] * 7 + [F] + [P] * 7 + [F, F, F, F, I] + [P] * 10 + [P, SZ, P]),
+    "gstex_pair_stream_bytes": (SZ, [I, I, I, ctypes.c_longlong]),
+    "gstex_pair_stream_supported": (I, [I, I, I]),
+    "gstex_texture_forward": (I, [I, I, I, I, I, I] + [P] * 7 + [F] + [P] * 7 + [F, F, F, F, I] + [P] * 10 +
+                              [P, SZ, P, SZ, P]),
     "gstex_texture_backward": (I, [I, I, I, I, I, I] + [P] * 7 + [F] + [P] * 7 + [F, F, F, F, I] + [P] * 11 + [P] * 9 +
-                               [P, SZ, I, P]),
+                               [P, SZ, I, P, SZ, P, SZ, ctypes.c_longlong, I, P]),
+    "gstex_grad_scratch_bytes": (SZ, [I, ctypes.c_longlong]),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)
@@ -75,7 +79,8 @@ class _TimedLib:
     def __getattr__(self, name):
         fn = getattr(self._cdll, name)
         if not name.startswith("gstex_") or name.endswith("_bytes") or name in ("gstex_abi_version", "gstex_error_string",
-                                                                               "gstex_launch_count"):
+                                                                               "gstex_launch_count",
+                                                                               "gstex_pair_stream_supported"):
             return fn
 
         def call(*args):
@@ -114,7 +119,7 @@ def load() -> ctypes.CDLL:
         fn = getattr(lib, name)  # AttributeError if the library does not export what the header declares
         fn.restype = res
         fn.argtypes = args
-    if lib.gstex_abi_version() != 1:
+    if lib.gstex_abi_version() != 2:
         raise GstexNativeError("gstex_b200: ABI version mismatch between the Python layer and the CUDA library")
     _LIB = _TimedLib(lib)
     return _LIB

@@ -1,0 +1,36 @@
+// bwd_stream.cuh -- interface between the backward entry point (raster_bwd.cu) and the stream kernel.
+#pragma once
+#include "pair_stream.cuh"
+#include "raster_common.cuh"
+
+namespace gstex {
+
+struct StreamBwdParams {
+    RasterGeom g;
+    int C;
+    const SplatRec* recs;
+    const SplatRecBwd* recs_bwd;
+    const float* texture;  // unused by the math (samples are recorded); kept for symmetry
+    const float *viewmat, *c2w, *background;
+    float fx, fy, cx, cy;
+    int settings;
+    const float *final_Ts, *final_s;
+    const int32_t* depth_idx;
+    const float *v_output, *v_output_depth, *v_output_reg, *v_output_alpha, *v_output_texture, *v_output_normal;
+    float *v_colors, *v_opacity, *v_means, *v_scales, *v_quats, *v_texture;
+    StreamView sv;
+    // padded accumulators (grad scratch): texel gradients as (T,4), splat gradients as (N,16) floats:
+    // [colors3 opacity | means3 - | scales.xy - - | quats4]
+    float4 *tex_acc, *splat_acc;
+    int n;
+    long long num_texels;
+};
+
+static inline size_t grad_scratch_bytes(int n, long long num_texels) {
+    return ((size_t)(num_texels > 0 ? num_texels : 0) + 4 * (size_t)(n > 0 ? n : 0)) * sizeof(float4);
+}
+
+// Enqueues the stream backward; the kernel returns at once when the forward flagged a pool overflow.
+int launch_backward_stream(const StreamBwdParams& p, cudaStream_t st);
+
+}  // namespace gstex

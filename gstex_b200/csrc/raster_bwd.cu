@@ -11,6 +11,7 @@
 //     lane 2s holds the total of value s, so ONE red instruction issues all of the warp's atomics for that
 //     splat instead of 22 serial ones from lane 0;
 //   * the bilinear index/weight computation is done once per pair, not once per channel.
+#include "bwd_stream.cuh"
 #include "pipeline.cuh"
 
 namespace gstex {
@@ -50,6 +51,8 @@ struct BwdParams {
     const int32_t *final_idx, *depth_idx;
     const float *v_output, *v_output_depth, *v_output_reg, *v_output_alpha, *v_output_texture, *v_output_normal;
     float *v_colors, *v_opacity, *v_means, *v_scales, *v_quats, *v_uv0, *v_umap, *v_vmap, *v_texture;
+    // non-null when a pair stream exists: this kernel only runs if the forward flagged a pool overflow there
+    const uint32_t* stream_overflow;
 };
 
 struct BwdShared {
@@ -85,6 +88,7 @@ template <int CMAX, bool UV>
 __global__ void __launch_bounds__(kMaxTileThreads + 32, 2) texture_backward_kernel(const BwdParams p) {
     constexpr int K = UV ? 32 : 16;
     __shared__ __align__(128) BwdShared sm;
+    if (p.stream_overflow != nullptr && *(volatile const uint32_t*)p.stream_overflow == 0u) return;
     const RasterGeom g = p.g;
     const int n_pix_warps = g.threads >> 5;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -322,6 +326,10 @@ static void launch_bwd(const BwdParams& p, bool uv, cudaStream_t st) {
     else texture_backward_kernel<CMAX, false><<<grid, threads, 0, st>>>(p);
 }
 
+extern "C" int gstex_pair_stream_supported(int channels, int n, int settings);
+
+extern "C" size_t gstex_grad_scratch_bytes(int n, long long num_texels) { return grad_scratch_bytes(n, num_texels); }
+
 extern "C" int gstex_texture_backward(
     int img_height, int img_width, int block_width, int channels, int n, int num_intersects,
     const int32_t* texture_dims, const int32_t* gaussian_ids_sorted, const int32_t* tile_bins, const float* colors,
@@ -332,13 +340,33 @@ extern "C" int gstex_texture_backward(
     const float* v_output, const float* v_output_depth, const float* v_output_reg, const float* v_output_alpha,
     const float* v_output_texture, const float* v_output_normal, float* v_colors, float* v_opacity, float* v_means,
     float* v_scales, float* v_quats, float* v_uv0, float* v_umap, float* v_vmap, float* v_texture, void* workspace,
-    size_t workspace_bytes, int records_valid, void* stream) {
+    size_t workspace_bytes, int records_valid, void* pair_stream, size_t pair_stream_bytes, void* grad_scratch,
+    size_t grad_scratch_size, long long num_texels, int zero_fill, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     if (img_height <= 0 || img_width <= 0 || block_width < 2 || block_width > 16 || n < 0 || num_intersects < 0)
         return GSTEX_E_BADARG;
     if (settings & ~GSTEX_SETTINGS_SUPPORTED) return GSTEX_E_UNSUPPORTED;
     if (channels < 1 || channels > GSTEX_MAX_CHANNELS) return GSTEX_E_UNSUPPORTED;
-    if (n == 0 || num_intersects == 0) return GSTEX_OK;  // gradients stay zero (texture.py:331-340)
+    if (zero_fill && (num_texels < 0 || (n > 0 && (!v_colors || !v_opacity || !v_means || !v_scales || !v_quats ||
+                                                    !v_uv0 || !v_umap || !v_vmap || !v_texture))))
+        return GSTEX_E_BADARG;
+    // zero_fill: the caller passed uninitialised gradient buffers (the reference allocates them with torch::zeros)
+    auto zero = [&](bool also_stream_outputs) -> int {
+        if (!zero_fill || n == 0) return GSTEX_OK;
+        const size_t f = sizeof(float);
+        GSTEX_CUDA_TRY(cudaMemsetAsync(v_uv0, 0, (size_t)n * 2 * f, st));
+        GSTEX_CUDA_TRY(cudaMemsetAsync(v_umap, 0, (size_t)n * 3 * f, st));
+        GSTEX_CUDA_TRY(cudaMemsetAsync(v_vmap, 0, (size_t)n * 3 * f, st));
+        if (!also_stream_outputs) return GSTEX_OK;
+        GSTEX_CUDA_TRY(cudaMemsetAsync(v_colors, 0, (size_t)n * 3 * f, st));
+        GSTEX_CUDA_TRY(cudaMemsetAsync(v_opacity, 0, (size_t)n * f, st));
+        GSTEX_CUDA_TRY(cudaMemsetAsync(v_means, 0, (size_t)n * 3 * f, st));
+        GSTEX_CUDA_TRY(cudaMemsetAsync(v_scales, 0, (size_t)n * 3 * f, st));
+        GSTEX_CUDA_TRY(cudaMemsetAsync(v_quats, 0, (size_t)n * 4 * f, st));
+        GSTEX_CUDA_TRY(cudaMemsetAsync(v_texture, 0, (size_t)num_texels * channels * f, st));
+        return GSTEX_OK;
+    };
+    if (n == 0 || num_intersects == 0) return zero(true);  // gradients are zero (texture.py:331-340)
     if (!texture_dims || !gaussian_ids_sorted || !tile_bins || !colors || !opacities || !means || !scales || !quats ||
         !uv0 || !umap || !vmap || !texture || !viewmat || !c2w || !background || !final_Ts || !final_idx ||
         !depth_idx || !final_s || !v_output || !v_output_depth || !v_output_reg || !v_output_alpha ||
@@ -362,6 +390,33 @@ extern "C" int gstex_texture_backward(
     p.v_output_alpha = v_output_alpha; p.v_output_texture = v_output_texture; p.v_output_normal = v_output_normal;
     p.v_colors = v_colors; p.v_opacity = v_opacity; p.v_means = v_means; p.v_scales = v_scales; p.v_quats = v_quats;
     p.v_uv0 = v_uv0; p.v_umap = v_umap; p.v_vmap = v_vmap; p.v_texture = v_texture;
+    p.stream_overflow = nullptr;
+    // Fast path: the forward of this view recorded its contributing pairs.  Both kernels are enqueued; exactly one
+    // of them does the work, decided on the device by the overflow flag in the stream header (no host sync).
+    StreamBwdParams sp;
+    if (pair_stream != nullptr && grad_scratch != nullptr && num_texels > 0 && ((uintptr_t)grad_scratch & 15) == 0 &&
+        ((uintptr_t)v_quats & 15) == 0 && grad_scratch_size >= grad_scratch_bytes(n, num_texels) && records_valid &&
+        gstex_pair_stream_supported(channels, n, settings) &&
+        make_stream_view(pair_stream, pair_stream_bytes, p.g.tiles_x * p.g.tiles_y, sp.sv)) {
+        sp.g = p.g; sp.C = channels; sp.recs = p.recs; sp.recs_bwd = p.recs_bwd; sp.texture = texture;
+        sp.viewmat = viewmat; sp.c2w = c2w; sp.background = background; sp.fx = fx; sp.fy = fy; sp.cx = cx; sp.cy = cy;
+        sp.settings = settings; sp.final_Ts = final_Ts; sp.final_s = final_s; sp.depth_idx = depth_idx;
+        sp.v_output = v_output; sp.v_output_depth = v_output_depth; sp.v_output_reg = v_output_reg;
+        sp.v_output_alpha = v_output_alpha; sp.v_output_texture = v_output_texture; sp.v_output_normal = v_output_normal;
+        sp.v_colors = v_colors; sp.v_opacity = v_opacity; sp.v_means = v_means; sp.v_scales = v_scales;
+        sp.v_quats = v_quats; sp.v_texture = v_texture;
+        sp.n = n; sp.num_texels = num_texels;
+        sp.tex_acc = reinterpret_cast<float4*>(grad_scratch); sp.splat_acc = sp.tex_acc + num_texels;
+        // the unpack kernel of the stream path overwrites colors/opacity/means/scales/quats/texture gradients
+        int rc = zero(false);
+        if (rc != GSTEX_OK) return rc;
+        rc = launch_backward_stream(sp, st);
+        if (rc != GSTEX_OK) return rc;
+        p.stream_overflow = &sp.sv.hdr->overflow;
+    } else {
+        const int rc = zero(true);
+        if (rc != GSTEX_OK) return rc;
+    }
     const bool uv = (settings & GSTEX_SET_UV_GRAD) != 0;
     if (channels <= 3) launch_bwd<3>(p, uv, st);
     else if (channels <= 6) launch_bwd<6>(p, uv, st);

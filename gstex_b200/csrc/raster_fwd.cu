@@ -13,6 +13,9 @@
 //   * the bilinear index/weight computation is done once per pair, not once per channel; texture
 //     accumulators live in registers (channel count is a template bound), not in a float[64] local array;
 //   * a warp stops as soon as all its 32 pixels are done (ballot), the producer when all warps are.
+#include <cstddef>
+
+#include "pair_stream.cuh"
 #include "pipeline.cuh"
 
 namespace gstex {
@@ -30,6 +33,7 @@ struct FwdParams {
     int settings;
     float *out_img, *out_depth, *out_reg, *out_texture, *out_normal, *final_Ts, *out_reg_s;
     int32_t *final_idx, *depth_idx;
+    StreamView sv;  // pair stream (REC kernels only)
 };
 
 struct FwdShared {
@@ -37,13 +41,14 @@ struct FwdShared {
     uint64_t full[kStages];
     uint64_t empty[kStages];
     unsigned bits[kStages][8];  // per stage, per pixel warp: records worth evaluating
+    int ids[kStages][kStageRecs];  // splat ids of the stage (recorded into the pair stream)
     Camera cam;
     int warps_done;
     volatile int stop_at;
 };
 
-template <int CMAX>
-__global__ void __launch_bounds__(kMaxTileThreads + 32, 3) texture_forward_kernel(const FwdParams p) {
+template <int CMAX, bool REC>
+__global__ void __launch_bounds__(kMaxTileThreads + 32, REC ? 2 : 3) texture_forward_kernel(const FwdParams p) {
     __shared__ __align__(128) FwdShared sm;
     const RasterGeom g = p.g;
     const int n_pix_warps = g.threads >> 5;
@@ -68,13 +73,19 @@ __global__ void __launch_bounds__(kMaxTileThreads + 32, 3) texture_forward_kerne
         // ===================== producer warp: gather records, build per-warp masks =====================
         const float tx0 = (float)(blockIdx.x * g.bw) + 0.5f, tx1 = (float)(blockIdx.x * g.bw + g.bw - 1) + 0.5f;
         const float ty = (float)(blockIdx.y * g.bw) + 0.5f;
+        // software pipeline: ids two stages ahead, support boxes one stage ahead of the stage being published
+        const float4 no_box = make_float4(1.f, 1.f, 0.f, 0.f);
         int g_next = (range.x + lane < range.y) ? __ldg(p.ids + range.x + lane) : -1;
+        int g_next2 = (range.x + kStageRecs + lane < range.y) ? __ldg(p.ids + range.x + kStageRecs + lane) : -1;
+        float4 box_next = (g_next >= 0) ? __ldg(p.boxes + g_next) : no_box;
         for (int n = 0; n < n_stages; ++n) {
             const int s = n % kStages;
             const int gid = g_next;
-            const int nxt = range.x + (n + 1) * kStageRecs + lane;
-            g_next = (nxt < range.y) ? __ldg(p.ids + nxt) : -1;  // prefetch the next stage's ids
-            const float4 box = (gid >= 0) ? __ldg(p.boxes + gid) : make_float4(1.f, 1.f, 0.f, 0.f);
+            const float4 box = box_next;
+            g_next = g_next2;
+            const int nxt = range.x + (n + 2) * kStageRecs + lane;
+            g_next2 = (nxt < range.y) ? __ldg(p.ids + nxt) : -1;
+            box_next = (g_next >= 0) ? __ldg(p.boxes + g_next) : no_box;
             if (n >= kStages) mbar_wait(&sm.empty[s], ((n / kStages) - 1) & 1);
             if (*(volatile int*)&sm.warps_done >= n_pix_warps) {  // every pixel of the tile is finished
                 if (lane == 0) sm.stop_at = n;
@@ -90,6 +101,7 @@ __global__ void __launch_bounds__(kMaxTileThreads + 32, 3) texture_forward_kerne
                 any |= b;
             }
             if (lane < n_pix_warps) sm.bits[s][lane] = mine;
+            if (REC) sm.ids[s][lane] = gid;
             __syncwarp();
             // every record of the stage is copied, also those no warp asked for: a warp in `danger` mode (below)
             // evaluates all of them
@@ -116,6 +128,10 @@ __global__ void __launch_bounds__(kMaxTileThreads + 32, 3) texture_forward_kerne
     float tex[CMAX];
 #pragma unroll
     for (int k = 0; k < CMAX; ++k) tex[k] = 0.f;
+
+    // pair-stream cursor of this unit (REC only): current chunk, items in it, items in total
+    int cur_chunk = -1, fill = kChunkItems, cnt = 0;
+    bool rec = REC && (*(volatile uint32_t*)&p.sv.hdr->overflow == 0u);
 
     bool warp_done = __all_sync(0xffffffffu, done);
     if (warp_done && lane == 0) atomicAdd(&sm.warps_done, 1);
@@ -146,6 +162,8 @@ __global__ void __launch_bounds__(kMaxTileThreads + 32, 3) texture_forward_kerne
                 const float4 r0 = r.q[0], r1 = r.q[1], r2 = r.q[2], r3 = r.q[3], r4 = r.q[4];
                 const PairEval e = eval_pair(pix, r0, r1, r2, r3, r4, use_blur);
                 const float next_T = T * (1.f - e.alpha);
+                bool hit = false;
+                float h_T = 0.f, h_u = 0.f, h_v = 0.f, h_val[3] = {0.f, 0.f, 0.f};
                 if (!done) {
                     if (next_T <= 1e-4f) {
                         done = true;  // this splat is not composited
@@ -169,8 +187,10 @@ __global__ void __launch_bounds__(kMaxTileThreads + 32, 3) texture_forward_kerne
                                 const float val = q.w00 * __ldg(t00 + k) + q.w01 * __ldg(t01 + k) +
                                                   q.w10 * __ldg(t10 + k) + q.w11 * __ldg(t11 + k);
                                 tex[k] += vis * val;
+                                if (REC && k < 3) h_val[k] = val;
                             }
                         }
+                        if (REC) { hit = true; h_T = T; h_u = u; h_v = v; }
                         if (T > 0.5f) {  // median depth, texture.cu:286-291
                             pix_depth = t_view;
                             pix_depth_index = batch_start + i;
@@ -181,6 +201,39 @@ __global__ void __launch_bounds__(kMaxTileThreads + 32, 3) texture_forward_kerne
                         ts.x += vis; ts.y += vis * d; ts.z += vis * d * d;
                         T = next_T;
                         cur_idx = batch_start + i;
+                    }
+                }
+                if (REC) {  // append this splat's contributing pairs to the unit's stream, lane order
+                    const unsigned hb = __ballot_sync(0xffffffffu, hit);
+                    if (hb != 0u && rec) {
+                        const int nh = __popc(hb);
+                        int new_chunk = cur_chunk;
+                        if (fill + nh > kChunkItems) {
+                            int c = 0;
+                            if (lane == 0) c = (int)atomicAdd(&p.sv.hdr->next_chunk, 1u);
+                            c = __shfl_sync(0xffffffffu, c, 0);
+                            if (c >= p.sv.num_chunks) {
+                                if (lane == 0) p.sv.hdr->overflow = 1u;
+                                rec = false;
+                            } else {
+                                if (lane == 0) p.sv.chunk_prev[c] = cur_chunk;
+                                new_chunk = c;
+                            }
+                        }
+                        if (rec) {
+                            if (hit) {
+                                int pos = fill + __popc(hb & ((1u << lane) - 1u));
+                                int ch = cur_chunk;
+                                if (pos >= kChunkItems) { pos -= kChunkItems; ch = new_chunk; }
+                                float4* dst = reinterpret_cast<float4*>(p.sv.items + (size_t)ch * kChunkItems + pos);
+                                const uint32_t gl = ((uint32_t)sm.ids[s][i] << 5) | (uint32_t)lane;
+                                dst[0] = make_float4(__uint_as_float(gl), __int_as_float(batch_start + i), h_T, h_u);
+                                dst[1] = make_float4(h_v, h_val[0], h_val[1], h_val[2]);
+                            }
+                            fill += nh;
+                            if (fill > kChunkItems) { fill -= kChunkItems; cur_chunk = new_chunk; }
+                            cnt += nh;
+                        }
                     }
                 }
                 if (__all_sync(0xffffffffu, done)) {
@@ -194,6 +247,11 @@ __global__ void __launch_bounds__(kMaxTileThreads + 32, 3) texture_forward_kerne
         if (lane == 0) mbar_arrive(&sm.empty[s]);
     }
 
+    if (REC) {
+        const int unit0 = tile_id * kUnitsPerTile;
+        if (lane == 0) p.sv.units[unit0 + warp] = make_int2(cur_chunk, rec ? cnt : 0);
+        if (warp == 0 && lane >= n_pix_warps && lane < kUnitsPerTile) p.sv.units[unit0 + lane] = make_int2(-1, 0);
+    }
     if (pix.inside) {
         const int id = pix.pix_id;
         p.final_Ts[id] = T;
@@ -217,6 +275,19 @@ __global__ void __launch_bounds__(kMaxTileThreads + 32, 3) texture_forward_kerne
 
 using namespace gstex;
 
+extern "C" int gstex_pair_stream_supported(int channels, int n, int settings) {
+    return channels >= 1 && channels <= 3 && n > 0 && n < (1 << 27) && !(settings & GSTEX_SET_UV_GRAD);
+}
+
+extern "C" size_t gstex_pair_stream_bytes(int img_height, int img_width, int block_width, long long max_pairs) {
+    if (img_height <= 0 || img_width <= 0 || block_width < 2 || block_width > 16 || max_pairs < 0) return 0;
+    const RasterGeom g = make_raster_geom(img_height, img_width, block_width);
+    const size_t units = (size_t)g.tiles_x * g.tiles_y * kUnitsPerTile;
+    // every unit can leave one partly filled chunk behind
+    const size_t chunks = (size_t)(max_pairs + kChunkItems - 1) / kChunkItems + units;
+    return stream_fixed_bytes((int)units) + 256 + chunks * (sizeof(PairItem) * kChunkItems + sizeof(int32_t)) + 128;
+}
+
 extern "C" int gstex_texture_forward(int img_height, int img_width, int block_width, int channels, int n,
                                      int num_intersects, const int32_t* texture_dims,
                                      const int32_t* gaussian_ids_sorted, const int32_t* tile_bins, const float* colors,
@@ -226,7 +297,8 @@ extern "C" int gstex_texture_forward(int img_height, int img_width, int block_wi
                                      float cx, float cy, int settings, const float* background, float* out_img,
                                      float* out_depth, float* out_reg, float* out_texture, float* out_normal,
                                      float* final_Ts, int32_t* final_idx, int32_t* depth_idx, float* out_reg_s,
-                                     void* workspace, size_t workspace_bytes, void* stream) {
+                                     void* workspace, size_t workspace_bytes, void* pair_stream,
+                                     size_t pair_stream_bytes, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     if (img_height <= 0 || img_width <= 0 || block_width < 2 || block_width > 16 || n < 0 || num_intersects < 0)
         return GSTEX_E_BADARG;
@@ -258,9 +330,19 @@ extern "C" int gstex_texture_forward(int img_height, int img_width, int block_wi
     p.depth_idx = depth_idx;
     const dim3 grid(p.g.tiles_x, p.g.tiles_y);
     const int threads = p.g.threads + 32;  // + the producer warp
-    if (channels <= 3) texture_forward_kernel<3><<<grid, threads, 0, st>>>(p);
-    else if (channels <= 6) texture_forward_kernel<6><<<grid, threads, 0, st>>>(p);
-    else texture_forward_kernel<GSTEX_MAX_CHANNELS><<<grid, threads, 0, st>>>(p);
+    // Record the pair stream for the stream backward when the caller gave a pool and the configuration is the
+    // one that backward covers (<= 3 channels, no uv gradients); otherwise the backward recomputes.
+    bool record = pair_stream != nullptr && gstex_pair_stream_supported(channels, n, settings) &&
+                  make_stream_view(pair_stream, pair_stream_bytes, p.g.tiles_x * p.g.tiles_y, p.sv);
+    if (pair_stream != nullptr && pair_stream_bytes >= sizeof(StreamHeader)) {
+        GSTEX_CUDA_TRY(cudaMemsetAsync(pair_stream, 0, sizeof(StreamHeader), st));
+        if (!record)  // tell the backward there is nothing to read
+            GSTEX_CUDA_TRY(cudaMemsetAsync(reinterpret_cast<char*>(pair_stream) + offsetof(StreamHeader, overflow), 1, 1, st));
+    }
+    if (record) texture_forward_kernel<3, true><<<grid, threads, 0, st>>>(p);
+    else if (channels <= 3) texture_forward_kernel<3, false><<<grid, threads, 0, st>>>(p);
+    else if (channels <= 6) texture_forward_kernel<6, false><<<grid, threads, 0, st>>>(p);
+    else texture_forward_kernel<GSTEX_MAX_CHANNELS, false><<<grid, threads, 0, st>>>(p);
     GSTEX_LAUNCH_CHECK();
     return GSTEX_OK;
 }

@@ -7,6 +7,7 @@ Same positional signature (27 arguments), the same six outputs
 """
 from __future__ import annotations
 
+import os
 from typing import Optional, Tuple
 
 import torch
@@ -17,6 +18,48 @@ from . import _lib
 from .utils import bin_and_sort_gaussians, compute_cumulative_intersects
 
 SUPPORTED_SETTINGS = (1 << 2) | (1 << 8) | (1 << 9) | (1 << 10)
+
+
+class PairStreamPolicy:
+    """Sizing of the pair stream (the forward's record of contributing (pixel, splat) pairs the stream backward
+    reads, include/gstex_b200.h).  No counterpart in the reference, which always recomputes.  The pool is sized
+    from the pairs the previous views actually produced (read back asynchronously, never synchronising); a pool
+    that turns out too small only costs speed: the backward then recomputes and the next pool is larger."""
+
+    enabled = os.environ.get("GSTEX_B200_PAIR_STREAM", "1") != "0"
+    pairs_per_pixel = float(os.environ.get("GSTEX_B200_PAIRS_PER_PIXEL", "40"))
+    headroom = 1.5
+    max_bytes = None  # optional hard cap of the pool in bytes (tests use it to provoke the overflow fallback)
+    _state = {}  # (device index, H, W, block_width) -> {"pairs": int, "pending": (pinned tensor, event) | None}
+
+    @classmethod
+    def max_pairs(cls, dev, H, W, bw) -> int:
+        st = cls._state.setdefault((dev.index, H, W, bw), {"pairs": int(cls.pairs_per_pixel * H * W), "pending": None})
+        pend = st["pending"]
+        if pend is not None and pend[1].query():
+            hdr = pend[0]
+            used, overflow = int(hdr[0]) * 128, int(hdr[1])
+            st["last"] = (used, overflow)  # pairs' worth of chunks taken, overflow flag of the last reported view
+            if overflow:
+                st["pairs"] = max(2 * st["pairs"], 1 << 20)
+            else:
+                st["pairs"] = max(int(cls.headroom * used), st["pairs"] // 2, 1 << 20)
+            st["pending"] = None
+        return st["pairs"]
+
+    @classmethod
+    def report(cls, dev, H, W, bw, stream_buf) -> None:
+        """Queue an async read-back of the stream header (chunks used, overflow flag)."""
+        st = cls._state.get((dev.index, H, W, bw))
+        if st is None or st["pending"] is not None:
+            return
+        host = st.get("host")
+        if host is None:
+            host = st["host"] = torch.empty(4, dtype=torch.int32).pin_memory()
+        host.copy_(stream_buf[:16].view(torch.int32), non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        st["pending"] = (host, ev)
 
 
 def texture_gaussians(
@@ -77,7 +120,7 @@ def texture_gaussians(
 
 def _raster_forward(texture_info, texture_dims, gaussian_ids_sorted, tile_bins, colors, opacity, means, scales,
                     glob_scale, quats, uv0, umap, vmap, texture, viewmat, c2w, fx, fy, cx, cy, img_height, img_width,
-                    block_width, settings, background, num_intersects):
+                    block_width, settings, background, num_intersects, record_pairs=False):
     """ref: `_C.texture_forward` (cuda/csrc/texture.cu:762-901).  Returns the 9 tensors + the workspace
     holding the per-view packed records (re-used by the backward)."""
     dev = _lib.require_cuda(texture_dims, colors, opacity, means, scales, quats, uv0, umap, vmap, texture, viewmat,
@@ -102,6 +145,13 @@ def _raster_forward(texture_info, texture_dims, gaussian_ids_sorted, tile_bins, 
     out_reg_s = torch.empty((H, W, 3), **f32)
     lib = _lib.load()
     ws = torch.empty((lib.gstex_texture_workspace_bytes(n),), dtype=torch.uint8, device=dev)
+    pairs = None
+    if (record_pairs and PairStreamPolicy.enabled and num_intersects > 0
+            and lib.gstex_pair_stream_supported(C, n, int(settings))):
+        nbytes = lib.gstex_pair_stream_bytes(H, W, int(block_width), PairStreamPolicy.max_pairs(dev, H, W, int(block_width)))
+        if PairStreamPolicy.max_bytes is not None:
+            nbytes = min(nbytes, int(PairStreamPolicy.max_bytes))
+        pairs = torch.empty((nbytes,), dtype=torch.uint8, device=dev)
     p = _lib.ptr
     with torch.cuda.device(dev):
         rc = lib.gstex_texture_forward(
@@ -109,9 +159,12 @@ def _raster_forward(texture_info, texture_dims, gaussian_ids_sorted, tile_bins, 
             p(colors), p(opacity), p(means), p(scales), float(glob_scale), p(quats), p(uv0), p(umap), p(vmap),
             p(texture), p(viewmat), p(c2w), float(fx), float(fy), float(cx), float(cy), int(settings), p(background),
             p(out_img), p(out_depth), p(out_reg), p(out_texture), p(out_normal), p(final_Ts), p(final_idx),
-            p(depth_idx), p(out_reg_s), p(ws), ws.numel(), _lib.stream_ptr(dev))
+            p(depth_idx), p(out_reg_s), p(ws), ws.numel(), p(pairs), pairs.numel() if pairs is not None else 0,
+            _lib.stream_ptr(dev))
     _lib.check(rc, "gstex_texture_forward")
-    return (out_img, out_depth, out_reg, out_texture, out_normal, final_Ts, final_idx, depth_idx, out_reg_s), ws
+    if pairs is not None:
+        PairStreamPolicy.report(dev, H, W, int(block_width), pairs)
+    return (out_img, out_depth, out_reg, out_texture, out_normal, final_Ts, final_idx, depth_idx, out_reg_s), ws, pairs
 
 
 class _TextureGaussians(Function):
@@ -133,10 +186,11 @@ class _TextureGaussians(Function):
         else:
             (_, _, _, gaussian_ids_sorted, tile_bins) = bin_and_sort_gaussians(
                 num_points, num_intersects, centers, extents, depths, cum_tiles_hit, tile_bounds, block_width)
-        outputs, ws = _raster_forward(texture_info, texture_dims, gaussian_ids_sorted, tile_bins, colors, opacity,
-                                      means, scales, glob_scale, quats, uv0, umap, vmap, texture, viewmat, c2w, fx, fy,
-                                      cx, cy, img_height, img_width, block_width, settings, background,
-                                      max(num_intersects, 0))
+        outputs, ws, pairs = _raster_forward(texture_info, texture_dims, gaussian_ids_sorted, tile_bins, colors,
+                                             opacity, means, scales, glob_scale, quats, uv0, umap, vmap, texture,
+                                             viewmat, c2w, fx, fy, cx, cy, img_height, img_width, block_width,
+                                             settings, background, max(num_intersects, 0),
+                                             record_pairs=any(ctx.needs_input_grad))
         out_img, out_depth, out_reg, out_texture, out_normal, final_Ts, final_idx, depth_idx, out_reg_s = outputs
         ctx.img_width, ctx.img_height = img_width, img_height
         ctx.texture_info = texture_info
@@ -146,6 +200,7 @@ class _TextureGaussians(Function):
         ctx.block_width = block_width
         ctx.settings = settings
         ctx.workspace = ws  # packed per-view records, valid as long as the inputs are unchanged
+        ctx.pair_stream = pairs  # contributing pairs recorded by the forward (None: the backward recomputes)
         ctx.save_for_backward(texture_dims, gaussian_ids_sorted, tile_bins, colors, opacity, means, scales, quats,
                               uv0, umap, vmap, texture, viewmat, c2w, background, final_Ts, final_idx, depth_idx,
                               out_reg_s)
@@ -172,29 +227,35 @@ class _TextureGaussians(Function):
         v_out_texture = grad_or_zero(v_out_texture, (H, W, C))
         v_out_normal = grad_or_zero(v_out_normal, (H, W, 3))
 
-        v_colors = torch.zeros_like(colors)
-        v_opacity = torch.zeros_like(opacity)
-        v_means = torch.zeros_like(means)
-        v_scales = torch.zeros_like(scales)
-        v_quats = torch.zeros_like(quats)
-        v_uv0 = torch.zeros_like(uv0)
-        v_umap = torch.zeros_like(umap)
-        v_vmap = torch.zeros_like(vmap)
-        v_texture = torch.zeros_like(texture)
-        if ctx.num_intersects >= 1:
-            lib = _lib.load()
-            ws = ctx.workspace
-            p = _lib.ptr
-            with torch.cuda.device(dev):
-                rc = lib.gstex_texture_backward(
-                    int(H), int(W), int(ctx.block_width), C, means.shape[0], int(ctx.num_intersects),
-                    p(texture_dims), p(gaussian_ids_sorted), p(tile_bins), p(colors), p(opacity), p(means), p(scales),
-                    float(ctx.glob_scale), p(quats), p(uv0), p(umap), p(vmap), p(texture), p(viewmat), p(c2w),
-                    float(ctx.fx), float(ctx.fy), float(ctx.cx), float(ctx.cy), int(ctx.settings), p(background),
-                    p(final_Ts), p(final_idx), p(depth_idx), p(out_reg_s), p(v_out_img), p(v_out_depth), p(v_out_reg),
-                    p(v_out_alpha), p(v_out_texture), p(v_out_normal), p(v_colors), p(v_opacity), p(v_means),
-                    p(v_scales), p(v_quats), p(v_uv0), p(v_umap), p(v_vmap), p(v_texture), p(ws), ws.numel(), 1,
-                    _lib.stream_ptr(dev))
-            _lib.check(rc, "gstex_texture_backward")
+        # uninitialised: the library defines every element (zero_fill=1), which saves nine memsets on the stream path
+        v_colors = torch.empty_like(colors)
+        v_opacity = torch.empty_like(opacity)
+        v_means = torch.empty_like(means)
+        v_scales = torch.empty_like(scales)
+        v_quats = torch.empty_like(quats)
+        v_uv0 = torch.empty_like(uv0)
+        v_umap = torch.empty_like(umap)
+        v_vmap = torch.empty_like(vmap)
+        v_texture = torch.empty_like(texture)
+        lib = _lib.load()
+        ws = ctx.workspace
+        p = _lib.ptr
+        pairs = ctx.pair_stream
+        scratch = None
+        if pairs is not None:
+            scratch = torch.empty((lib.gstex_grad_scratch_bytes(means.shape[0], texture.shape[0]),),
+                                  dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            rc = lib.gstex_texture_backward(
+                int(H), int(W), int(ctx.block_width), C, means.shape[0], max(int(ctx.num_intersects), 0),
+                p(texture_dims), p(gaussian_ids_sorted), p(tile_bins), p(colors), p(opacity), p(means), p(scales),
+                float(ctx.glob_scale), p(quats), p(uv0), p(umap), p(vmap), p(texture), p(viewmat), p(c2w),
+                float(ctx.fx), float(ctx.fy), float(ctx.cx), float(ctx.cy), int(ctx.settings), p(background),
+                p(final_Ts), p(final_idx), p(depth_idx), p(out_reg_s), p(v_out_img), p(v_out_depth), p(v_out_reg),
+                p(v_out_alpha), p(v_out_texture), p(v_out_normal), p(v_colors), p(v_opacity), p(v_means),
+                p(v_scales), p(v_quats), p(v_uv0), p(v_umap), p(v_vmap), p(v_texture), p(ws), ws.numel(), 1,
+                p(pairs), pairs.numel() if pairs is not None else 0, p(scratch),
+                scratch.numel() if scratch is not None else 0, int(texture.shape[0]), 1, _lib.stream_ptr(dev))
+        _lib.check(rc, "gstex_texture_backward")
         return (None, None, None, None, None, None, v_colors, v_opacity, v_means, v_scales, None, v_quats, v_uv0,
                 v_umap, v_vmap, v_texture, None, None, None, None, None, None, None, None, None, None, None)

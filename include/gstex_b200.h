@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define GSTEX_B200_ABI_VERSION 1
+#define GSTEX_B200_ABI_VERSION 2
 
 #define GSTEX_OK 0
 #define GSTEX_E_BADARG (-1)      /* null pointer, negative size, block_width outside [2,16] ... */
@@ -107,8 +107,18 @@ int gstex_get_tile_bin_edges(int num_intersects, const int64_t* isect_ids_sorted
  * written for every pixel (no zero-fill needed):
  *   out_img (H,W,3) out_depth (H,W) out_reg (H,W) out_texture (H,W,C) out_normal (H,W,3)
  *   final_Ts (H,W) final_idx (H,W) int32 depth_idx (H,W) int32 out_reg_s (H,W,3).
- * workspace: gstex_texture_forward_workspace_bytes(n) (per-view packed splat records). */
+ * workspace: gstex_texture_workspace_bytes(n) (per-view packed splat records).
+ *
+ * pair_stream (optional, may be NULL): a device buffer of pair_stream_bytes in which the forward records
+ * one 32-byte item per contributing (pixel, splat) pair, so that gstex_texture_backward can run its
+ * lane-dense stream kernel instead of re-walking the tile lists (the reference has no counterpart: it
+ * always recomputes, texture.cu:455-759).  Size it with gstex_pair_stream_bytes(H, W, block_width,
+ * max_pairs); if the pool is too small the forward flags an overflow inside the buffer and the backward
+ * transparently recomputes -- results never depend on the pool.  Recording is used when
+ * gstex_pair_stream_supported(channels, n, settings) is non-zero (<= 3 channels, no uv gradients). */
 size_t gstex_texture_workspace_bytes(int n);
+size_t gstex_pair_stream_bytes(int img_height, int img_width, int block_width, long long max_pairs);
+int gstex_pair_stream_supported(int channels, int n, int settings);
 int gstex_texture_forward(int img_height, int img_width, int block_width, int channels, int n, int num_intersects,
                           const int32_t* texture_dims, const int32_t* gaussian_ids_sorted, const int32_t* tile_bins,
                           const float* colors, const float* opacities, const float* means, const float* scales,
@@ -117,12 +127,21 @@ int gstex_texture_forward(int img_height, int img_width, int block_width, int ch
                           float fy, float cx, float cy, int settings, const float* background, float* out_img,
                           float* out_depth, float* out_reg, float* out_texture, float* out_normal, float* final_Ts,
                           int32_t* final_idx, int32_t* depth_idx, float* out_reg_s, void* workspace,
-                          size_t workspace_bytes, void* stream);
+                          size_t workspace_bytes, void* pair_stream, size_t pair_stream_bytes, void* stream);
 
 /* ref: cuda/csrc/texture.cu:903-1053 texture_backward_tensor -> kernel :331-760.
  * The nine gradient outputs (shapes of the inputs they belong to) must be ZERO-FILLED by the caller
  * (the reference allocates them with torch::zeros); gradients are accumulated into them.
- * `workspace` may be the one the forward of the same view filled (records_valid != 0 skips re-packing). */
+ * `workspace` may be the one the forward of the same view filled (records_valid != 0 skips re-packing).
+ * `pair_stream`: the buffer the forward of the same view recorded into, or NULL to recompute.
+ * `grad_scratch` (gstex_grad_scratch_bytes(n, num_texels) bytes, 16-byte aligned; needed by the stream path,
+ * may be NULL otherwise): padded accumulators the stream kernel reduces into with 16-byte vector atomics before
+ * an unpack kernel writes the reference's gradient tensors.  num_texels = rows of `texture`.
+ * zero_fill != 0: the nine gradient buffers are uninitialised on entry and the library defines every element
+ * (memsets what a kernel does not overwrite); zero_fill == 0: they are zero-filled by the caller.  With the
+ * stream path the colors/opacity/means/scales/quats/texture gradients are overwritten, not accumulated into
+ * (on the zero-filled buffers the contract asks for, that is the same thing). */
+size_t gstex_grad_scratch_bytes(int n, long long num_texels);
 int gstex_texture_backward(int img_height, int img_width, int block_width, int channels, int n, int num_intersects,
                            const int32_t* texture_dims, const int32_t* gaussian_ids_sorted, const int32_t* tile_bins,
                            const float* colors, const float* opacities, const float* means, const float* scales,
@@ -135,7 +154,8 @@ int gstex_texture_backward(int img_height, int img_width, int block_width, int c
                            const float* v_output_normal, float* v_colors, float* v_opacity, float* v_means,
                            float* v_scales, float* v_quats, float* v_uv0, float* v_umap, float* v_vmap,
                            float* v_texture, void* workspace, size_t workspace_bytes, int records_valid,
-                           void* stream);
+                           void* pair_stream, size_t pair_stream_bytes, void* grad_scratch, size_t grad_scratch_size,
+                           long long num_texels, int zero_fill, void* stream);
 
 #ifdef __cplusplus
 }

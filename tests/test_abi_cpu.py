@@ -30,7 +30,7 @@ def test_library_builds_and_exports_header_symbols():
         assert hasattr(lib, name), f"{name} declared in include/gstex_b200.h but not exported"
     assert sorted(_lib.EXPORTED_SYMBOLS) == declared
     lib.gstex_abi_version.restype = ctypes.c_int
-    assert lib.gstex_abi_version() == 1
+    assert lib.gstex_abi_version() == 2
     lib.gstex_error_string.restype = ctypes.c_char_p
     assert b"bad argument" in lib.gstex_error_string(-1)
     # size queries are pure host code

@@ -31,6 +31,19 @@ def _id(c):
     return f"{c['name']}-n{c['n']}-{c['width']}x{c['height']}-s{c['settings']}-C{c['C']}-T{c['texels']}"
 
 
+@pytest.fixture(params=["stream", "recompute", "overflow"], autouse=True)
+def backward_path(request):
+    """Every test of this file runs three times: with the forward recording the pair stream (stream backward),
+    with recording off (recompute backward), and with a pool so small that it overflows (device-side fallback)."""
+    from gstex_b200.texture import PairStreamPolicy
+
+    old = (PairStreamPolicy.enabled, PairStreamPolicy.max_bytes)
+    PairStreamPolicy.enabled = request.param != "recompute"
+    PairStreamPolicy.max_bytes = 40000 if request.param == "overflow" else None
+    yield request.param
+    PairStreamPolicy.enabled, PairStreamPolicy.max_bytes = old
+
+
 def run_ours(s, v=None, block_width=16):
     """The reference's call sequence (example.py:145-184 / NS/models/gstex.py:1075-1170) on our package."""
     import gstex_b200 as G
@@ -166,3 +179,25 @@ def test_errors_are_loud():
         G.texture_gaussians(*args, 32, 0, sd["background"])  # block_width > 16
     with pytest.raises(NotImplementedError):
         G.texture_gaussians(*args, 16, 1 << 16, sd["background"])  # viewer visualisation bit
+
+
+def test_pair_stream_is_recorded_and_overflow_is_flagged(backward_path):
+    """The stream backward must really be the path taken when recording is on (and the fallback when the pool is
+    too small): read the stream header the forward left behind."""
+    from gstex_b200.synthetic import make_scene, make_upstream_grads
+    from gstex_b200.texture import PairStreamPolicy
+
+    s = make_scene("cfg2", n=6000, width=160, height=160, texels=60000, settings=(1 << 9) | (1 << 10))
+    key = (torch.cuda.current_device(), 160, 160, 16)
+    PairStreamPolicy._state.pop(key, None)
+    run_ours(s, make_upstream_grads(s))
+    torch.cuda.synchronize()
+    if backward_path == "recompute":
+        assert key not in PairStreamPolicy._state
+        return
+    PairStreamPolicy.max_pairs(torch.device("cuda", key[0]), 160, 160, 16)  # consumes the pending header read-back
+    used, overflow = PairStreamPolicy._state[key]["last"]
+    if backward_path == "stream":
+        assert overflow == 0 and used > 0
+    else:
+        assert overflow == 1
