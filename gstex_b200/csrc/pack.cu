@@ -20,6 +20,7 @@ struct PackParams {
     SplatRec* recs;
     SplatRecBwd* recs_bwd;
     float4* boxes;
+    uint32_t* counters;
 };
 
 // Support box.  alpha = opac*exp(-sigma) >= 1/255  <=>  sigma <= smax = ln(255*opac), sigma = (u^2+v^2)/2 in
@@ -71,6 +72,7 @@ __device__ __forceinline__ float4 support_box(const double a[3], const double b[
 __global__ void __launch_bounds__(kThreads1D) pack_records_kernel(const PackParams p) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= p.n) return;
+    if (i == 0) p.counters[0] = 0u;  // unit cursor of the forward kernel that follows on the stream
     const float mx = p.means[3 * i], my = p.means[3 * i + 1], mz = p.means[3 * i + 2];
     const float4 qt = reinterpret_cast<const float4*>(p.quats)[i];
     const float w = qt.x, x = qt.y, y = qt.z, z = qt.w;
@@ -134,6 +136,7 @@ int launch_pack_records(int n, const int32_t* texture_dims, const float* colors,
     p.glob_scale = glob_scale; p.fx = fx; p.fy = fy; p.cx = cx; p.cy = cy;
     p.use_blur = (settings & GSTEX_SET_BLUR) ? 1 : 0;
     p.recs = ws_recs(workspace); p.recs_bwd = ws_recs_bwd(workspace, n); p.boxes = ws_boxes(workspace, n);
+    p.counters = ws_counters(workspace);
     pack_records_kernel<<<div_up(n, kThreads1D), kThreads1D, 0, st>>>(p);
     GSTEX_LAUNCH_CHECK();
     return GSTEX_OK;

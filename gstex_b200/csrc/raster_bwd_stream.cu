@@ -67,7 +67,9 @@ __global__ void __launch_bounds__(kStreamWarps * 32, 2) texture_backward_stream_
         const int tile_x = tile_id % g.tiles_x, tile_y = tile_id / g.tiles_x;
         __syncwarp();
         {  // this lane's own pixel -> table column `lane`
-            const Pixel pix = make_pixel_at(sm.cam, g, tile_x, tile_y, w * 32 + lane);
+            int lx, ly;
+            unit_pixel_xy(g, w, lane, lx, ly);  // the forward's lane -> pixel mapping
+            const Pixel pix = make_pixel_xy(sm.cam, g, tile_x, tile_y, lx, ly);
             const int id = pix.pix_id;
             tab[F_RAYX][lane] = pix.ray.x; tab[F_RAYY][lane] = pix.ray.y; tab[F_RAYZ][lane] = pix.ray.z;
             tab[F_PX][lane] = pix.px; tab[F_PY][lane] = pix.py; tab[F_VDEPTH][lane] = pix.view_depth;

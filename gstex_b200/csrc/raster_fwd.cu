@@ -1,18 +1,25 @@
-// raster_fwd.cu -- stage (c): per-tile textured forward compositing.
+// raster_fwd.cu -- stage (c): textured forward compositing.
 // Replaces texture_forward (gstex_cuda/cuda/csrc/texture.cu:11-329, wrapper :762-901).  sm_100a.
 //
 // Differences in HOW (not WHAT) from the reference kernel:
 //   * per-splat invariants (rotation axes, inverse-scale squares, ray/plane numerator, projected mean) come
 //     from a 128-byte packed record computed once per (view, splat) (pack.cu) instead of once per pixel;
-//   * warp-specialised: one producer warp gathers the tile's records by sorted id with TMA bulk copies
-//     (cp.async.bulk -> UBLKCP, 128 B each) into an 8-stage shared-memory ring guarded by full/empty
-//     mbarriers; the eight pixel warps consume stages independently -- no block-wide barrier per batch;
-//   * per stage the producer also tests each record's conservative support box against the pixel rows of
-//     every warp and hands each warp a 32-bit "worth evaluating" mask, so a warp never touches splats that
-//     cannot reach alpha >= 1/255 on its rows (exact: see pack.cu and the `danger` fallback below);
+//   * warp-autonomous units: the work item is one warp's 32 pixels of a tile (an 8x4 block for 16x16 tiles),
+//     handed out by a persistent grid through an atomic cursor.  A warp walks its tile's sorted list on its own:
+//     32 list entries at a time it tests the conservative support boxes (pack.cu) against its 8x4 block,
+//     compacts the survivors into a small queue, and pulls their 128-byte records into its private
+//     double-buffered shared-memory stage with TMA bulk copies (cp.async.bulk -> UBLKCP) completing on an
+//     mbarrier, one batch ahead of the batch being composited.  Warps never wait for each other (the reference
+//     and our earlier ring pipeline synchronise the 8 warps of a tile on every batch), a warp whose pixels are
+//     all finished just takes the next unit;
+//   * culling is exact: a culled pair has alpha < 1/255 (skipped by the reference too, texture.cu:213); only a
+//     pixel whose transmittance sits in (1e-4, 1e-4/(1-1/255)] can be terminated by such a pair (next_T <= 1e-4
+//     is tested before `skip`, texture.cu:216-221), and as soon as a warp sees one it drops its queue and
+//     re-walks the list from that entry with culling off;
 //   * the bilinear index/weight computation is done once per pair, not once per channel; texture
 //     accumulators live in registers (channel count is a template bound), not in a float[64] local array;
-//   * a warp stops as soon as all its 32 pixels are done (ballot), the producer when all warps are.
+//   * REC kernels append one 32-byte item per contributing pair to the pair stream (pair_stream.cuh) that the
+//     stream backward consumes.
 #include <cstddef>
 
 #include "pair_stream.cuh"
@@ -33,132 +40,144 @@ struct FwdParams {
     int settings;
     float *out_img, *out_depth, *out_reg, *out_texture, *out_normal, *final_Ts, *out_reg_s;
     int32_t *final_idx, *depth_idx;
+    uint32_t* unit_cursor;  // zeroed before the launch
+    int units_per_tile, num_units;
     StreamView sv;  // pair stream (REC kernels only)
 };
 
+constexpr int kFwdWarps = 4;    // warps per CTA; they share nothing but the camera
+constexpr int kBatch = 32;      // records per stage = one TMA bulk copy per lane
+constexpr int kQueue = 128;     // survivor ring: current batch + prefetched batch + one culling round
+
+struct FwdWarpShared {
+    SplatRec rec[2][kBatch];  // 8 KB
+    int q_gid[kQueue];
+    int q_idx[kQueue];
+    uint64_t bar[2];
+};
+
 struct FwdShared {
-    SplatRec recs[kStages][kStageRecs];  // 32 KB
-    uint64_t full[kStages];
-    uint64_t empty[kStages];
-    unsigned bits[kStages][8];  // per stage, per pixel warp: records worth evaluating
-    int ids[kStages][kStageRecs];  // splat ids of the stage (recorded into the pair stream)
+    FwdWarpShared w[kFwdWarps];
     Camera cam;
-    int warps_done;
-    volatile int stop_at;
 };
 
 template <int CMAX, bool REC>
-__global__ void __launch_bounds__(kMaxTileThreads + 32, REC ? 2 : 3) texture_forward_kernel(const FwdParams p) {
+__global__ void __launch_bounds__(kFwdWarps * 32, REC ? 4 : 5) texture_forward_kernel(const FwdParams p) {
     __shared__ __align__(128) FwdShared sm;
     const RasterGeom g = p.g;
-    const int n_pix_warps = g.threads >> 5;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const bool is_producer = warp == n_pix_warps;
+    FwdWarpShared& ws = sm.w[warp];
     load_camera(sm.cam, p.viewmat, p.c2w, p.fx, p.fy, p.cx, p.cy);
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < kStages; ++s) {
-            mbar_init(&sm.full[s], 1);
-            mbar_init(&sm.empty[s], n_pix_warps);
-        }
-        sm.warps_done = 0;
-        sm.stop_at = 0x7fffffff;
+    if (lane == 0) {
+        mbar_init(&ws.bar[0], 1);
+        mbar_init(&ws.bar[1], 1);
         mbar_fence_init();
     }
     __syncthreads();
-    const int tile_id = blockIdx.y * g.tiles_x + blockIdx.x;
-    const int2 range = p.tile_bins[tile_id];
-    const int n_stages = (range.y - range.x + kStageRecs - 1) / kStageRecs;
-
-    if (is_producer) {
-        // ===================== producer warp: gather records, build per-warp masks =====================
-        const float tx0 = (float)(blockIdx.x * g.bw) + 0.5f, tx1 = (float)(blockIdx.x * g.bw + g.bw - 1) + 0.5f;
-        const float ty = (float)(blockIdx.y * g.bw) + 0.5f;
-        // software pipeline: ids two stages ahead, support boxes one stage ahead of the stage being published
-        const float4 no_box = make_float4(1.f, 1.f, 0.f, 0.f);
-        int g_next = (range.x + lane < range.y) ? __ldg(p.ids + range.x + lane) : -1;
-        int g_next2 = (range.x + kStageRecs + lane < range.y) ? __ldg(p.ids + range.x + kStageRecs + lane) : -1;
-        float4 box_next = (g_next >= 0) ? __ldg(p.boxes + g_next) : no_box;
-        for (int n = 0; n < n_stages; ++n) {
-            const int s = n % kStages;
-            const int gid = g_next;
-            const float4 box = box_next;
-            g_next = g_next2;
-            const int nxt = range.x + (n + 2) * kStageRecs + lane;
-            g_next2 = (nxt < range.y) ? __ldg(p.ids + nxt) : -1;
-            box_next = (g_next >= 0) ? __ldg(p.boxes + g_next) : no_box;
-            if (n >= kStages) mbar_wait(&sm.empty[s], ((n / kStages) - 1) & 1);
-            if (*(volatile int*)&sm.warps_done >= n_pix_warps) {  // every pixel of the tile is finished
-                if (lane == 0) sm.stop_at = n;
-                break;
-            }
-            unsigned mine = 0, any = 0;
-            for (int w = 0; w < n_pix_warps; ++w) {
-                int r0, r1;
-                warp_rows(w, g.bw, r0, r1);
-                const bool hit = gid >= 0 && box_overlaps(box, tx0, tx1, ty + (float)r0, ty + (float)r1);
-                const unsigned b = __ballot_sync(0xffffffffu, hit);
-                if (lane == w) mine = b;
-                any |= b;
-            }
-            if (lane < n_pix_warps) sm.bits[s][lane] = mine;
-            if (REC) sm.ids[s][lane] = gid;
-            __syncwarp();
-            // every record of the stage is copied, also those no warp asked for: a warp in `danger` mode (below)
-            // evaluates all of them
-            (void)any;
-            const unsigned present = __ballot_sync(0xffffffffu, gid >= 0);
-            if (lane == 0) mbar_arrive_expect_tx(&sm.full[s], (uint32_t)__popc(present) * (uint32_t)sizeof(SplatRec));
-            if (gid >= 0) bulk_copy_g2s(&sm.recs[s][lane], p.recs + gid, sizeof(SplatRec), &sm.full[s]);
-        }
-        return;
-    }
-
-    // =============================== pixel warps: composite front to back ===============================
-    const Pixel pix = make_pixel(sm.cam, g, blockIdx.x, blockIdx.y);
     const bool use_blur = p.settings & GSTEX_SET_BLUR;
     const bool use_ndc = p.settings & GSTEX_SET_NDC_REG;
     const bool bilinear = !(p.settings & GSTEX_SET_NEAREST);
     const int C = p.C;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const float4 no_box = make_float4(1.f, 1.f, 0.f, 0.f);
+    const float bg0 = __ldg(p.background), bg1 = __ldg(p.background + 1), bg2 = __ldg(p.background + 2);
+    unsigned phase = 0;  // bit b: parity to wait for on bar[b]
+    bool rec_ok = REC && (*(volatile uint32_t*)&p.sv.hdr->overflow == 0u);
 
-    bool done = !pix.inside;
-    float T = 1.f;
-    int cur_idx = 0, pix_depth_index = -1;
-    float3 rgb = make_float3(0.f, 0.f, 0.f), nrm = make_float3(0.f, 0.f, 0.f), ts = make_float3(0.f, 0.f, 0.f);
-    float pix_depth = 0.f, pix_reg = 0.f;
-    float tex[CMAX];
-#pragma unroll
-    for (int k = 0; k < CMAX; ++k) tex[k] = 0.f;
-
-    // pair-stream cursor of this unit (REC only): current chunk, items in it, items in total
-    int cur_chunk = -1, fill = kChunkItems, cnt = 0;
-    bool rec = REC && (*(volatile uint32_t*)&p.sv.hdr->overflow == 0u);
-
-    bool warp_done = __all_sync(0xffffffffu, done);
-    if (warp_done && lane == 0) atomicAdd(&sm.warps_done, 1);
-
-    for (int n = 0; n < n_stages; ++n) {
-        const int s = n % kStages;
-        const uint32_t parity = (n / kStages) & 1;
-        bool stopped = false;
-        while (!mbar_try_wait(&sm.full[s], parity)) {
-            if (sm.stop_at <= n) { stopped = true; break; }
+    while (true) {
+        int unit = 0;
+        if (lane == 0) unit = (int)atomicAdd(p.unit_cursor, 1u);
+        unit = __shfl_sync(0xffffffffu, unit, 0);
+        if (unit >= p.num_units) break;
+        const int tile_id = unit / p.units_per_tile, w = unit - tile_id * p.units_per_tile;
+        const int tile_x = tile_id % g.tiles_x, tile_y = tile_id / g.tiles_x;
+        const int2 range = p.tile_bins[tile_id];
+        int lx, ly;
+        unit_pixel_xy(g, w, lane, lx, ly);
+        const Pixel pix = make_pixel_xy(sm.cam, g, tile_x, tile_y, lx, ly);
+        // pixel centres covered by this unit, for the support-box test
+        float X0, X1, Y0, Y1;
+        {
+            int x0, x1, y0, y1;
+            unit_rect(g, w, x0, x1, y0, y1);
+            X0 = (float)(tile_x * g.bw + x0) + 0.5f; X1 = (float)(tile_x * g.bw + x1) + 0.5f;
+            Y0 = (float)(tile_y * g.bw + y0) + 0.5f; Y1 = (float)(tile_y * g.bw + y1) + 0.5f;
         }
-        if (stopped) break;
-        if (!warp_done) {
-            const int batch_start = range.x + n * kStageRecs;
-            const int count = min(kStageRecs, range.y - batch_start);
-            unsigned remaining = (count >= 32) ? 0xffffffffu : ((1u << count) - 1u);  // records not yet passed
-            unsigned todo = sm.bits[s][warp] & remaining;
-            while (true) {
-                // A pixel whose transmittance sits in (1e-4, 1e-4/(1-1/255)] can be terminated even by a pair
-                // with alpha < 1/255 (next_T <= 1e-4 is tested before `skip`, texture.cu:216-221): then nothing
-                // may be culled for this warp.
-                if (__any_sync(0xffffffffu, !done && T <= 1.0041e-4f)) todo = remaining;
-                if (todo == 0) break;
-                const int i = __ffs(todo) - 1;
-                remaining &= ~((2u << i) - 1u);
-                todo &= remaining;
-                const SplatRec& r = sm.recs[s][i];
+
+        bool done = !pix.inside;
+        float T = 1.f;
+        int cur_idx = 0, pix_depth_index = -1;
+        float3 rgb = make_float3(0.f, 0.f, 0.f), nrm = make_float3(0.f, 0.f, 0.f), ts = make_float3(0.f, 0.f, 0.f);
+        float pix_depth = 0.f, pix_reg = 0.f;
+        float tex[CMAX];
+#pragma unroll
+        for (int k = 0; k < CMAX; ++k) tex[k] = 0.f;
+        // pair-stream cursor of this unit (REC only): current chunk, items in it, items in total
+        int cur_chunk = -1, fill = kChunkItems, cnt = 0;
+
+        // ---- list walk state: cursor = next list position to test; ring indices are monotonic
+        int cursor = range.x, last_pos = range.x - 1;
+        int q_head = 0, q_issue = 0, q_tail = 0;
+        bool nocull = false;
+        int gid_pf, gid_pf2;
+        float4 box_pf;
+        auto prime = [&]() {  // ids two rounds ahead, support boxes one round ahead of the round being tested
+            gid_pf = (cursor + lane < range.y) ? __ldg(p.ids + cursor + lane) : -1;
+            gid_pf2 = (cursor + 32 + lane < range.y) ? __ldg(p.ids + cursor + 32 + lane) : -1;
+            box_pf = (gid_pf >= 0) ? __ldg(p.boxes + gid_pf) : no_box;
+        };
+        // Test list entries until a batch of survivors is queued (or the list ends), then start the TMA copies
+        // of the next `kBatch` queued records into stage `buf`.  Returns the number of records in flight.
+        auto fill_and_issue = [&](int buf) -> int {
+            while (q_tail - q_issue < kBatch && cursor < range.y) {
+                const int gid = gid_pf;
+                const float4 box = box_pf;
+                const int pos = cursor + lane;
+                cursor += 32;
+                gid_pf = gid_pf2;
+                gid_pf2 = (cursor + 32 + lane < range.y) ? __ldg(p.ids + cursor + 32 + lane) : -1;
+                box_pf = (gid_pf >= 0) ? __ldg(p.boxes + gid_pf) : no_box;
+                const bool hit = gid >= 0 && (nocull || box_overlaps(box, X0, X1, Y0, Y1));
+                const unsigned m = __ballot_sync(0xffffffffu, hit);
+                if (hit) {
+                    const int slot = (q_tail + __popc(m & lt_mask)) & (kQueue - 1);
+                    ws.q_gid[slot] = gid;
+                    ws.q_idx[slot] = pos;
+                }
+                q_tail += __popc(m);
+            }
+            __syncwarp();
+            const int n_rec = min(q_tail - q_issue, kBatch);
+            if (n_rec > 0) {
+                if (lane == 0) mbar_arrive_expect_tx(&ws.bar[buf], (uint32_t)n_rec * (uint32_t)sizeof(SplatRec));
+                if (lane < n_rec)
+                    bulk_copy_g2s(&ws.rec[buf][lane], p.recs + ws.q_gid[(q_issue + lane) & (kQueue - 1)], sizeof(SplatRec),
+                                  &ws.bar[buf]);
+                q_issue += n_rec;
+            }
+            return n_rec;
+        };
+
+        bool unit_done = __all_sync(0xffffffffu, done);
+        int cur = 0, n_cur = 0;
+        if (!unit_done) {
+            prime();
+            n_cur = fill_and_issue(cur);
+        }
+        while (n_cur > 0) {
+            const int n_next = fill_and_issue(cur ^ 1);  // next batch in flight while this one is composited
+            mbar_wait(&ws.bar[cur], (phase >> cur) & 1u);
+            phase ^= 1u << cur;
+            bool flush = false;
+            for (int i = 0; i < n_cur; ++i) {
+                // A pixel whose transmittance sits in (1e-4, 1e-4/(1-1/255)] can be terminated even by a pair with
+                // alpha < 1/255: from here on nothing may be culled for this warp until that pixel is finished.
+                const bool danger = __any_sync(0xffffffffu, !done && T <= 1.0041e-4f);
+                if (danger && !nocull) { flush = true; break; }
+                if (!danger) nocull = false;
+                const SplatRec& r = ws.rec[cur][i];
+                const int q = (q_head + i) & (kQueue - 1);
+                const int idx = ws.q_idx[q];
                 const float4 r0 = r.q[0], r1 = r.q[1], r2 = r.q[2], r3 = r.q[3], r4 = r.q[4];
                 const PairEval e = eval_pair(pix, r0, r1, r2, r3, r4, use_blur);
                 const float next_T = T * (1.f - e.alpha);
@@ -175,17 +194,17 @@ __global__ void __launch_bounds__(kMaxTileThreads + 32, REC ? 2 : 3) texture_for
                         const float t_view = e.t * pix.view_depth;
                         const float u = clamp01(r6.w + (r6.x * e.delta.x + r6.y * e.delta.y + r6.z * e.delta.z));
                         const float v = clamp01(r7.w + (r7.x * e.delta.x + r7.y * e.delta.y + r7.z * e.delta.z));
-                        const TexQuery q =
+                        const TexQuery tq =
                             tex_query(__float_as_int(r4.z), __float_as_int(r4.w), __float_as_int(r5.w), u, v, bilinear);
-                        const float* t00 = p.texture + (size_t)q.b00 * C;
-                        const float* t01 = p.texture + (size_t)q.b01 * C;
-                        const float* t10 = p.texture + (size_t)q.b10 * C;
-                        const float* t11 = p.texture + (size_t)q.b11 * C;
+                        const float* t00 = p.texture + (size_t)tq.b00 * C;
+                        const float* t01 = p.texture + (size_t)tq.b01 * C;
+                        const float* t10 = p.texture + (size_t)tq.b10 * C;
+                        const float* t11 = p.texture + (size_t)tq.b11 * C;
 #pragma unroll
                         for (int k = 0; k < CMAX; ++k) {
                             if (k < C) {
-                                const float val = q.w00 * __ldg(t00 + k) + q.w01 * __ldg(t01 + k) +
-                                                  q.w10 * __ldg(t10 + k) + q.w11 * __ldg(t11 + k);
+                                const float val = tq.w00 * __ldg(t00 + k) + tq.w01 * __ldg(t01 + k) +
+                                                  tq.w10 * __ldg(t10 + k) + tq.w11 * __ldg(t11 + k);
                                 tex[k] += vis * val;
                                 if (REC && k < 3) h_val[k] = val;
                             }
@@ -193,19 +212,20 @@ __global__ void __launch_bounds__(kMaxTileThreads + 32, REC ? 2 : 3) texture_for
                         if (REC) { hit = true; h_T = T; h_u = u; h_v = v; }
                         if (T > 0.5f) {  // median depth, texture.cu:286-291
                             pix_depth = t_view;
-                            pix_depth_index = batch_start + i;
+                            pix_depth_index = idx;
                         }
                         float d = e.t;
                         if (use_ndc) d = (kFar * t_view - kFar * kNear) / ((kFar - kNear) * t_view);
                         pix_reg += vis * (d * d * ts.x + ts.z - 2.f * d * ts.y);  // distortion(), helpers.cuh:259-264
                         ts.x += vis; ts.y += vis * d; ts.z += vis * d * d;
                         T = next_T;
-                        cur_idx = batch_start + i;
+                        cur_idx = idx;
                     }
                 }
+                last_pos = idx;
                 if (REC) {  // append this splat's contributing pairs to the unit's stream, lane order
                     const unsigned hb = __ballot_sync(0xffffffffu, hit);
-                    if (hb != 0u && rec) {
+                    if (hb != 0u && rec_ok) {
                         const int nh = __popc(hb);
                         int new_chunk = cur_chunk;
                         if (fill + nh > kChunkItems) {
@@ -214,20 +234,20 @@ __global__ void __launch_bounds__(kMaxTileThreads + 32, REC ? 2 : 3) texture_for
                             c = __shfl_sync(0xffffffffu, c, 0);
                             if (c >= p.sv.num_chunks) {
                                 if (lane == 0) p.sv.hdr->overflow = 1u;
-                                rec = false;
+                                rec_ok = false;
                             } else {
                                 if (lane == 0) p.sv.chunk_prev[c] = cur_chunk;
                                 new_chunk = c;
                             }
                         }
-                        if (rec) {
+                        if (rec_ok) {
                             if (hit) {
-                                int pos = fill + __popc(hb & ((1u << lane) - 1u));
+                                int pos = fill + __popc(hb & lt_mask);
                                 int ch = cur_chunk;
                                 if (pos >= kChunkItems) { pos -= kChunkItems; ch = new_chunk; }
                                 float4* dst = reinterpret_cast<float4*>(p.sv.items + (size_t)ch * kChunkItems + pos);
-                                const uint32_t gl = ((uint32_t)sm.ids[s][i] << 5) | (uint32_t)lane;
-                                dst[0] = make_float4(__uint_as_float(gl), __int_as_float(batch_start + i), h_T, h_u);
+                                const uint32_t gl = ((uint32_t)ws.q_gid[q] << 5) | (uint32_t)lane;
+                                dst[0] = make_float4(__uint_as_float(gl), __int_as_float(idx), h_T, h_u);
                                 dst[1] = make_float4(h_v, h_val[0], h_val[1], h_val[2]);
                             }
                             fill += nh;
@@ -236,38 +256,50 @@ __global__ void __launch_bounds__(kMaxTileThreads + 32, REC ? 2 : 3) texture_for
                         }
                     }
                 }
-                if (__all_sync(0xffffffffu, done)) {
-                    warp_done = true;
-                    if (lane == 0) atomicAdd(&sm.warps_done, 1);
-                    break;
-                }
+                if (__all_sync(0xffffffffu, done)) { unit_done = true; break; }
             }
+            __syncwarp();
+            if (unit_done || flush) {
+                if (n_next > 0) {  // drain the copies in flight before their stage and barrier are reused
+                    mbar_wait(&ws.bar[cur ^ 1], (phase >> (cur ^ 1)) & 1u);
+                    phase ^= 1u << (cur ^ 1);
+                }
+                if (unit_done) break;
+                // re-walk from the entry after the last composited one, with culling off
+                nocull = true;
+                cursor = last_pos + 1;
+                q_head = q_issue = q_tail = 0;
+                prime();
+                n_cur = fill_and_issue(cur);
+                continue;
+            }
+            q_head += n_cur;
+            n_cur = n_next;
+            cur ^= 1;
+        }
+
+        if (REC) {
+            const int unit0 = tile_id * kUnitsPerTile;
+            if (lane == 0) p.sv.units[unit0 + w] = make_int2(cur_chunk, rec_ok ? cnt : 0);
+            if (w == 0 && lane >= p.units_per_tile && lane < kUnitsPerTile) p.sv.units[unit0 + lane] = make_int2(-1, 0);
+        }
+        if (pix.inside) {
+            const int id = pix.pix_id;
+            p.final_Ts[id] = T;
+            p.final_idx[id] = cur_idx;
+            p.depth_idx[id] = pix_depth_index;
+            p.out_img[3 * id + 0] = rgb.x + T * bg0;
+            p.out_img[3 * id + 1] = rgb.y + T * bg1;
+            p.out_img[3 * id + 2] = rgb.z + T * bg2;
+            p.out_normal[3 * id + 0] = nrm.x; p.out_normal[3 * id + 1] = nrm.y; p.out_normal[3 * id + 2] = nrm.z;
+            p.out_depth[id] = pix_depth;
+            p.out_reg[id] = pix_reg;
+            p.out_reg_s[3 * id + 0] = ts.x; p.out_reg_s[3 * id + 1] = ts.y; p.out_reg_s[3 * id + 2] = ts.z;
+#pragma unroll
+            for (int k = 0; k < CMAX; ++k)
+                if (k < C) p.out_texture[(size_t)C * id + k] = tex[k];
         }
         __syncwarp();
-        if (lane == 0) mbar_arrive(&sm.empty[s]);
-    }
-
-    if (REC) {
-        const int unit0 = tile_id * kUnitsPerTile;
-        if (lane == 0) p.sv.units[unit0 + warp] = make_int2(cur_chunk, rec ? cnt : 0);
-        if (warp == 0 && lane >= n_pix_warps && lane < kUnitsPerTile) p.sv.units[unit0 + lane] = make_int2(-1, 0);
-    }
-    if (pix.inside) {
-        const int id = pix.pix_id;
-        p.final_Ts[id] = T;
-        p.final_idx[id] = cur_idx;
-        p.depth_idx[id] = pix_depth_index;
-        const float bg0 = __ldg(p.background), bg1 = __ldg(p.background + 1), bg2 = __ldg(p.background + 2);
-        p.out_img[3 * id + 0] = rgb.x + T * bg0;
-        p.out_img[3 * id + 1] = rgb.y + T * bg1;
-        p.out_img[3 * id + 2] = rgb.z + T * bg2;
-        p.out_normal[3 * id + 0] = nrm.x; p.out_normal[3 * id + 1] = nrm.y; p.out_normal[3 * id + 2] = nrm.z;
-        p.out_depth[id] = pix_depth;
-        p.out_reg[id] = pix_reg;
-        p.out_reg_s[3 * id + 0] = ts.x; p.out_reg_s[3 * id + 1] = ts.y; p.out_reg_s[3 * id + 2] = ts.z;
-#pragma unroll
-        for (int k = 0; k < CMAX; ++k)
-            if (k < C) p.out_texture[(size_t)C * id + k] = tex[k];
     }
 }
 
@@ -307,15 +339,18 @@ extern "C" int gstex_texture_forward(int img_height, int img_width, int block_wi
     if (!tile_bins || !viewmat || !c2w || !background || !out_img || !out_depth || !out_reg || !out_texture ||
         !out_normal || !final_Ts || !final_idx || !depth_idx || !out_reg_s)
         return GSTEX_E_BADARG;
+    if (!workspace) return GSTEX_E_BADARG;
     if (n > 0 && (!texture_dims || !colors || !opacities || !means || !scales || !quats || !uv0 || !umap || !vmap ||
-                  !texture || !workspace))
+                  !texture))
         return GSTEX_E_BADARG;
     if (num_intersects > 0 && !gaussian_ids_sorted) return GSTEX_E_BADARG;
-    if (n > 0 && workspace_bytes < ws_bytes(n)) return GSTEX_E_WORKSPACE;
+    if (workspace_bytes < ws_bytes(n)) return GSTEX_E_WORKSPACE;
     if (n > 0) {
         const int rc = launch_pack_records(n, texture_dims, colors, opacities, means, scales, glob_scale, quats, uv0, umap,
                                            vmap, viewmat, c2w, fx, fy, cx, cy, settings, workspace, st);
         if (rc != GSTEX_OK) return rc;
+    } else {  // the pack kernel zeroes the unit cursor; without splats nobody did
+        GSTEX_CUDA_TRY(cudaMemsetAsync(ws_counters(workspace), 0, sizeof(uint32_t), st));
     }
     FwdParams p;
     p.g = make_raster_geom(img_height, img_width, block_width);
@@ -328,8 +363,13 @@ extern "C" int gstex_texture_forward(int img_height, int img_width, int block_wi
     p.out_img = out_img; p.out_depth = out_depth; p.out_reg = out_reg; p.out_texture = out_texture;
     p.out_normal = out_normal; p.final_Ts = final_Ts; p.out_reg_s = out_reg_s; p.final_idx = final_idx;
     p.depth_idx = depth_idx;
-    const dim3 grid(p.g.tiles_x, p.g.tiles_y);
-    const int threads = p.g.threads + 32;  // + the producer warp
+    p.unit_cursor = ws_counters(workspace);
+    p.units_per_tile = p.g.threads / 32;
+    p.num_units = p.g.tiles_x * p.g.tiles_y * p.units_per_tile;
+    // persistent grid: enough CTAs to fill every SM at the kernels' occupancy, never more than there are units
+    int grid = 148 * 5;
+    if (grid > (p.num_units + kFwdWarps - 1) / kFwdWarps) grid = (p.num_units + kFwdWarps - 1) / kFwdWarps;
+    const int threads = kFwdWarps * 32;
     // Record the pair stream for the stream backward when the caller gave a pool and the configuration is the
     // one that backward covers (<= 3 channels, no uv gradients); otherwise the backward recomputes.
     bool record = pair_stream != nullptr && gstex_pair_stream_supported(channels, n, settings) &&
