@@ -62,7 +62,7 @@ struct FwdShared {
 };
 
 template <int CMAX, bool REC>
-__global__ void __launch_bounds__(kFwdWarps * 32, REC ? 4 : 5) texture_forward_kernel(const FwdParams p) {
+__global__ void __launch_bounds__(kFwdWarps * 32, 5) texture_forward_kernel(const FwdParams p) {
     __shared__ __align__(128) FwdShared sm;
     const RasterGeom g = p.g;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
