@@ -27,6 +27,13 @@
 
 namespace gstex {
 
+#ifdef GSTEX_STATS
+__device__ unsigned long long g_fwd_stats[16];
+#define STAT_ADD(k, v) st_[k] += (unsigned long long)(v)
+#else
+#define STAT_ADD(k, v)
+#endif
+
 struct FwdParams {
     RasterGeom g;
     int C;
@@ -158,6 +165,11 @@ __global__ void __launch_bounds__(kFwdWarps * 32, 5) texture_forward_kernel(cons
             return n_rec;
         };
 
+#ifdef GSTEX_STATS
+        unsigned long long st_[16];
+        for (int k = 0; k < 16; ++k) st_[k] = 0;
+        STAT_ADD(9, 1);
+#endif
         bool unit_done = __all_sync(0xffffffffu, done);
         int cur = 0, n_cur = 0;
         if (!unit_done) {
@@ -181,6 +193,19 @@ __global__ void __launch_bounds__(kFwdWarps * 32, 5) texture_forward_kernel(cons
                 const float4 r0 = r.q[0], r1 = r.q[1], r2 = r.q[2], r3 = r.q[3], r4 = r.q[4];
                 const PairEval e = eval_pair(pix, r0, r1, r2, r3, r4, use_blur);
                 const float next_T = T * (1.f - e.alpha);
+#ifdef GSTEX_STATS
+                {
+                    const unsigned live = __ballot_sync(0xffffffffu, !done);
+                    const unsigned pot = __ballot_sync(0xffffffffu, !e.skip);
+                    const float4 bx = __ldg(p.boxes + ws.q_gid[q]);
+                    const bool inbox = pix.px >= bx.x && pix.px <= bx.z && pix.py >= bx.y && pix.py <= bx.w;
+                    const unsigned inb = __ballot_sync(0xffffffffu, inbox);
+                    STAT_ADD(0, 1); STAT_ADD(1, __popc(live)); STAT_ADD(2, __popc(pot)); STAT_ADD(3, __popc(pot & live));
+                    STAT_ADD(4, (pot & live) == 0u); STAT_ADD(6, pot == 0u); STAT_ADD(7, __popc(inb & live));
+                    STAT_ADD(8, __popc(inb)); STAT_ADD(5, (inb & live) == 0u);
+                    STAT_ADD(10, nocull);
+                }
+#endif
                 bool hit = false;
                 float h_T = 0.f, h_u = 0.f, h_v = 0.f, h_val[3] = {0.f, 0.f, 0.f};
                 if (!done) {
@@ -278,6 +303,10 @@ __global__ void __launch_bounds__(kFwdWarps * 32, 5) texture_forward_kernel(cons
             cur ^= 1;
         }
 
+#ifdef GSTEX_STATS
+        if (lane == 0)
+            for (int k = 0; k < 16; ++k) if (st_[k]) atomicAdd(&g_fwd_stats[k], st_[k]);
+#endif
         if (REC) {
             const int unit0 = tile_id * kUnitsPerTile;
             if (lane == 0) p.sv.units[unit0 + w] = make_int2(cur_chunk, rec_ok ? cnt : 0);
@@ -306,6 +335,15 @@ __global__ void __launch_bounds__(kFwdWarps * 32, 5) texture_forward_kernel(cons
 }  // namespace gstex
 
 using namespace gstex;
+
+#ifdef GSTEX_STATS
+extern "C" int gstex_debug_fwd_stats(unsigned long long* out, int reset) {
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out, g_fwd_stats, sizeof(unsigned long long) * 16);
+    if (reset) { unsigned long long z[16] = {0}; cudaMemcpyToSymbol(g_fwd_stats, z, sizeof(z)); }
+    return 0;
+}
+#endif
 
 extern "C" int gstex_pair_stream_supported(int channels, int n, int settings) {
     return channels >= 1 && channels <= 3 && n > 0 && n < (1 << 27) && !(settings & GSTEX_SET_UV_GRAD);

@@ -32,3 +32,77 @@ def allreduce_gradients(grads: Iterable[Optional[torch.Tensor]], world: int, gro
         if g is None:
             raise ValueError("allreduce_gradients: a gradient is None on this rank")
         dist.all_reduce(g, op=dist.ReduceOp.SUM, group=group)
+
+
+class HostViewFeeder:
+    """Feeds per-view HOST inputs (camera matrices, upstream-gradient images, ... in pinned memory) to the
+    device one view ahead of the view being rendered, and takes per-view results back to pinned host
+    buffers behind the compute: host->device copies run on their own stream, device->host copies on a
+    second one, both ordered against the compute stream with events only (no host synchronisation until
+    `finish()`).  The reference has nothing comparable: nerfstudio moves one camera + one image per step with
+    blocking `.to(device)` calls (nerfstudio/data/datamanagers/full_images_datamanager.py).
+
+        feeder = HostViewFeeder(device)
+        feeder.prefetch(host_inputs[0])
+        for i in range(V):
+            dev_inputs = feeder.take()                  # compute stream now waits for view i's copies
+            if i + 1 < V: feeder.prefetch(host_inputs[i + 1])
+            outs = render(dev_inputs)
+            feeder.send_back(outs[0].detach(), host_out[i])
+        feeder.finish()                                 # host may read host_out[*]
+    """
+
+    def __init__(self, device):
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("HostViewFeeder needs a CUDA device (there is no CPU path)")
+        self.h2d = torch.cuda.Stream(self.device)
+        self.d2h = torch.cuda.Stream(self.device)
+        self._pending = None
+
+    @staticmethod
+    def _map(obj, fn):
+        if isinstance(obj, torch.Tensor):
+            return fn(obj)
+        if isinstance(obj, dict):
+            return {k: HostViewFeeder._map(v, fn) for k, v in obj.items()}
+        if isinstance(obj, (list, tuple)):
+            return type(obj)(HostViewFeeder._map(v, fn) for v in obj)
+        return obj
+
+    def prefetch(self, host_inputs):
+        """Start the host->device copies of one view's inputs (any nest of dict/list/tuple of pinned tensors)."""
+        if self._pending is not None:
+            raise RuntimeError("HostViewFeeder.prefetch: the previous view has not been taken")
+        with torch.cuda.stream(self.h2d):
+            dev = self._map(host_inputs, lambda t: t.to(self.device, non_blocking=True))
+            ev = torch.cuda.Event()
+            ev.record(self.h2d)
+        self._pending = (dev, ev)
+
+    def take(self):
+        """Device copies of the prefetched view; the current (compute) stream waits for them."""
+        if self._pending is None:
+            raise RuntimeError("HostViewFeeder.take: nothing was prefetched")
+        dev, ev = self._pending
+        self._pending = None
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(ev)
+        self._map(dev, lambda t: (t.record_stream(cur), t)[1])
+        return dev
+
+    def send_back(self, dev_tensor, host_tensor):
+        """Copy a result into a pinned host tensor behind the compute stream (asynchronous)."""
+        cur = torch.cuda.current_stream(self.device)
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        self.d2h.wait_event(ev)
+        dev_tensor.record_stream(self.d2h)
+        with torch.cuda.stream(self.d2h):
+            host_tensor.copy_(dev_tensor, non_blocking=True)
+
+    def finish(self):
+        """Block the host until every copy issued so far has landed."""
+        self.h2d.synchronize()
+        self.d2h.synchronize()
+        torch.cuda.current_stream(self.device).synchronize()
