@@ -7,11 +7,11 @@ C ABI declared in `include/gstex_b200.h` (no CPU path, no fallback).
 """
 from .get_aabb_2d import get_aabb_2d, get_num_tiles_hit_2d, project_bounds, project_points  # noqa: F401
 from .texture import texture_gaussians  # noqa: F401
-from .utils import (bin_and_sort_gaussians, compute_cumulative_intersects, get_tile_bin_edges,  # noqa: F401
+from .utils import (bin_and_sort_gaussians, bin_gaussians_to_tiles, compute_cumulative_intersects, get_tile_bin_edges,  # noqa: F401
                     map_gaussian_to_intersects, sort_isects)
 
 __all__ = [
     "project_points", "get_aabb_2d", "get_num_tiles_hit_2d", "project_bounds", "compute_cumulative_intersects",
-    "map_gaussian_to_intersects", "sort_isects", "get_tile_bin_edges", "bin_and_sort_gaussians",
+    "map_gaussian_to_intersects", "sort_isects", "get_tile_bin_edges", "bin_and_sort_gaussians", "bin_gaussians_to_tiles",
     "texture_gaussians",
 ]

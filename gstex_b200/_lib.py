@@ -32,6 +32,11 @@ _SIGNATURES = {
     "gstex_sort_workspace_bytes": (SZ, [I]),
     "gstex_sort_isects": (I, [I, P, P, P, P, I, P, SZ, P]),
     "gstex_get_tile_bin_edges": (I, [I, P, I, P, P]),
+    "gstex_tile_bucket_max_list": (I, []),
+    "gstex_tile_bucket_count": (I, [I, P, P, P, I, I, I, P, P, P, P, P]),
+    "gstex_tile_bucket_max_tiles": (I, []),
+    "gstex_tile_bucket_scratch_bytes": (SZ, [I]),
+    "gstex_tile_bucket_sort": (I, [I, I, I, P, P, P, P, I, I, I, P, P, P, P, P, P]),
     "gstex_texture_workspace_bytes": (SZ, [I]),
     "gstex_pair_stream_bytes": (SZ, [I, I, I, ctypes.c_longlong]),
     "gstex_pair_stream_supported": (I, [I, I, I]),
@@ -80,7 +85,8 @@ class _TimedLib:
         fn = getattr(self._cdll, name)
         if not name.startswith("gstex_") or name.endswith("_bytes") or name in ("gstex_abi_version", "gstex_error_string",
                                                                                "gstex_launch_count",
-                                                                               "gstex_pair_stream_supported"):
+                                                                               "gstex_pair_stream_supported",
+                                                                               "gstex_tile_bucket_max_list", "gstex_tile_bucket_max_tiles"):
             return fn
 
         def call(*args):

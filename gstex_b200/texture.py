@@ -15,7 +15,7 @@ from torch import Tensor
 from torch.autograd import Function
 
 from . import _lib
-from .utils import bin_and_sort_gaussians, compute_cumulative_intersects
+from .utils import bin_gaussians_to_tiles
 
 SUPPORTED_SETTINGS = (1 << 2) | (1 << 8) | (1 << 9) | (1 << 10)
 
@@ -177,15 +177,10 @@ class _TextureGaussians(Function):
         num_points = centers.size(0)
         tile_bounds = ((img_width + block_width - 1) // block_width, (img_height + block_width - 1) // block_width, 1)
         dev = centers.device
-        num_intersects, cum_tiles_hit = compute_cumulative_intersects(num_tiles_hit)
-        if num_intersects < 1:
-            # The reference leaves most outputs undefined here (texture.py:197-205, a latent NameError guarded
-            # by the model at NS/models/gstex.py:1127); we return a well-formed empty render instead.
-            gaussian_ids_sorted = torch.zeros((0,), dtype=torch.int32, device=dev)
-            tile_bins = torch.zeros((tile_bounds[0] * tile_bounds[1], 2), dtype=torch.int32, device=dev)
-        else:
-            (_, _, _, gaussian_ids_sorted, tile_bins) = bin_and_sort_gaussians(
-                num_points, num_intersects, centers, extents, depths, cum_tiles_hit, tile_bounds, block_width)
+        # The reference leaves most outputs undefined without intersections (texture.py:197-205, a latent
+        # NameError guarded by the model at NS/models/gstex.py:1127); we return a well-formed empty render.
+        num_intersects, gaussian_ids_sorted, tile_bins = bin_gaussians_to_tiles(
+            num_points, centers, extents, depths, num_tiles_hit, tile_bounds, block_width)
         outputs, ws, pairs = _raster_forward(texture_info, texture_dims, gaussian_ids_sorted, tile_bins, colors,
                                              opacity, means, scales, glob_scale, quats, uv0, umap, vmap, texture,
                                              viewmat, c2w, fx, fy, cx, cy, img_height, img_width, block_width,

@@ -117,3 +117,56 @@ def bin_and_sort_gaussians(num_points: int, num_intersects: int, centers: Tensor
     isect_ids_sorted, gaussian_ids_sorted = sort_isects(isect_ids, gaussian_ids, key_bits_for(tile_bounds))
     tile_bins = get_tile_bin_edges(num_intersects, isect_ids_sorted, tile_bounds)
     return isect_ids, gaussian_ids, isect_ids_sorted, gaussian_ids_sorted, tile_bins
+
+
+def bin_gaussians_to_tiles(num_points: int, centers: Tensor, extents: Tensor, depths: Tensor, num_tiles_hit: Tensor,
+                           tile_bounds, block_size: int):
+    """What `texture_gaussians` needs from `compute_cumulative_intersects` + `bin_and_sort_gaussians`
+    (ref: utils.py:40-59,106-162): `(num_intersects, gaussian_ids_sorted (I,) int32, tile_bins (tiles,2) int32)`,
+    bit-identical to them, through the tile-bucket path (csrc/tile_bucket.cu) -- per-tile counts, one scan, an
+    atomic-cursor emit and a per-tile shared-memory sort by (depth bits, splat id) -- instead of a radix sort of
+    the whole list.  One blocking read of two ints (`num_intersects`, longest tile list) replaces the
+    reference's `.item()` (utils.py:58).  A tile list longer than the shared-memory capacity sends the call
+    down the general path."""
+    centers, extents, depths = centers.contiguous(), extents.contiguous(), depths.contiguous()
+    nth = num_tiles_hit.contiguous().reshape(-1)
+    dev = _lib.require_cuda(centers, extents, depths, nth)
+    for t, nm in ((centers, "centers"), (extents, "extents"), (depths, "depths")):
+        _lib.require_dtype(t, torch.float32, nm)
+    num_tiles = int(tile_bounds[0]) * int(tile_bounds[1])
+    i32 = dict(dtype=torch.int32, device=dev)
+    if nth.numel() == 0:
+        return 0, torch.zeros((0,), **i32), torch.zeros((num_tiles, 2), **i32)
+    cum, total = cumsum_i32(nth)
+    lib = _lib.load()
+
+    def general(num_intersects):
+        if num_intersects < 1:
+            return num_intersects, torch.zeros((0,), **i32), torch.zeros((num_tiles, 2), **i32)
+        (_, _, _, ids_sorted, bins) = bin_and_sort_gaussians(num_points, num_intersects, centers, extents, depths, cum,
+                                                             tile_bounds, block_size)
+        return num_intersects, ids_sorted, bins
+
+    if num_tiles > lib.gstex_tile_bucket_max_tiles():
+        return general(int(total.item()))
+    block_counts = _workspace(lib.gstex_tile_bucket_scratch_bytes(num_tiles), dev)
+    small = torch.empty((num_tiles + 2,), **i32)  # tile_start | stats
+    tile_start, stats = small[:num_tiles], small[num_tiles:]
+    tile_bins = torch.empty((num_tiles, 2), **i32)
+    p, st = _lib.ptr, _lib.stream_ptr(dev)
+    with torch.cuda.device(dev):
+        rc = lib.gstex_tile_bucket_count(int(num_points), p(centers), p(extents), p(cum), int(tile_bounds[0]),
+                                         int(tile_bounds[1]), int(block_size), p(block_counts), p(tile_bins),
+                                         p(tile_start), p(stats), st)
+    _lib.check(rc, "gstex_tile_bucket_count")
+    num_intersects, max_list = stats.tolist()  # the one host sync of the binning stage
+    if num_intersects < 1 or max_list > lib.gstex_tile_bucket_max_list():
+        return general(num_intersects)
+    keys = torch.empty((num_intersects,), dtype=torch.int64, device=dev)
+    ids_sorted = torch.empty((num_intersects,), **i32)
+    with torch.cuda.device(dev):
+        rc = lib.gstex_tile_bucket_sort(int(num_points), int(num_intersects), int(max_list), p(centers), p(extents),
+                                        p(depths), p(cum), int(tile_bounds[0]), int(tile_bounds[1]), int(block_size),
+                                        p(block_counts), p(tile_start), p(tile_bins), p(keys), p(ids_sorted), st)
+    _lib.check(rc, "gstex_tile_bucket_sort")
+    return num_intersects, ids_sorted, tile_bins

@@ -99,6 +99,30 @@ int gstex_sort_isects(int num_intersects, const int64_t* isect_ids, const int32_
 int gstex_get_tile_bin_edges(int num_intersects, const int64_t* isect_ids_sorted, int num_tiles, int32_t* tile_bins,
                              void* stream);
 
+/* Fast path of stage (b) used by texture_gaussians (no counterpart in the reference, which always sorts the
+ * whole list, utils.py:106-162): tile-bucketed binning.  Results are bit-identical to
+ * map_gaussian_to_intersects -> gstex_sort_isects -> gstex_get_tile_bin_edges, but only
+ * gaussian_ids_sorted and tile_bins are produced.
+ *   gstex_tile_bucket_count: per-tile intersection counts (block_counts: gstex_tile_bucket_scratch_bytes(
+ *     num_tiles) of scratch, kept for the sort call), their exclusive scan -> tile_bins (num_tiles,2) with (0,0)
+ *     for empty tiles, tile_start (num_tiles int32), stats[0] = num_intersects, stats[1] = longest tile list.
+ *     GSTEX_E_UNSUPPORTED when tiles_x*tiles_y exceeds gstex_tile_bucket_max_tiles().
+ *   gstex_tile_bucket_sort: claims a slot per intersection in its tile's range (keys: num_intersects x 8 B
+ *     scratch) and sorts every tile's range by (depth bits, splat id) in shared memory.  max_list = stats[1]
+ *     read back by the host; returns GSTEX_E_UNSUPPORTED when it exceeds gstex_tile_bucket_max_list() (the
+ *     caller then takes the general path above).  Depths of emitted splats must be non-negative (they are:
+ *     splats with z <= 0.01 are clipped and emit nothing, get_aabb_2d.cu:25). */
+int gstex_tile_bucket_max_list(void);
+int gstex_tile_bucket_max_tiles(void);
+size_t gstex_tile_bucket_scratch_bytes(int num_tiles);
+int gstex_tile_bucket_count(int n, const float* centers, const float* extents, const int32_t* cum_tiles_hit,
+                            int tiles_x, int tiles_y, int block_width, int32_t* block_counts, int32_t* tile_bins,
+                            int32_t* tile_start, int32_t* stats, void* stream);
+int gstex_tile_bucket_sort(int n, int num_intersects, int max_list, const float* centers, const float* extents,
+                           const float* depths, const int32_t* cum_tiles_hit, int tiles_x, int tiles_y,
+                           int block_width, const int32_t* block_counts, const int32_t* tile_start,
+                           const int32_t* tile_bins, void* keys, int32_t* gaussian_ids_sorted, void* stream);
+
 /* ---- stages (c), (d): textured forward compositing and backward -------------------------------- */
 
 /* ref: cuda/csrc/texture.cu:762-901 texture_forward_tensor -> kernel :11-329.

@@ -165,3 +165,105 @@ def test_radix_sort_stable(n, bits):
     assert torch.equal(ks, ts)
     assert torch.equal(vs, vals[ti]), "payload order differs from a stable sort"
     assert torch.equal(keys, keys.clone()) and bool((ks[1:] >= ks[:-1]).all())
+
+
+def _general_and_fast(centers, extents, depths, nth, N, H, W, bw):
+    import gstex_b200 as G
+    from gstex_b200.utils import bin_gaussians_to_tiles
+
+    tb = ((W + bw - 1) // bw, (H + bw - 1) // bw, 1)
+    total, cum = G.compute_cumulative_intersects(nth)
+    I, ids_f, bins_f = bin_gaussians_to_tiles(N, centers, extents, depths, nth, tb, bw)
+    assert I == total
+    if total < 1:
+        assert ids_f.numel() == 0 and int(bins_f.abs().sum()) == 0
+        return None
+    _, _, isect_s, ids_g, bins_g = G.bin_and_sort_gaussians(N, total, centers, extents, depths, cum, tb, bw)
+    assert torch.equal(bins_f, bins_g), "tile_bins of the tile-bucket path differ from the general path"
+    assert torch.equal(ids_f, ids_g), "sorted ids of the tile-bucket path differ from the general path"
+    return isect_s, ids_g, bins_g
+
+
+@pytest.mark.parametrize("cfg", SCENES, ids=lambda c: c["name"])
+@pytest.mark.parametrize("behind", [False, True], ids=["plain", "clipped"])
+@pytest.mark.parametrize("bw", [16, 7, 2])
+def test_tile_bucket_path_matches_general(cfg, behind, bw):
+    """texture_gaussians' binning (csrc/tile_bucket.cu) == emit + stable radix sort + bin edges, bit for bit."""
+    import gstex_b200 as G
+
+    if bw == 2 and cfg["name"] != "cfg1":
+        pytest.skip("block width 2 only on the small scene (tile count)")
+    s = _scene(cfg, behind)
+    sd = _dev(s)
+    intr = (s["fx"], s["fy"], s["cx"], s["cy"])
+    H, W = s["H"], s["W"]
+    _, depths, centers, extents, nth = G.project_bounds(sd["means"], sd["scales"], 1, sd["quats"], sd["viewmat"], intr,
+                                                        H, W, bw)
+    r = _general_and_fast(centers, extents, depths, nth, s["N"], H, W, bw)
+    assert r is not None
+    if behind:
+        assert int((r[0] == 0).sum()) > 0, "scene should exercise the zero-key quirk"
+
+
+def test_tile_bucket_ties_long_lists_and_empty():
+    """Equal depths (ties resolved by splat index), every splat on every tile (long lists), no intersections."""
+    g = torch.Generator().manual_seed(5)
+    H, W, bw = 64, 96, 16
+    for n, ext, depth_vals in ((5000, 200.0, 3), (30000, 40.0, 2), (100, 0.0, 1)):
+        centers = (torch.rand(n, 2, generator=g) * torch.tensor([W, H])).cuda()
+        extents = torch.full((n, 2), ext).cuda()
+        depths = (torch.randint(0, depth_vals, (n,), generator=g).float() * 0.25 + 1.0).cuda()
+        import gstex_b200 as G
+
+        nth = G.get_num_tiles_hit_2d(centers, extents, H, W, bw)
+        if ext == 0.0:
+            nth = torch.zeros_like(nth)
+        r = _general_and_fast(centers, extents, depths, nth, n, H, W, bw)
+        if r is not None:
+            keys = r[0]
+            assert bool((keys[1:] >= keys[:-1]).all())
+
+
+def test_tile_bucket_falls_back_beyond_capacity():
+    """A tile list longer than the shared-memory capacity takes the general path (same results)."""
+    import gstex_b200 as G
+    from gstex_b200 import _lib
+
+    cap = _lib.load().gstex_tile_bucket_max_list()
+    n = cap + 1500
+    g = torch.Generator().manual_seed(9)
+    H, W, bw = 32, 32, 16
+    centers = (torch.rand(n, 2, generator=g) * 32).cuda()
+    extents = torch.full((n, 2), 64.0).cuda()
+    depths = (torch.rand(n, generator=g) + 1.0).cuda()
+    nth = G.get_num_tiles_hit_2d(centers, extents, H, W, bw)
+    assert int(nth.max()) == 4
+    assert _general_and_fast(centers, extents, depths, nth, n, H, W, bw) is not None
+
+
+def test_tile_bucket_full_size_properties():
+    """cfg5-sized scene (1M splats, 800x800): per-tile lists sorted by (depth, id), ranges tile the list."""
+    import gstex_b200 as G
+    from gstex_b200.synthetic import make_scene
+    from gstex_b200.utils import bin_gaussians_to_tiles
+
+    s = make_scene("cfg5", views=1)
+    sd = _dev(s)
+    intr = (s["fx"], s["fy"], s["cx"], s["cy"])
+    H, W, bw = s["H"], s["W"], 16
+    _, depths, centers, extents, nth = G.project_bounds(sd["means"], sd["scales"], 1, sd["quats"], sd["viewmats"][0],
+                                                        intr, H, W, bw)
+    tb = ((W + bw - 1) // bw, (H + bw - 1) // bw, 1)
+    I, ids, bins = bin_gaussians_to_tiles(s["N"], centers, extents, depths, nth, tb, bw)
+    assert I == int(nth.sum()) and ids.numel() == I
+    cnt = (bins[:, 1] - bins[:, 0]).long()
+    assert int(cnt.sum()) == I
+    ne = cnt > 0
+    starts = torch.cumsum(cnt, 0) - cnt
+    assert torch.equal(bins[ne, 0].long(), starts[ne])
+    tile_of = torch.repeat_interleave(torch.arange(bins.shape[0], device=ids.device), cnt)
+    key = (tile_of << 32) | depths.view(torch.int32)[ids.long()].long()
+    assert bool((key[1:] >= key[:-1]).all()), "list not sorted by (tile, depth)"
+    same = key[1:] == key[:-1]
+    assert bool((ids[1:][same] > ids[:-1][same]).all()), "ties must keep ascending splat index"
+    _general_and_fast(centers, extents, depths, nth, s["N"], H, W, bw)
