@@ -25,11 +25,12 @@
 
 namespace gstex {
 
-constexpr int kLsWarpsSmall = 8, kLsWarpsLarge = 16;  // threads per block for lists <= / > kLsSmallCap
-constexpr int kLsSmallCap = 2048;
-constexpr int kLsMaxSmem = 227 * 1024;
-constexpr int ls_fixed_smem(int warps) { return warps * 256 * 4 + 256; }
-constexpr int kLsMaxList = ((kLsMaxSmem - ls_fixed_smem(kLsWarpsLarge)) / 16) & ~511;
+// size classes of the per-tile sort: (warps per block, keys per thread); capacity = warps * 32 * keys
+constexpr int kLsSmallW = 8, kLsSmallK = 8;    // lists <= 2048
+constexpr int kLsLargeW = 16;                  // longer lists: K = 12 / 16 / 26
+constexpr int kLsSmallCap = kLsSmallW * 32 * kLsSmallK;
+constexpr int kLsMaxList = kLsLargeW * 32 * 26;  // 13312 keys = 104 KB of shared memory
+constexpr int ls_smem_bytes(int warps, int k) { return warps * 32 * k * 8 + warps * 256 * 4 + 256; }
 
 struct TileRect {
     int min_x, max_x, min_y, max_y;
@@ -164,11 +165,15 @@ tile_emit_kernel(int n, int chunk, const float2* __restrict__ centers, const flo
     }
 }
 
-// One block per tile whose list length lies in [n_lo, n_hi].  smem: bufA[cap] | bufB[cap] (64-bit keys) |
-// warp_hist[kLsWarps][256] | scan scratch.  Strategy: sort by the depth bits only (stable LSD, 4 passes minus the
-// ones whose digit is constant over the tile); that is already the final order unless two entries with EQUAL
-// depth bits arrived with descending splat ids (the emit cursor hands slots out in arbitrary order).  Such a
-// tile -- rare, depth ties are rare -- is sorted again from the original keys over the id bits first.
+// ---- per-tile sort ------------------------------------------------------------------------------------------
+// One block (W warps) per tile whose list length lies in [n_lo, n_hi], n_hi <= W*32*K.  Shared memory holds ONE
+// copy of the tile's 64-bit keys: in every pass each thread first takes its K keys into registers (warp w owns
+// a contiguous segment, lane l's j-th key is segment[j*32 + l], so (warp, j, lane) order == list order), the
+// block counts digits, scans, and only then scatters the registers back into the same array.
+// Strategy: sort by the depth bits only (stable LSD, 4 passes minus those whose digit is constant over the tile);
+// that is already the final order unless two entries with EQUAL depth bits arrived with descending splat ids
+// (the emit cursor hands slots out in arbitrary order) -- see the fix-up in the kernel.
+
 // Lanes of the warp holding the same 8-bit digit as this lane (invalid lanes: none).  Eight ballots instead of
 // MATCH.ANY: measured here, MATCH.ANY through the MIO pipe with 32 warps per SM left the kernel at 0.02
 // instructions per cycle per warp; VOTE is a few cycles.
@@ -183,42 +188,49 @@ __device__ __forceinline__ unsigned digit_peers(int d, bool valid) {
     return valid ? peers : 0u;
 }
 
-template <int kLsWarps>
-__device__ __forceinline__ unsigned long long* ls_radix_passes(unsigned long long* src, unsigned long long* dst,
-                                                               int (*warp_hist)[256], int* scan_tmp, int n,
-                                                               int seg_begin, int seg_end, int first_pass, int last_pass,
-                                                               int id_passes, int id_bits) {
+template <int W, int K>
+__device__ __forceinline__ void ls_radix_passes(unsigned long long* buf, int (*warp_hist)[256], int* scan_tmp, int n,
+                                                int seg_begin, int seg_end, int first_pass, int last_pass,
+                                                int id_passes, int id_bits) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned lt_mask = (1u << lane) - 1u;
+    __syncthreads();  // the caller's copy into buf is complete
     for (int pass = first_pass; pass < last_pass; ++pass) {
         const int shift = pass < id_passes ? 8 * pass : 32 + 8 * (pass - id_passes);
         const int bits = pass < id_passes ? min(8, id_bits - 8 * pass) : 8;
         const int mask = (1 << bits) - 1;
-        for (int j = tid; j < kLsWarps * 256; j += kLsWarps * 32) (&warp_hist[0][0])[j] = 0;
-        __syncthreads();  // also orders the previous pass's scatter (or the load) before this pass's reads
-        for (int base = seg_begin; base < seg_end; base += 64) {  // two rounds per trip: independent match chains
-            const int i0 = base + lane, i1 = base + 32 + lane;
-            const bool ok0 = i0 < seg_end, ok1 = i1 < seg_end;
-            const int d0 = ok0 ? (int)(src[i0] >> shift) & mask : 0;
-            const int d1 = ok1 ? (int)(src[i1] >> shift) & mask : 0;
-            const unsigned p0 = digit_peers(d0, ok0);
-            const unsigned p1 = digit_peers(d1, ok1);
-            if (ok0 && lane == __ffs(p0) - 1) warp_hist[warp][d0] += __popc(p0);
-            __syncwarp();
-            if (ok1 && lane == __ffs(p1) - 1) warp_hist[warp][d1] += __popc(p1);
-            __syncwarp();
+        unsigned long long key[K];
+        unsigned peers[K];
+#pragma unroll
+        for (int j = 0; j < K; ++j) {
+            const int i = seg_begin + j * 32 + lane;
+            key[j] = (i < seg_end) ? buf[i] : 0ull;
+        }
+        for (int j = tid; j < W * 256; j += W * 32) (&warp_hist[0][0])[j] = 0;
+        __syncthreads();  // every key is in a register; histograms are clear
+#pragma unroll
+        for (int j = 0; j < K; ++j) {
+            if (seg_begin + j * 32 < seg_end) {  // warp-uniform
+                const bool ok = seg_begin + j * 32 + lane < seg_end;
+                const int d = (int)(key[j] >> shift) & mask;
+                peers[j] = digit_peers(d, ok);
+                if (ok && lane == __ffs(peers[j]) - 1) warp_hist[warp][d] += __popc(peers[j]);
+                __syncwarp();
+            } else {
+                peers[j] = 0u;
+            }
         }
         __syncthreads();
         int total = 0;
         if (tid < 256) {
 #pragma unroll 8
-            for (int w = 0; w < kLsWarps; ++w) {  // thread d: exclusive prefix of digit d over the warps
+            for (int w = 0; w < W; ++w) {  // thread d: exclusive prefix of digit d over the warps
                 const int c = warp_hist[w][tid];
                 warp_hist[w][tid] = total;
                 total += c;
             }
         }
-        // a digit that holds every key: nothing to reorder in this pass
+        // a digit that holds every key: nothing to reorder in this pass (the keys in shared memory are untouched)
         if (__syncthreads_or(tid < 256 && total == n)) continue;
         if (tid < 256) {  // exclusive scan of the digit totals over the first 256 threads
             int v = total;
@@ -235,94 +247,79 @@ __device__ __forceinline__ unsigned long long* ls_radix_passes(unsigned long lon
                 if (w < warp) wprefix += scan_tmp[w];
             const int dbase = wprefix + v - total;
 #pragma unroll 8
-            for (int w = 0; w < kLsWarps; ++w) warp_hist[w][tid] += dbase;
+            for (int w = 0; w < W; ++w) warp_hist[w][tid] += dbase;
         }
         __syncthreads();
-        for (int base = seg_begin; base < seg_end; base += 64) {
-            const int i0 = base + lane, i1 = base + 32 + lane;
-            const bool ok0 = i0 < seg_end, ok1 = i1 < seg_end;
-            const unsigned long long k0 = ok0 ? src[i0] : 0ull, k1 = ok1 ? src[i1] : 0ull;
-            const int d0 = ok0 ? (int)(k0 >> shift) & mask : 0;
-            const int d1 = ok1 ? (int)(k1 >> shift) & mask : 0;
-            const unsigned p0 = digit_peers(d0, ok0);
-            const unsigned p1 = digit_peers(d1, ok1);
-            const int l0 = ok0 ? __ffs(p0) - 1 : lane, l1 = ok1 ? __ffs(p1) - 1 : lane;
-            int prev0 = 0, prev1 = 0;
-            if (ok0 && lane == l0) {
-                prev0 = warp_hist[warp][d0];
-                warp_hist[warp][d0] = prev0 + __popc(p0);
+#pragma unroll
+        for (int j = 0; j < K; ++j) {
+            if (seg_begin + j * 32 < seg_end) {
+                const unsigned p = peers[j];
+                const int d = (int)(key[j] >> shift) & mask;
+                const int leader = p ? __ffs(p) - 1 : lane;
+                int prev = 0;
+                if (p && lane == leader) {
+                    prev = warp_hist[warp][d];
+                    warp_hist[warp][d] = prev + __popc(p);
+                }
+                prev = __shfl_sync(0xffffffffu, prev, leader);
+                if (p) buf[prev + __popc(p & lt_mask)] = key[j];
+                __syncwarp();
             }
-            __syncwarp();
-            if (ok1 && lane == l1) {
-                prev1 = warp_hist[warp][d1];
-                warp_hist[warp][d1] = prev1 + __popc(p1);
-            }
-            prev0 = __shfl_sync(0xffffffffu, prev0, l0);
-            prev1 = __shfl_sync(0xffffffffu, prev1, l1);
-            if (ok0) dst[prev0 + __popc(p0 & lt_mask)] = k0;
-            if (ok1) dst[prev1 + __popc(p1 & lt_mask)] = k1;
-            __syncwarp();
         }
         __syncthreads();
-        unsigned long long* t = src; src = dst; dst = t;
     }
-    return src;
 }
 
-template <int kLsWarps>
-__global__ void __launch_bounds__(kLsWarps * 32)
+template <int W, int K>
+__global__ void __launch_bounds__(W * 32)
 tile_local_sort_kernel(const int2* __restrict__ tile_bins, const unsigned long long* __restrict__ keys,
-                       int32_t* __restrict__ ids_out, int id_bits, int cap, int n_lo, int n_hi) {
+                       int32_t* __restrict__ ids_out, int id_bits, int n_lo, int n_hi) {
+    constexpr int kThreads = W * 32, kCap = W * 32 * K;
     extern __shared__ __align__(16) unsigned char ls_smem[];
-    unsigned long long* buf_a = reinterpret_cast<unsigned long long*>(ls_smem);
-    unsigned long long* buf_b = buf_a + cap;
-    int (*warp_hist)[256] = reinterpret_cast<int (*)[256]>(buf_b + cap);
-    int* scan_tmp = reinterpret_cast<int*>(warp_hist + kLsWarps);
+    unsigned long long* buf = reinterpret_cast<unsigned long long*>(ls_smem);
+    int (*warp_hist)[256] = reinterpret_cast<int (*)[256]>(buf + kCap);
+    int* scan_tmp = reinterpret_cast<int*>(warp_hist + W);
 
     const int2 range = tile_bins[blockIdx.x];
     const int n = range.y - range.x;
-    if (n < n_lo || n > n_hi || n > cap) return;  // n > cap cannot happen: the host checks the longest list first
+    if (n < n_lo || n > n_hi || n > kCap) return;  // n > kCap cannot happen: the host picks K from the longest list
     const int tid = threadIdx.x;
     if (n == 1) {
         if (tid == 0) ids_out[range.x] = (int32_t)(unsigned)keys[range.x];
         return;
     }
-    // each warp owns a contiguous segment (a multiple of 32 keys), so (warp, round, lane) order == list order
     const int warp = tid >> 5;
-    const int seg = ((n + kLsWarps * 32 - 1) / (kLsWarps * 32)) * 32;
+    const int seg = ((n + kThreads - 1) / kThreads) * 32;  // <= K*32 keys per warp, spread over all warps
     const int seg_begin = min(warp * seg, n), seg_end = min(seg_begin + seg, n);
     const int id_passes = (id_bits + 7) / 8;
 
-    constexpr int kLsThreads = kLsWarps * 32;
-    for (int i = tid; i < n; i += kLsThreads) buf_a[i] = keys[range.x + i];
-    unsigned long long* src = ls_radix_passes<kLsWarps>(buf_a, buf_b, warp_hist, scan_tmp, n, seg_begin, seg_end, id_passes,
-                                              id_passes + 4, id_passes, id_bits);
+    for (int i = tid; i < n; i += kThreads) buf[i] = keys[range.x + i];
+    ls_radix_passes<W, K>(buf, warp_hist, scan_tmp, n, seg_begin, seg_end, id_passes, id_passes + 4, id_passes, id_bits);
     // after the last pass's barrier: equal depths with descending ids?  Isolated pairs (the usual case: two
     // splats of a tile with the same depth bits) are put right by a few odd-even exchange rounds, which only
     // ever swap equal-depth neighbours; anything longer is sorted again from the original keys, ids first.
     bool bad = false;
-    for (int i = tid; i + 1 < n; i += kLsThreads) bad |= src[i] > src[i + 1];
+    for (int i = tid; i + 1 < n; i += kThreads) bad |= buf[i] > buf[i + 1];
     if (__syncthreads_or(bad)) {
         bad = true;  // uniform from here on
         for (int round = 0; round < 4 && bad; ++round) {
             bool moved = false;
 #pragma unroll
             for (int parity = 0; parity < 2; ++parity) {
-                for (int i = 2 * tid + parity; i + 1 < n; i += 2 * kLsThreads) {
-                    const unsigned long long a = src[i], b = src[i + 1];
-                    if (a > b) { src[i] = b; src[i + 1] = a; moved = true; }
+                for (int i = 2 * tid + parity; i + 1 < n; i += 2 * kThreads) {
+                    const unsigned long long a = buf[i], b = buf[i + 1];
+                    if (a > b) { buf[i] = b; buf[i + 1] = a; moved = true; }
                 }
                 __syncthreads();
             }
             bad = __syncthreads_or(moved);
         }
         if (bad) {  // uniform: still moving after four rounds -> a long run of equal depths
-            for (int i = tid; i < n; i += kLsThreads) buf_a[i] = keys[range.x + i];
-            src = ls_radix_passes<kLsWarps>(buf_a, buf_b, warp_hist, scan_tmp, n, seg_begin, seg_end, 0, id_passes + 4,
-                                            id_passes, id_bits);
+            for (int i = tid; i < n; i += kThreads) buf[i] = keys[range.x + i];
+            ls_radix_passes<W, K>(buf, warp_hist, scan_tmp, n, seg_begin, seg_end, 0, id_passes + 4, id_passes, id_bits);
         }
     }
-    for (int i = tid; i < n; i += kLsThreads) ids_out[range.x + i] = (int32_t)(unsigned)src[i];
+    for (int i = tid; i < n; i += kThreads) ids_out[range.x + i] = (int32_t)(unsigned)buf[i];
 }
 
 // tile totals over the blocks: one warp per tile; block_counts[b][t] becomes the exclusive prefix over b
@@ -402,27 +399,31 @@ extern "C" int gstex_tile_bucket_sort(int n, int num_intersects, int max_list, c
         cum_tiles_hit, tiles_x, tiles_y, (float)block_width, tile_start, block_counts,
         reinterpret_cast<unsigned long long*>(keys));
     GSTEX_LAUNCH_CHECK();
-    // per device, cheap: set every time rather than caching a flag across devices
-    GSTEX_CUDA_TRY(cudaFuncSetAttribute(tile_local_sort_kernel<kLsWarpsSmall>, cudaFuncAttributeMaxDynamicSharedMemorySize, kLsMaxSmem));
-    GSTEX_CUDA_TRY(cudaFuncSetAttribute(tile_local_sort_kernel<kLsWarpsLarge>, cudaFuncAttributeMaxDynamicSharedMemorySize, kLsMaxSmem));
     int id_bits = 1;
     while (id_bits < 32 && (1ll << id_bits) < (long long)n) ++id_bits;
-    // two size classes, so that the many short lists do not pay the shared memory of the longest one and the
-    // long ones get 32 warps
+    const int2* bins = reinterpret_cast<const int2*>(tile_bins);
+    const unsigned long long* k64 = reinterpret_cast<const unsigned long long*>(keys);
+    // size classes, so that the many short lists do not pay the shared memory / registers of the longest one
     {
         const int hi = max_list < kLsSmallCap ? max_list : kLsSmallCap;
-        tile_local_sort_kernel<kLsWarpsSmall>
-            <<<(int)num_tiles, kLsWarpsSmall * 32, (size_t)kLsSmallCap * 16 + ls_fixed_smem(kLsWarpsSmall), st>>>(
-                reinterpret_cast<const int2*>(tile_bins), reinterpret_cast<const unsigned long long*>(keys),
-                gaussian_ids_sorted, id_bits, kLsSmallCap, 1, hi);
+        tile_local_sort_kernel<kLsSmallW, kLsSmallK>
+            <<<(int)num_tiles, kLsSmallW * 32, ls_smem_bytes(kLsSmallW, kLsSmallK), st>>>(bins, k64, gaussian_ids_sorted,
+                                                                                          id_bits, 1, hi);
         GSTEX_LAUNCH_CHECK();
     }
     if (max_list > kLsSmallCap) {
-        const int cap = ((max_list + 511) / 512) * 512;
-        tile_local_sort_kernel<kLsWarpsLarge>
-            <<<(int)num_tiles, kLsWarpsLarge * 32, (size_t)cap * 16 + ls_fixed_smem(kLsWarpsLarge), st>>>(
-                reinterpret_cast<const int2*>(tile_bins), reinterpret_cast<const unsigned long long*>(keys),
-                gaussian_ids_sorted, id_bits, cap, kLsSmallCap + 1, max_list);
+        // cudaFuncSetAttribute is per device and cheap: set every time rather than caching a flag across devices
+#define GSTEX_LS_LAUNCH(KK)                                                                                            \
+    do {                                                                                                               \
+        GSTEX_CUDA_TRY(cudaFuncSetAttribute(tile_local_sort_kernel<kLsLargeW, KK>,                                     \
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize, ls_smem_bytes(kLsLargeW, KK))); \
+        tile_local_sort_kernel<kLsLargeW, KK><<<(int)num_tiles, kLsLargeW * 32, ls_smem_bytes(kLsLargeW, KK), st>>>(   \
+            bins, k64, gaussian_ids_sorted, id_bits, kLsSmallCap + 1, max_list);                                       \
+    } while (0)
+        if (max_list <= kLsLargeW * 32 * 12) GSTEX_LS_LAUNCH(12);
+        else if (max_list <= kLsLargeW * 32 * 16) GSTEX_LS_LAUNCH(16);
+        else GSTEX_LS_LAUNCH(26);
+#undef GSTEX_LS_LAUNCH
         GSTEX_LAUNCH_CHECK();
     }
     return GSTEX_OK;

@@ -209,7 +209,8 @@ def test_tile_bucket_ties_long_lists_and_empty():
     """Equal depths (ties resolved by splat index), every splat on every tile (long lists), no intersections."""
     g = torch.Generator().manual_seed(5)
     H, W, bw = 64, 96, 16
-    for n, ext, depth_vals in ((5000, 200.0, 3), (30000, 40.0, 2), (100, 0.0, 1)):
+    for n, ext, depth_vals in ((5000, 200.0, 3), (30000, 40.0, 2), (100, 0.0, 1), (7000, 200.0, 1 << 20),
+                              (12000, 200.0, 7), (2048, 200.0, 1 << 20), (2049, 200.0, 1 << 20), (600, 200.0, 40)):
         centers = (torch.rand(n, 2, generator=g) * torch.tensor([W, H])).cuda()
         extents = torch.full((n, 2), ext).cuda()
         depths = (torch.randint(0, depth_vals, (n,), generator=g).float() * 0.25 + 1.0).cuda()
