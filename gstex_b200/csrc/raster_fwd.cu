@@ -52,7 +52,9 @@ struct FwdParams {
     StreamView sv;  // pair stream (REC kernels only)
 };
 
-constexpr int kFwdWarps = 4;    // warps per CTA; they share nothing but the camera
+constexpr int kFwdWarps = 5;    // warps per CTA; they share nothing but the camera (4 CTAs/SM = 20 warps)
+constexpr int kFwdCtasPerSm = 4;
+constexpr int kHits = 64;       // ring of contributing pairs waiting for their texture fetch (deferred, lane-dense)
 constexpr int kBatch = 32;      // records per stage = one TMA bulk copy per lane
 constexpr int kQueue = 128;     // survivor ring: current batch + prefetched batch + one culling round
 
@@ -60,6 +62,8 @@ struct FwdWarpShared {
     SplatRec rec[2][kBatch];  // 8 KB
     int q_gid[kQueue];
     int q_idx[kQueue];
+    float4 h_e[kHits];   // (record slot | pixel lane << 5, T before the pair, u, v); after the fetch: (val0..2, vis)
+    float h_vis[kHits];  // alpha * T of the pair
     uint64_t bar[2];
 };
 
@@ -69,8 +73,11 @@ struct FwdShared {
 };
 
 template <int CMAX, bool REC>
-__global__ void __launch_bounds__(kFwdWarps * 32, 5) texture_forward_kernel(const FwdParams p) {
-    __shared__ __align__(128) FwdShared sm;
+__global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward_kernel(const FwdParams p) {
+    // <= 3 channels (training): the texture fetch of a contributing pair is deferred to a lane-dense phase
+    constexpr bool kDefer = (CMAX == 3);
+    extern __shared__ __align__(128) unsigned char fwd_smem[];
+    FwdShared& sm = *reinterpret_cast<FwdShared*>(fwd_smem);
     const RasterGeom g = p.g;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     FwdWarpShared& ws = sm.w[warp];
@@ -110,6 +117,7 @@ __global__ void __launch_bounds__(kFwdWarps * 32, 5) texture_forward_kernel(cons
             X0 = (float)(tile_x * g.bw + x0) + 0.5f; X1 = (float)(tile_x * g.bw + x1) + 0.5f;
             Y0 = (float)(tile_y * g.bw + y0) + 0.5f; Y1 = (float)(tile_y * g.bw + y1) + 0.5f;
         }
+        const int ipx = tile_x * g.bw + lx, ipy = tile_y * g.bw + ly;
 
         bool done = !pix.inside;
         float T = 1.f;
@@ -170,8 +178,89 @@ __global__ void __launch_bounds__(kFwdWarps * 32, 5) texture_forward_kernel(cons
         for (int k = 0; k < 16; ++k) st_[k] = 0;
         STAT_ADD(9, 1);
 #endif
-        bool unit_done = __all_sync(0xffffffffu, done);
+        // ---- deferred texture phase (kDefer): one queued pair per lane, whatever pixel it belongs to.
+        // Computes the bilinear sample, appends the pair to the stream (REC) and hands vis*sample back to the
+        // lane that owns the pixel, which adds its pairs in list order (so the sums are deterministic).
+        int h_head = 0, h_tail = 0;
+        unsigned long long mine = 0ull;  // ring slots holding pairs of this lane's pixel
         int cur = 0, n_cur = 0;
+        auto fetch_hits = [&](const int m) {
+            __syncwarp();
+            const int hs = (h_head + lane) & (kHits - 1);
+            const bool valid = lane < m;
+            float4 ent = make_float4(0.f, 0.f, 0.f, 0.f);
+            float vis = 0.f, val0 = 0.f, val1 = 0.f, val2 = 0.f;
+            int si = 0, pl = 0;
+            if (valid) {
+                ent = ws.h_e[hs];
+                vis = ws.h_vis[hs];
+                const int pk = __float_as_int(ent.x);
+                si = pk & 31; pl = (pk >> 5) & 31;
+                const SplatRec& rr = ws.rec[cur][si];
+                const float4 r4 = rr.q[4];
+                const int start = __float_as_int(rr.q[5].w);
+                const TexQuery tq = tex_query(__float_as_int(r4.z), __float_as_int(r4.w), start, ent.z, ent.w, bilinear);
+                const float* t00 = p.texture + (size_t)tq.b00 * C;
+                const float* t01 = p.texture + (size_t)tq.b01 * C;
+                const float* t10 = p.texture + (size_t)tq.b10 * C;
+                const float* t11 = p.texture + (size_t)tq.b11 * C;
+                val0 = tq.w00 * __ldg(t00) + tq.w01 * __ldg(t01) + tq.w10 * __ldg(t10) + tq.w11 * __ldg(t11);
+                if (C > 1) val1 = tq.w00 * __ldg(t00 + 1) + tq.w01 * __ldg(t01 + 1) + tq.w10 * __ldg(t10 + 1) + tq.w11 * __ldg(t11 + 1);
+                if (C > 2) val2 = tq.w00 * __ldg(t00 + 2) + tq.w01 * __ldg(t01 + 2) + tq.w10 * __ldg(t10 + 2) + tq.w11 * __ldg(t11 + 2);
+            }
+            if (REC && rec_ok) {  // the m pairs are consecutive items of the unit's stream, list order
+                int new_chunk = cur_chunk;
+                if (fill + m > kChunkItems) {
+                    int c = 0;
+                    if (lane == 0) c = (int)atomicAdd(&p.sv.hdr->next_chunk, 1u);
+                    c = __shfl_sync(0xffffffffu, c, 0);
+                    if (c >= p.sv.num_chunks) {
+                        if (lane == 0) p.sv.hdr->overflow = 1u;
+                        rec_ok = false;
+                    } else {
+                        if (lane == 0) p.sv.chunk_prev[c] = cur_chunk;
+                        new_chunk = c;
+                    }
+                }
+                if (rec_ok) {
+                    if (valid) {
+                        int pos = fill + lane;
+                        int ch = cur_chunk;
+                        if (pos >= kChunkItems) { pos -= kChunkItems; ch = new_chunk; }
+                        float4* dst = reinterpret_cast<float4*>(p.sv.items + (size_t)ch * kChunkItems + pos);
+                        const int q = (q_head + si) & (kQueue - 1);
+                        const uint32_t gl = ((uint32_t)ws.q_gid[q] << 5) | (uint32_t)pl;
+                        dst[0] = make_float4(__uint_as_float(gl), __int_as_float(ws.q_idx[q]), ent.y, ent.z);
+                        dst[1] = make_float4(ent.w, val0, val1, val2);
+                    }
+                    fill += m;
+                    if (fill > kChunkItems) { fill -= kChunkItems; cur_chunk = new_chunk; }
+                    cnt += m;
+                }
+            }
+            if (valid) ws.h_e[hs] = make_float4(val0, val1, val2, vis);
+            __syncwarp();
+            {   // this lane's pixel: its pairs among the m just fetched, oldest first
+                const int sh = h_head & (kHits - 1);
+                const unsigned long long rot = sh ? ((mine >> sh) | (mine << (64 - sh))) : mine;
+                const unsigned window = (m >= 32) ? 0xffffffffu : ((1u << m) - 1u);
+                unsigned low = (unsigned)rot & window;
+                while (low) {
+                    const int j = __ffs(low) - 1;
+                    low &= low - 1u;
+                    const float4 e4 = ws.h_e[(h_head + j) & (kHits - 1)];
+                    tex[0] += e4.w * e4.x;
+                    if (CMAX > 1) tex[1] += e4.w * e4.y;
+                    if (CMAX > 2) tex[2] += e4.w * e4.z;
+                }
+                const unsigned long long wmask = (unsigned long long)window;
+                mine &= ~(sh ? ((wmask << sh) | (wmask >> (64 - sh))) : wmask);
+            }
+            h_head += m;
+            __syncwarp();
+        };
+
+        bool unit_done = __all_sync(0xffffffffu, done);
         if (!unit_done) {
             prime();
             n_cur = fill_and_issue(cur);
@@ -207,7 +296,7 @@ __global__ void __launch_bounds__(kFwdWarps * 32, 5) texture_forward_kernel(cons
                 }
 #endif
                 bool hit = false;
-                float h_T = 0.f, h_u = 0.f, h_v = 0.f, h_val[3] = {0.f, 0.f, 0.f};
+                float h_T = 0.f, h_u = 0.f, h_v = 0.f, h_vis = 0.f;
                 if (!done) {
                     if (next_T <= 1e-4f) {
                         done = true;  // this splat is not composited
@@ -219,22 +308,24 @@ __global__ void __launch_bounds__(kFwdWarps * 32, 5) texture_forward_kernel(cons
                         const float t_view = e.t * pix.view_depth;
                         const float u = clamp01(r6.w + (r6.x * e.delta.x + r6.y * e.delta.y + r6.z * e.delta.z));
                         const float v = clamp01(r7.w + (r7.x * e.delta.x + r7.y * e.delta.y + r7.z * e.delta.z));
-                        const TexQuery tq =
-                            tex_query(__float_as_int(r4.z), __float_as_int(r4.w), __float_as_int(r5.w), u, v, bilinear);
-                        const float* t00 = p.texture + (size_t)tq.b00 * C;
-                        const float* t01 = p.texture + (size_t)tq.b01 * C;
-                        const float* t10 = p.texture + (size_t)tq.b10 * C;
-                        const float* t11 = p.texture + (size_t)tq.b11 * C;
+                        if constexpr (kDefer) {
+                            hit = true; h_T = T; h_u = u; h_v = v; h_vis = vis;
+                        } else {
+                            const TexQuery tq =
+                                tex_query(__float_as_int(r4.z), __float_as_int(r4.w), __float_as_int(r5.w), u, v, bilinear);
+                            const float* t00 = p.texture + (size_t)tq.b00 * C;
+                            const float* t01 = p.texture + (size_t)tq.b01 * C;
+                            const float* t10 = p.texture + (size_t)tq.b10 * C;
+                            const float* t11 = p.texture + (size_t)tq.b11 * C;
 #pragma unroll
-                        for (int k = 0; k < CMAX; ++k) {
-                            if (k < C) {
-                                const float val = tq.w00 * __ldg(t00 + k) + tq.w01 * __ldg(t01 + k) +
-                                                  tq.w10 * __ldg(t10 + k) + tq.w11 * __ldg(t11 + k);
-                                tex[k] += vis * val;
-                                if (REC && k < 3) h_val[k] = val;
+                            for (int k = 0; k < CMAX; ++k) {
+                                if (k < C) {
+                                    const float val = tq.w00 * __ldg(t00 + k) + tq.w01 * __ldg(t01 + k) +
+                                                      tq.w10 * __ldg(t10 + k) + tq.w11 * __ldg(t11 + k);
+                                    tex[k] += vis * val;
+                                }
                             }
                         }
-                        if (REC) { hit = true; h_T = T; h_u = u; h_v = v; }
                         if (T > 0.5f) {  // median depth, texture.cu:286-291
                             pix_depth = t_view;
                             pix_depth_index = idx;
@@ -248,42 +339,25 @@ __global__ void __launch_bounds__(kFwdWarps * 32, 5) texture_forward_kernel(cons
                     }
                 }
                 last_pos = idx;
-                if (REC) {  // append this splat's contributing pairs to the unit's stream, lane order
+                if constexpr (kDefer) {  // queue this splat's contributing pairs for the lane-dense texture phase
                     const unsigned hb = __ballot_sync(0xffffffffu, hit);
-                    if (hb != 0u && rec_ok) {
-                        const int nh = __popc(hb);
-                        int new_chunk = cur_chunk;
-                        if (fill + nh > kChunkItems) {
-                            int c = 0;
-                            if (lane == 0) c = (int)atomicAdd(&p.sv.hdr->next_chunk, 1u);
-                            c = __shfl_sync(0xffffffffu, c, 0);
-                            if (c >= p.sv.num_chunks) {
-                                if (lane == 0) p.sv.hdr->overflow = 1u;
-                                rec_ok = false;
-                            } else {
-                                if (lane == 0) p.sv.chunk_prev[c] = cur_chunk;
-                                new_chunk = c;
-                            }
+                    if (hb != 0u) {
+                        if (hit) {
+                            const int pos = (h_tail + __popc(hb & lt_mask)) & (kHits - 1);
+                            ws.h_e[pos] = make_float4(__int_as_float(i | (lane << 5)), h_T, h_u, h_v);
+                            ws.h_vis[pos] = h_vis;
+                            mine |= 1ull << pos;
                         }
-                        if (rec_ok) {
-                            if (hit) {
-                                int pos = fill + __popc(hb & lt_mask);
-                                int ch = cur_chunk;
-                                if (pos >= kChunkItems) { pos -= kChunkItems; ch = new_chunk; }
-                                float4* dst = reinterpret_cast<float4*>(p.sv.items + (size_t)ch * kChunkItems + pos);
-                                const uint32_t gl = ((uint32_t)ws.q_gid[q] << 5) | (uint32_t)lane;
-                                dst[0] = make_float4(__uint_as_float(gl), __int_as_float(idx), h_T, h_u);
-                                dst[1] = make_float4(h_v, h_val[0], h_val[1], h_val[2]);
-                            }
-                            fill += nh;
-                            if (fill > kChunkItems) { fill -= kChunkItems; cur_chunk = new_chunk; }
-                            cnt += nh;
-                        }
+                        h_tail += __popc(hb);
+                        if (h_tail - h_head >= 32) fetch_hits(32);
                     }
                 }
                 if (__all_sync(0xffffffffu, done)) { unit_done = true; break; }
             }
             __syncwarp();
+            if constexpr (kDefer) {  // the queued pairs point into this batch's record stage: finish them now
+                while (h_tail != h_head) fetch_hits(min(32, h_tail - h_head));
+            }
             if (unit_done || flush) {
                 if (n_next > 0) {  // drain the copies in flight before their stage and barrier are reused
                     mbar_wait(&ws.bar[cur ^ 1], (phase >> (cur ^ 1)) & 1u);
@@ -301,6 +375,12 @@ __global__ void __launch_bounds__(kFwdWarps * 32, 5) texture_forward_kernel(cons
             q_head += n_cur;
             n_cur = n_next;
             cur ^= 1;
+            {   // cull the rest of the list against the rectangle of the pixels that are still alive
+                const int big = 1 << 30;
+                const int ax0 = __reduce_min_sync(0xffffffffu, done ? big : ipx), ax1 = __reduce_max_sync(0xffffffffu, done ? -big : ipx);
+                const int ay0 = __reduce_min_sync(0xffffffffu, done ? big : ipy), ay1 = __reduce_max_sync(0xffffffffu, done ? -big : ipy);
+                X0 = (float)ax0 + 0.5f; X1 = (float)ax1 + 0.5f; Y0 = (float)ay0 + 0.5f; Y1 = (float)ay1 + 0.5f;
+            }
         }
 
 #ifdef GSTEX_STATS
@@ -405,7 +485,7 @@ extern "C" int gstex_texture_forward(int img_height, int img_width, int block_wi
     p.units_per_tile = p.g.threads / 32;
     p.num_units = p.g.tiles_x * p.g.tiles_y * p.units_per_tile;
     // persistent grid: enough CTAs to fill every SM at the kernels' occupancy, never more than there are units
-    int grid = 148 * 5;
+    int grid = 148 * kFwdCtasPerSm;
     if (grid > (p.num_units + kFwdWarps - 1) / kFwdWarps) grid = (p.num_units + kFwdWarps - 1) / kFwdWarps;
     const int threads = kFwdWarps * 32;
     // Record the pair stream for the stream backward when the caller gave a pool and the configuration is the
@@ -417,10 +497,18 @@ extern "C" int gstex_texture_forward(int img_height, int img_width, int block_wi
         if (!record)  // tell the backward there is nothing to read
             GSTEX_CUDA_TRY(cudaMemsetAsync(reinterpret_cast<char*>(pair_stream) + offsetof(StreamHeader, overflow), 1, 1, st));
     }
-    if (record) texture_forward_kernel<3, true><<<grid, threads, 0, st>>>(p);
-    else if (channels <= 3) texture_forward_kernel<3, false><<<grid, threads, 0, st>>>(p);
-    else if (channels <= 6) texture_forward_kernel<6, false><<<grid, threads, 0, st>>>(p);
-    else texture_forward_kernel<GSTEX_MAX_CHANNELS, false><<<grid, threads, 0, st>>>(p);
+    // > 48 KB of shared memory: opt in (per device, cheap: done at every launch)
+#define GSTEX_FWD_LAUNCH(CM, RC)                                                                                        \
+    do {                                                                                                                \
+        GSTEX_CUDA_TRY(cudaFuncSetAttribute(texture_forward_kernel<CM, RC>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                            (int)sizeof(FwdShared)));                                                   \
+        texture_forward_kernel<CM, RC><<<grid, threads, sizeof(FwdShared), st>>>(p);                                    \
+    } while (0)
+    if (record) GSTEX_FWD_LAUNCH(3, true);
+    else if (channels <= 3) GSTEX_FWD_LAUNCH(3, false);
+    else if (channels <= 6) GSTEX_FWD_LAUNCH(6, false);
+    else GSTEX_FWD_LAUNCH(GSTEX_MAX_CHANNELS, false);
+#undef GSTEX_FWD_LAUNCH
     GSTEX_LAUNCH_CHECK();
     return GSTEX_OK;
 }
