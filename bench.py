@@ -370,7 +370,8 @@ def main():
 
     # ---- end to end through the public API with host buffers
     host, h2d, d2h = wl.make_host()
-    wl.step_e2e(world, host)
+    for _ in range(max(args.warmup, 1)):
+        wl.step_e2e(world, host)
     barrier()
     t0 = time.perf_counter()
     e0.record()

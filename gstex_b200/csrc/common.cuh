@@ -84,10 +84,9 @@ __device__ __forceinline__ void get_ray(const Camera& cam, float px, float py, f
 
 // ref: texture_helpers.cuh:302-313 (denominator clamp of compute_tt)
 __device__ __forceinline__ float clamp_tt_denom(float d) {
+    // 0 <= d < eps -> eps; -eps < d <= 0 -> -eps (d == -0.0 takes the first branch, as in the reference); NaN stays
     const float eps = 1e-6f;
-    if (0.f <= d && d < eps) d = eps;
-    else if (-eps < d && d <= 0.f) d = -eps;
-    return d;
+    return (fabsf(d) < eps) ? ((d < 0.f) ? -eps : eps) : d;
 }
 
 // ref: texture_helpers.cuh:37-51 clamp_coord (replicate padding is hard-wired on, texture.cu:65)

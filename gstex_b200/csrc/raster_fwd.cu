@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
         // ---- list walk state: cursor = next list position to test; ring indices are monotonic
         int cursor = range.x, last_pos = range.x - 1;
         int q_head = 0, q_issue = 0, q_tail = 0;
-        bool nocull = false;
+        bool nocull = false, danger = false;
         int gid_pf, gid_pf2;
         float4 box_pf;
         auto prime = [&]() {  // ids two rounds ahead, support boxes one round ahead of the round being tested
@@ -270,15 +270,16 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
             mbar_wait(&ws.bar[cur], (phase >> cur) & 1u);
             phase ^= 1u << cur;
             bool flush = false;
-            for (int i = 0; i < n_cur; ++i) {
+            int i = 0;
+            for (; i < n_cur; ++i) {
                 // A pixel whose transmittance sits in (1e-4, 1e-4/(1-1/255)] can be terminated even by a pair with
                 // alpha < 1/255: from here on nothing may be culled for this warp until that pixel is finished.
-                const bool danger = __any_sync(0xffffffffu, !done && T <= 1.0041e-4f);
+                // `danger` is warp-uniform and refreshed whenever a transmittance changed (a pixel that finishes
+                // without one may leave it set a little longer, which only delays the return to culling).
                 if (danger && !nocull) { flush = true; break; }
                 if (!danger) nocull = false;
                 const SplatRec& r = ws.rec[cur][i];
                 const int q = (q_head + i) & (kQueue - 1);
-                const int idx = ws.q_idx[q];
                 const float4 r0 = r.q[0], r1 = r.q[1], r2 = r.q[2], r3 = r.q[3], r4 = r.q[4];
                 const PairEval e = eval_pair(pix, r0, r1, r2, r3, r4, use_blur);
                 const float next_T = T * (1.f - e.alpha);
@@ -301,6 +302,7 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
                     if (next_T <= 1e-4f) {
                         done = true;  // this splat is not composited
                     } else if (!e.skip) {
+                        const int idx = ws.q_idx[q];
                         const float vis = e.alpha * T;
                         const float4 r5 = r.q[5], r6 = r.q[6], r7 = r.q[7];
                         rgb.x += r5.x * vis; rgb.y += r5.y * vis; rgb.z += r5.z * vis;
@@ -308,8 +310,9 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
                         const float t_view = e.t * pix.view_depth;
                         const float u = clamp01(r6.w + (r6.x * e.delta.x + r6.y * e.delta.y + r6.z * e.delta.z));
                         const float v = clamp01(r7.w + (r7.x * e.delta.x + r7.y * e.delta.y + r7.z * e.delta.z));
+                        hit = true;
                         if constexpr (kDefer) {
-                            hit = true; h_T = T; h_u = u; h_v = v; h_vis = vis;
+                            h_T = T; h_u = u; h_v = v; h_vis = vis;
                         } else {
                             const TexQuery tq =
                                 tex_query(__float_as_int(r4.z), __float_as_int(r4.w), __float_as_int(r5.w), u, v, bilinear);
@@ -338,10 +341,10 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
                         cur_idx = idx;
                     }
                 }
-                last_pos = idx;
-                if constexpr (kDefer) {  // queue this splat's contributing pairs for the lane-dense texture phase
-                    const unsigned hb = __ballot_sync(0xffffffffu, hit);
-                    if (hb != 0u) {
+                const unsigned hb = __ballot_sync(0xffffffffu, hit);
+                if (hb != 0u) {
+                    danger = __any_sync(0xffffffffu, !done && T <= 1.0041e-4f);
+                    if constexpr (kDefer) {  // queue this splat's contributing pairs for the lane-dense texture phase
                         if (hit) {
                             const int pos = (h_tail + __popc(hb & lt_mask)) & (kHits - 1);
                             ws.h_e[pos] = make_float4(__int_as_float(i | (lane << 5)), h_T, h_u, h_v);
@@ -364,7 +367,8 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
                     phase ^= 1u << (cur ^ 1);
                 }
                 if (unit_done) break;
-                // re-walk from the entry after the last composited one, with culling off
+                // re-walk from the entry after the last evaluated one, with culling off
+                if (i > 0) last_pos = ws.q_idx[(q_head + i - 1) & (kQueue - 1)];
                 nocull = true;
                 cursor = last_pos + 1;
                 q_head = q_issue = q_tail = 0;
@@ -372,6 +376,7 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
                 n_cur = fill_and_issue(cur);
                 continue;
             }
+            last_pos = ws.q_idx[(q_head + n_cur - 1) & (kQueue - 1)];
             q_head += n_cur;
             n_cur = n_next;
             cur ^= 1;

@@ -52,30 +52,49 @@ class HostViewFeeder:
         feeder.finish()                                 # host may read host_out[*]
     """
 
-    def __init__(self, device):
+    def __init__(self, device, slots: int = 2):
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise RuntimeError("HostViewFeeder needs a CUDA device (there is no CPU path)")
         self.h2d = torch.cuda.Stream(self.device)
         self.d2h = torch.cuda.Stream(self.device)
         self._pending = None
+        # Device staging buffers, `slots` sets used round-robin and allocated once per (position, shape, dtype):
+        # nothing is allocated in steady state (a cudaMalloc in the middle of a step synchronises the device).
+        # The tensors `take()` returns for a view stay valid until `slots` further views have been prefetched.
+        self._slots = [dict() for _ in range(max(2, int(slots)))]
+        self._turn = 0
 
     @staticmethod
-    def _map(obj, fn):
+    def _map(obj, fn, path=()):
         if isinstance(obj, torch.Tensor):
-            return fn(obj)
+            return fn(obj, path)
         if isinstance(obj, dict):
-            return {k: HostViewFeeder._map(v, fn) for k, v in obj.items()}
+            return {k: HostViewFeeder._map(v, fn, path + (k,)) for k, v in obj.items()}
         if isinstance(obj, (list, tuple)):
-            return type(obj)(HostViewFeeder._map(v, fn) for v in obj)
+            return type(obj)(HostViewFeeder._map(v, fn, path + (i,)) for i, v in enumerate(obj))
         return obj
 
     def prefetch(self, host_inputs):
         """Start the host->device copies of one view's inputs (any nest of dict/list/tuple of pinned tensors)."""
         if self._pending is not None:
             raise RuntimeError("HostViewFeeder.prefetch: the previous view has not been taken")
+        slot = self._slots[self._turn % len(self._slots)]
+        self._turn += 1
+        # the slot's previous user (a view rendered `slots` views ago) was enqueued on the compute stream before now
+        free = torch.cuda.Event()
+        free.record(torch.cuda.current_stream(self.device))
+        self.h2d.wait_event(free)
+
+        def stage(t, path):
+            buf = slot.get(path)
+            if buf is None or buf.shape != t.shape or buf.dtype != t.dtype:
+                buf = slot[path] = torch.empty(t.shape, dtype=t.dtype, device=self.device)
+            buf.copy_(t, non_blocking=True)
+            return buf
+
         with torch.cuda.stream(self.h2d):
-            dev = self._map(host_inputs, lambda t: t.to(self.device, non_blocking=True))
+            dev = self._map(host_inputs, stage)
             ev = torch.cuda.Event()
             ev.record(self.h2d)
         self._pending = (dev, ev)
@@ -86,9 +105,7 @@ class HostViewFeeder:
             raise RuntimeError("HostViewFeeder.take: nothing was prefetched")
         dev, ev = self._pending
         self._pending = None
-        cur = torch.cuda.current_stream(self.device)
-        cur.wait_event(ev)
-        self._map(dev, lambda t: (t.record_stream(cur), t)[1])
+        torch.cuda.current_stream(self.device).wait_event(ev)
         return dev
 
     def send_back(self, dev_tensor, host_tensor):
