@@ -45,6 +45,8 @@ _SIGNATURES = {
     "gstex_texture_backward": (I, [I, I, I, I, I, I] + [P] * 7 + [F] + [P] * 7 + [F, F, F, F, I] + [P] * 11 + [P] * 9 +
                                [P, SZ, I, P, SZ, P, SZ, ctypes.c_longlong, I, P]),
     "gstex_grad_scratch_bytes": (SZ, [I, ctypes.c_longlong]),
+    "gstex_compute_sh_forward": (I, [I, I, I, P, P, P, P]),
+    "gstex_compute_sh_backward": (I, [I, I, I, P, P, P, P]),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)

@@ -181,6 +181,20 @@ int gstex_texture_backward(int img_height, int img_width, int block_width, int c
                            void* pair_stream, size_t pair_stream_bytes, void* grad_scratch, size_t grad_scratch_size,
                            long long num_texels, int zero_fill, void* stream);
 
+/* ---- next row: per-splat colour from spherical harmonics -------------------- */
+
+/* ref: cuda/csrc/bindings.cu:18-43 compute_sh_forward_tensor -> sh.cuh:217-235 (sh_coeffs_to_color :47-119).
+ * viewdirs (n,3) need not be normalised; coeffs (n, num_bases(degree), 3); colors (n,3), every element written.
+ * degree in 0..4 fixes the row length (1/4/9/16/25 bases), degrees_to_use <= degree selects the bases summed. */
+int gstex_compute_sh_forward(int n, int degree, int degrees_to_use, const float* viewdirs, const float* coeffs,
+                             float* colors, void* stream);
+
+/* ref: cuda/csrc/bindings.cu:45-75 compute_sh_backward_tensor -> sh.cuh:237-253 (sh_coeffs_to_color_vjp :121-215).
+ * v_coeffs (n, num_bases(degree), 3): every element written (zeros above the used bases, as the reference's
+ * torch::zeros leaves them).  No gradient with respect to viewdirs (sh.py:44-45). */
+int gstex_compute_sh_backward(int n, int degree, int degrees_to_use, const float* viewdirs, const float* v_colors,
+                              float* v_coeffs, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -22,7 +22,8 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _BUILD = os.path.join(_HERE, "_build")
 _SO = os.path.join(_BUILD, "libgstex_oracle.so")
-_SRCS = [os.path.join(_HERE, "gstex_oracle.c"), os.path.join(_HERE, "gstex_oracle_raster.c")]
+_SRCS = [os.path.join(_HERE, "gstex_oracle.c"), os.path.join(_HERE, "gstex_oracle_raster.c"),
+         os.path.join(_HERE, "gstex_oracle_sh.c")]
 
 _lib = None
 
@@ -163,3 +164,38 @@ def bin_and_sort_gaussians(num_points, num_intersects, centers, extents, depths,
     isect_s, gids_s = sort_isects(isect, gids)
     bins = get_tile_bin_edges(num_intersects, isect_s, tile_bounds)
     return isect, gids, isect_s, gids_s, bins
+
+
+# ---- spherical harmonics (gstex_cuda/sh.py:36-96 -> cuda/csrc/sh.cuh) ------------------------------------------
+
+def num_sh_bases(degree: int) -> int:
+    return {0: 1, 1: 4, 2: 9, 3: 16}.get(int(degree), 25)
+
+
+def deg_from_sh(num_bases: int) -> int:
+    return {1: 0, 4: 1, 9: 2, 16: 3, 25: 4}[int(num_bases)]
+
+
+def spherical_harmonics(degrees_to_use: int, viewdirs: np.ndarray, coeffs: np.ndarray) -> np.ndarray:
+    """colors (N,3); ref: sh.py:36-58 -> compute_sh_forward (sh.cuh:217-235)."""
+    viewdirs = np.ascontiguousarray(viewdirs, np.float32)
+    coeffs = np.ascontiguousarray(coeffs, np.float32)
+    n = coeffs.shape[0]
+    assert coeffs.shape[-2] >= num_sh_bases(degrees_to_use)
+    out = np.empty((n, 3), np.float32)
+    f = ctypes.POINTER(ctypes.c_float)
+    lib().orc_sh_forward(ctypes.c_int(n), ctypes.c_int(deg_from_sh(coeffs.shape[-2])), ctypes.c_int(int(degrees_to_use)),
+                         viewdirs.ctypes.data_as(f), coeffs.ctypes.data_as(f), out.ctypes.data_as(f))
+    return out
+
+
+def spherical_harmonics_vjp(degrees_to_use: int, num_bases: int, viewdirs: np.ndarray, v_colors: np.ndarray) -> np.ndarray:
+    """v_coeffs (N, num_bases, 3); ref: sh.py:84-96 -> compute_sh_backward (sh.cuh:237-253)."""
+    viewdirs = np.ascontiguousarray(viewdirs, np.float32)
+    v_colors = np.ascontiguousarray(v_colors, np.float32)
+    n = v_colors.shape[0]
+    out = np.empty((n, int(num_bases), 3), np.float32)
+    f = ctypes.POINTER(ctypes.c_float)
+    lib().orc_sh_backward(ctypes.c_int(n), ctypes.c_int(deg_from_sh(num_bases)), ctypes.c_int(int(degrees_to_use)),
+                          viewdirs.ctypes.data_as(f), v_colors.ctypes.data_as(f), out.ctypes.data_as(f))
+    return out
