@@ -1,5 +1,5 @@
 #!/bin/bash
-# One GPU-box pass: parity tests, bench line, ncu launch list, ncu --set full of the compositing kernels.
+# One GPU-box pass: parity tests, bench line, ncu launch list, ncu --set full of the compositing and binning kernels.
 # Usage (from the repo root, under gpurun): bash scripts/gpu_round.sh <tag>
 TAG=${1:-r1}
 OUT=gpurun_out
@@ -14,6 +14,6 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-fil
   python bench.py --steps 1 --warmup 1 --views-per-gpu 2 --no-ref-cuda --no-cpu-baseline > $OUT/ncu_launch_$TAG.log 2>&1; echo "ncu launches rc=$?"
 ncu --set full --clock-control none --import-source on -k regex:'texture_(forward_kernel|backward_stream_kernel)' -s 4 -c 2 \
   -o $OUT/raster_$TAG -f python bench.py --steps 1 --warmup 1 --views-per-gpu 2 --no-ref-cuda --no-cpu-baseline > $OUT/ncu_full_$TAG.log 2>&1; echo "ncu full rc=$?"
-ncu --set full --clock-control none --import-source on -k regex:'radix_' -s 12 -c 3 \
+ncu --set full --clock-control none --import-source on -k regex:'tile_(count|colscan|scan|emit|local_sort)' -s 6 -c 6 \
   -o $OUT/sort_$TAG -f python bench.py --steps 1 --warmup 1 --views-per-gpu 2 --no-ref-cuda --no-cpu-baseline > $OUT/ncu_sort_$TAG.log 2>&1; echo "ncu sort rc=$?"
 ls -la $OUT
