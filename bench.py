@@ -144,29 +144,46 @@ class Workload:
         self.last_I = 0
         self.feeder = None
 
-    def render_view(self, viewmat, c2w, v):
-        """One view through the public API (the reference's call sequence, NS/models/gstex.py:1075-1170)."""
+    def prep_view(self, viewmat):
+        """Projection + the asynchronous half of the binning of one view (no host synchronisation)."""
+        import gstex_b200 as G
+
+        p = self.params
+        _, depths, centers, extents, nth = G.project_bounds(p["means"], p["scales"], 1, p["quats"], viewmat, self.intr,
+                                                            self.H, self.W, self.bw)
+        tb = ((self.W + self.bw - 1) // self.bw, (self.H + self.bw - 1) // self.bw, 1)
+        return centers, extents, depths, nth, G.begin_binning(self.s["N"], centers, extents, depths, nth, tb, self.bw)
+
+    def forward_view(self, pre, viewmat, c2w):
+        """The reference's call (NS/models/gstex.py:1075-1170) on a prepared view."""
         import gstex_b200 as G
 
         p, s = self.params, self.s
-        _, depths, centers, extents, nth = G.project_bounds(p["means"], p["scales"], 1, p["quats"], viewmat, self.intr,
-                                                            self.H, self.W, self.bw)
-        outs = G.texture_gaussians(s["texture_info"], self.texture_dims, centers, extents, depths, nth, p["colors"],
+        centers, extents, depths, nth, binning = pre
+        return G.texture_gaussians(s["texture_info"], self.texture_dims, centers, extents, depths, nth, p["colors"],
                                    p["opacities"], p["means"], p["scales"], 1, p["quats"], p["uv0"], p["umap"],
                                    p["vmap"], p["texture"], viewmat, c2w, *self.intr, self.H, self.W, self.bw,
-                                   s["settings"], self.background)
+                                   s["settings"], self.background, binning=binning)
+
+    def backward_view(self, outs, v):
         self.torch.autograd.backward(list(outs), [v["v_out_img"], v["v_out_depth"], v["v_out_reg"], v["v_out_alpha"],
                                                   v["v_out_texture"], v["v_out_normal"]])
-        return outs
 
     def zero_grad(self):
         for p in self.params.values():
             p.grad = None
 
     def step(self, world):
+        """All local views, fwd+bwd through the public API.  View i+1's projection and binning counts are launched
+        between view i's forward and backward, so the host reads view i+1's `num_intersects` while the backward runs
+        (the reference's blocking `.item()` per view would drain the GPU each time)."""
         self.zero_grad()
-        for vm, c2w in zip(self.viewmats, self.c2ws):
-            self.render_view(vm, c2w, self.v)
+        nv = len(self.viewmats)
+        pre = self.prep_view(self.viewmats[0])
+        for i in range(nv):
+            outs = self.forward_view(pre, self.viewmats[i], self.c2ws[i])
+            pre = self.prep_view(self.viewmats[i + 1]) if i + 1 < nv else None
+            self.backward_view(outs, self.v)
         allreduce_gradients([p.grad for p in self.params.values()], world)
 
     def step_e2e(self, world, host):
@@ -181,13 +198,20 @@ class Workload:
         self.zero_grad()
         view_in = lambda i: {"vm": host["viewmats"][i], "c2w": host["c2ws"][i], "v": host["v"]}
         fd.prefetch(view_in(0))
+        d = fd.take()
+        pre = self.prep_view(d["vm"])
+        if nv > 1:
+            fd.prefetch(view_in(1))
         for i in range(nv):
-            d = fd.take()
-            if i + 1 < nv:
-                fd.prefetch(view_in(i + 1))
-            outs = self.render_view(d["vm"], d["c2w"], d["v"])
+            outs = self.forward_view(pre, d["vm"], d["c2w"])
+            d_next = fd.take() if i + 1 < nv else None
+            pre = self.prep_view(d_next["vm"]) if d_next is not None else None
+            self.backward_view(outs, d["v"])
+            if i + 2 < nv:  # view i's staging slot is free once its backward is enqueued
+                fd.prefetch(view_in(i + 2))
             fd.send_back(outs[0].detach(), host["out_img"][i])
             fd.send_back(outs[3].detach().sum(), host["scalar"][i])
+            d = d_next
         allreduce_gradients([p.grad for p in self.params.values()], world)
         fd.finish()  # the host consumes the result every step
 

@@ -15,7 +15,7 @@ from torch import Tensor
 from torch.autograd import Function
 
 from . import _lib
-from .utils import bin_gaussians_to_tiles
+from .utils import TileBinning, bin_gaussians_to_tiles, finish_binning
 
 SUPPORTED_SETTINGS = (1 << 2) | (1 << 8) | (1 << 9) | (1 << 10)
 
@@ -91,8 +91,14 @@ def texture_gaussians(
     settings: int,
     background: Optional[Tensor] = None,
     use_torch_impl: bool = False,
+    *,
+    binning: Optional[TileBinning] = None,
 ):
-    """Rasterizes textured 2D gaussians (ref: texture.py:14-150)."""
+    """Rasterizes textured 2D gaussians (ref: texture.py:14-150).
+
+    `binning` (not in the reference): a request started earlier with `gstex_b200.utils.begin_binning` on the same
+    `centers / extents / depths / num_tiles_hit`; the call then only waits for that request's sizes instead of
+    synchronising the stream (multi-view pipelining, see `TileBinning`)."""
     assert block_width > 1 and block_width <= 16, "block_width must be between 2 and 16"
     if use_torch_impl:
         raise NotImplementedError("gstex_b200 has no PyTorch/CPU rasterizer: the CUDA kernels are the only path")
@@ -115,7 +121,7 @@ def texture_gaussians(
         num_tiles_hit.contiguous(), colors.contiguous(), opacity.contiguous(), means.contiguous(),
         scales.contiguous(), glob_scale, quats.contiguous(), uv0.contiguous(), umap.contiguous(), vmap.contiguous(),
         texture.contiguous(), viewmat.contiguous(), c2w.contiguous(), fx, fy, cx, cy, img_height, img_width,
-        block_width, settings, background.contiguous())
+        block_width, settings, background.contiguous(), binning)
 
 
 def _raster_forward(texture_info, texture_dims, gaussian_ids_sorted, tile_bins, colors, opacity, means, scales,
@@ -173,14 +179,17 @@ class _TextureGaussians(Function):
     @staticmethod
     def forward(ctx, texture_info, texture_dims, centers, extents, depths, num_tiles_hit, colors, opacity, means,
                 scales, glob_scale, quats, uv0, umap, vmap, texture, viewmat, c2w, fx, fy, cx, cy, img_height,
-                img_width, block_width, settings, background=None):
+                img_width, block_width, settings, background=None, binning=None):
         num_points = centers.size(0)
         tile_bounds = ((img_width + block_width - 1) // block_width, (img_height + block_width - 1) // block_width, 1)
         dev = centers.device
         # The reference leaves most outputs undefined without intersections (texture.py:197-205, a latent
         # NameError guarded by the model at NS/models/gstex.py:1127); we return a well-formed empty render.
-        num_intersects, gaussian_ids_sorted, tile_bins = bin_gaussians_to_tiles(
-            num_points, centers, extents, depths, num_tiles_hit, tile_bounds, block_width)
+        if binning is not None:
+            num_intersects, gaussian_ids_sorted, tile_bins = finish_binning(binning)
+        else:
+            num_intersects, gaussian_ids_sorted, tile_bins = bin_gaussians_to_tiles(
+                num_points, centers, extents, depths, num_tiles_hit, tile_bounds, block_width)
         outputs, ws, pairs = _raster_forward(texture_info, texture_dims, gaussian_ids_sorted, tile_bins, colors,
                                              opacity, means, scales, glob_scale, quats, uv0, umap, vmap, texture,
                                              viewmat, c2w, fx, fy, cx, cy, img_height, img_width, block_width,
@@ -253,4 +262,4 @@ class _TextureGaussians(Function):
                 scratch.numel() if scratch is not None else 0, int(texture.shape[0]), 1, _lib.stream_ptr(dev))
         _lib.check(rc, "gstex_texture_backward")
         return (None, None, None, None, None, None, v_colors, v_opacity, v_means, v_scales, None, v_quats, v_uv0,
-                v_umap, v_vmap, v_texture, None, None, None, None, None, None, None, None, None, None, None)
+                v_umap, v_vmap, v_texture, None, None, None, None, None, None, None, None, None, None, None, None)

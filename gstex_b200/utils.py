@@ -119,54 +119,114 @@ def bin_and_sort_gaussians(num_points: int, num_intersects: int, centers: Tensor
     return isect_ids, gaussian_ids, isect_ids_sorted, gaussian_ids_sorted, tile_bins
 
 
-def bin_gaussians_to_tiles(num_points: int, centers: Tensor, extents: Tensor, depths: Tensor, num_tiles_hit: Tensor,
-                           tile_bounds, block_size: int):
-    """What `texture_gaussians` needs from `compute_cumulative_intersects` + `bin_and_sort_gaussians`
-    (ref: utils.py:40-59,106-162): `(num_intersects, gaussian_ids_sorted (I,) int32, tile_bins (tiles,2) int32)`,
-    bit-identical to them, through the tile-bucket path (csrc/tile_bucket.cu) -- per-tile counts, one scan, an
-    atomic-cursor emit and a per-tile shared-memory sort by (depth bits, splat id) -- instead of a radix sort of
-    the whole list.  One blocking read of two ints (`num_intersects`, longest tile list) replaces the
-    reference's `.item()` (utils.py:58).  A tile list longer than the shared-memory capacity sends the call
-    down the general path."""
+class TileBinning:
+    """State of a binning request between `begin_binning` (asynchronous: prefix sum, per-tile counts, a pinned
+    read-back of `num_intersects` and the longest tile list) and `finish_binning` (waits for that read-back only,
+    then emits and sorts).  Splitting the two lets a multi-view step launch view i+1's `begin_binning` between
+    view i's forward and backward: the host learns view i+1's sizes while the backward still runs, so the one
+    host synchronisation of the stage (the reference's `.item()`, utils.py:58) no longer drains the GPU."""
+
+    __slots__ = ("num_points", "centers", "extents", "depths", "cum", "total", "tile_bounds", "block_size", "num_tiles",
+                 "block_counts", "tile_start", "tile_bins", "stats_host", "event", "fast", "result")
+
+
+_PINNED_STATS = {"ring": [], "next": 0}
+
+
+def _pinned_stats() -> Tensor:
+    ring = _PINNED_STATS["ring"]
+    if len(ring) < 8:
+        ring.append(torch.empty(2, dtype=torch.int32).pin_memory())
+        return ring[-1]
+    _PINNED_STATS["next"] = (_PINNED_STATS["next"] + 1) % len(ring)
+    return ring[_PINNED_STATS["next"]]
+
+
+def begin_binning(num_points: int, centers: Tensor, extents: Tensor, depths: Tensor, num_tiles_hit: Tensor,
+                  tile_bounds, block_size: int) -> TileBinning:
+    """Asynchronous first half of `bin_gaussians_to_tiles` (no host synchronisation)."""
     centers, extents, depths = centers.contiguous(), extents.contiguous(), depths.contiguous()
     nth = num_tiles_hit.contiguous().reshape(-1)
     dev = _lib.require_cuda(centers, extents, depths, nth)
     for t, nm in ((centers, "centers"), (extents, "extents"), (depths, "depths")):
         _lib.require_dtype(t, torch.float32, nm)
-    num_tiles = int(tile_bounds[0]) * int(tile_bounds[1])
+    b = TileBinning()
+    b.num_points, b.centers, b.extents, b.depths = int(num_points), centers, extents, depths
+    b.tile_bounds, b.block_size = tile_bounds, int(block_size)
+    b.num_tiles = int(tile_bounds[0]) * int(tile_bounds[1])
+    b.result = None
+    b.event = b.stats_host = b.block_counts = b.tile_start = b.tile_bins = None
     i32 = dict(dtype=torch.int32, device=dev)
     if nth.numel() == 0:
-        return 0, torch.zeros((0,), **i32), torch.zeros((num_tiles, 2), **i32)
-    cum, total = cumsum_i32(nth)
+        b.result = (0, torch.zeros((0,), **i32), torch.zeros((b.num_tiles, 2), **i32))
+        return b
+    b.cum, b.total = cumsum_i32(nth)
+    lib = _lib.load()
+    b.fast = b.num_tiles <= lib.gstex_tile_bucket_max_tiles()
+    if not b.fast:
+        return b
+    b.block_counts = _workspace(lib.gstex_tile_bucket_scratch_bytes(b.num_tiles), dev)
+    small = torch.empty((b.num_tiles + 2,), **i32)  # tile_start | stats
+    b.tile_start, stats = small[:b.num_tiles], small[b.num_tiles:]
+    b.tile_bins = torch.empty((b.num_tiles, 2), **i32)
+    p, st = _lib.ptr, _lib.stream_ptr(dev)
+    with torch.cuda.device(dev):
+        rc = lib.gstex_tile_bucket_count(b.num_points, p(centers), p(extents), p(b.cum), int(tile_bounds[0]),
+                                         int(tile_bounds[1]), b.block_size, p(b.block_counts), p(b.tile_bins),
+                                         p(b.tile_start), p(stats), st)
+    _lib.check(rc, "gstex_tile_bucket_count")
+    b.stats_host = _pinned_stats()
+    b.stats_host.copy_(stats, non_blocking=True)
+    b.event = torch.cuda.Event()
+    b.event.record(torch.cuda.current_stream(dev))
+    return b
+
+
+def finish_binning(b: TileBinning):
+    """Second half: `(num_intersects, gaussian_ids_sorted, tile_bins)`.  Blocks the host until the sizes recorded by
+    `begin_binning` have arrived (not until the stream is idle); idempotent."""
+    if b.result is not None:
+        return b.result
+    dev = b.centers.device
+    i32 = dict(dtype=torch.int32, device=dev)
     lib = _lib.load()
 
     def general(num_intersects):
         if num_intersects < 1:
-            return num_intersects, torch.zeros((0,), **i32), torch.zeros((num_tiles, 2), **i32)
-        (_, _, _, ids_sorted, bins) = bin_and_sort_gaussians(num_points, num_intersects, centers, extents, depths, cum,
-                                                             tile_bounds, block_size)
+            return num_intersects, torch.zeros((0,), **i32), torch.zeros((b.num_tiles, 2), **i32)
+        (_, _, _, ids_sorted, bins) = bin_and_sort_gaussians(b.num_points, num_intersects, b.centers, b.extents, b.depths,
+                                                             b.cum, b.tile_bounds, b.block_size)
         return num_intersects, ids_sorted, bins
 
-    if num_tiles > lib.gstex_tile_bucket_max_tiles():
-        return general(int(total.item()))
-    block_counts = _workspace(lib.gstex_tile_bucket_scratch_bytes(num_tiles), dev)
-    small = torch.empty((num_tiles + 2,), **i32)  # tile_start | stats
-    tile_start, stats = small[:num_tiles], small[num_tiles:]
-    tile_bins = torch.empty((num_tiles, 2), **i32)
-    p, st = _lib.ptr, _lib.stream_ptr(dev)
-    with torch.cuda.device(dev):
-        rc = lib.gstex_tile_bucket_count(int(num_points), p(centers), p(extents), p(cum), int(tile_bounds[0]),
-                                         int(tile_bounds[1]), int(block_size), p(block_counts), p(tile_bins),
-                                         p(tile_start), p(stats), st)
-    _lib.check(rc, "gstex_tile_bucket_count")
-    num_intersects, max_list = stats.tolist()  # the one host sync of the binning stage
+    if not b.fast:
+        b.result = general(int(b.total.item()))
+        return b.result
+    b.event.synchronize()  # the one host wait of the binning stage
+    num_intersects, max_list = b.stats_host.tolist()
     if num_intersects < 1 or max_list > lib.gstex_tile_bucket_max_list():
-        return general(num_intersects)
+        b.result = general(num_intersects)
+        return b.result
     keys = torch.empty((num_intersects,), dtype=torch.int64, device=dev)
     ids_sorted = torch.empty((num_intersects,), **i32)
+    p = _lib.ptr
     with torch.cuda.device(dev):
-        rc = lib.gstex_tile_bucket_sort(int(num_points), int(num_intersects), int(max_list), p(centers), p(extents),
-                                        p(depths), p(cum), int(tile_bounds[0]), int(tile_bounds[1]), int(block_size),
-                                        p(block_counts), p(tile_start), p(tile_bins), p(keys), p(ids_sorted), st)
+        rc = lib.gstex_tile_bucket_sort(b.num_points, int(num_intersects), int(max_list), p(b.centers), p(b.extents),
+                                        p(b.depths), p(b.cum), int(b.tile_bounds[0]), int(b.tile_bounds[1]), b.block_size,
+                                        p(b.block_counts), p(b.tile_start), p(b.tile_bins), p(keys), p(ids_sorted),
+                                        _lib.stream_ptr(dev))
     _lib.check(rc, "gstex_tile_bucket_sort")
-    return num_intersects, ids_sorted, tile_bins
+    b.result = (num_intersects, ids_sorted, b.tile_bins)
+    b.block_counts = b.tile_start = None
+    return b.result
+
+
+def bin_gaussians_to_tiles(num_points: int, centers: Tensor, extents: Tensor, depths: Tensor, num_tiles_hit: Tensor,
+                           tile_bounds, block_size: int):
+    """What `texture_gaussians` needs from `compute_cumulative_intersects` + `bin_and_sort_gaussians`
+    (ref: utils.py:40-59,106-162): `(num_intersects, gaussian_ids_sorted (I,) int32, tile_bins (tiles,2) int32)`,
+    bit-identical to them, through the tile-bucket path (csrc/tile_bucket.cu) -- per-tile counts, one scan, a
+    shared-memory-cursor emit and a per-tile shared-memory sort by (depth bits, splat id) -- instead of a radix sort
+    of the whole list.  One blocking read of two ints (`num_intersects`, longest tile list) replaces the
+    reference's `.item()` (utils.py:58).  A tile list longer than the shared-memory capacity (or more tiles than
+    the counting kernels hold) sends the call down the general path.  = `finish_binning(begin_binning(...))`."""
+    return finish_binning(begin_binning(num_points, centers, extents, depths, num_tiles_hit, tile_bounds, block_size))

@@ -56,7 +56,9 @@ def test_python_surface_mirrors_reference():
     ref_sig = ["texture_info", "texture_dims", "centers", "extents", "depths", "num_tiles_hit", "colors", "opacity",
                "means", "scales", "glob_scale", "quats", "uv0", "umap", "vmap", "texture", "viewmat", "c2w", "fx", "fy",
                "cx", "cy", "img_height", "img_width", "block_width", "settings", "background", "use_torch_impl"]
-    assert list(inspect.signature(G.texture_gaussians).parameters) == ref_sig  # texture.py:14-43
+    params = inspect.signature(G.texture_gaussians).parameters
+    assert [k for k, v in params.items() if v.kind != v.KEYWORD_ONLY] == ref_sig  # texture.py:14-43
+    assert [k for k, v in params.items() if v.kind == v.KEYWORD_ONLY] == ["binning"]  # ours: multi-view pipelining hook
     assert list(inspect.signature(G.get_aabb_2d).parameters) == ["means", "scales", "glob_scale", "quats", "viewmat", "intrins"]
     assert list(inspect.signature(G.get_num_tiles_hit_2d).parameters) == ["centers", "extents", "img_height", "img_width", "block_width"]
     assert list(inspect.signature(G.project_points).parameters)[:3] == ["points", "viewmat", "intrins"]

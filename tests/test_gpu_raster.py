@@ -201,3 +201,32 @@ def test_pair_stream_is_recorded_and_overflow_is_flagged(backward_path):
         assert overflow == 0 and used > 0
     else:
         assert overflow == 1
+
+
+def test_prepared_binning_gives_identical_results():
+    """`texture_gaussians(..., binning=begin_binning(...))` (multi-view pipelining hook) == the plain call, bit for
+    bit, including when other work is enqueued between the two halves; a request can be finished twice."""
+    import gstex_b200 as G
+    from gstex_b200.synthetic import make_scene
+
+    s = make_scene("cfg2", n=20000, width=320, height=320)
+    sd = {k: (x.cuda() if isinstance(x, torch.Tensor) else x) for k, x in s.items()}
+    intr = (s["fx"], s["fy"], s["cx"], s["cy"])
+    H, W, bw = s["H"], s["W"], 16
+    _, depths, centers, extents, nth = G.project_bounds(sd["means"], sd["scales"], 1, sd["quats"], sd["viewmat"], intr,
+                                                        H, W, bw)
+    args = (s["texture_info"], sd["texture_dims"], centers, extents, depths, nth, sd["colors"], sd["opacities"],
+            sd["means"], sd["scales"], 1, sd["quats"], sd["uv0"], sd["umap"], sd["vmap"], sd["texture"], sd["viewmat"],
+            sd["c2w"], *intr, H, W, bw, s["settings"], sd["background"])
+    plain = G.texture_gaussians(*args)
+    tb = ((W + bw - 1) // bw, (H + bw - 1) // bw, 1)
+    h = G.begin_binning(s["N"], centers, extents, depths, nth, tb, bw)
+    junk = torch.randn(1 << 22, device="cuda").sort().values  # unrelated work between the halves
+    prepared = G.texture_gaussians(*args, binning=h)
+    for a, b in zip(plain, prepared):
+        assert torch.equal(a, b)
+    r1, r2 = G.finish_binning(h), G.finish_binning(h)
+    assert r1[0] == r2[0] and r1[1] is r2[1] and r1[2] is r2[2]
+    ref = G.bin_gaussians_to_tiles(s["N"], centers, extents, depths, nth, tb, bw)
+    assert ref[0] == r1[0] and torch.equal(ref[1], r1[1]) and torch.equal(ref[2], r1[2])
+    assert junk.numel() == 1 << 22
