@@ -47,6 +47,7 @@ _SIGNATURES = {
     "gstex_grad_scratch_bytes": (SZ, [I, ctypes.c_longlong]),
     "gstex_compute_sh_forward": (I, [I, I, I, P, P, P, P]),
     "gstex_compute_sh_backward": (I, [I, I, I, P, P, P, P]),
+    "gstex_texture_sample_forward": (I, [I, I, P, P, P, P, P]),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)

@@ -195,6 +195,15 @@ int gstex_compute_sh_forward(int n, int degree, int degrees_to_use, const float*
 int gstex_compute_sh_backward(int n, int degree, int degrees_to_use, const float* viewdirs, const float* v_colors,
                               float* v_coeffs, void* stream);
 
+/* ---- next row: jagged-texture sampling used by re-charting ------------------- */
+
+/* ref: cuda/csrc/texture_sample.cu:77-110 texture_sample_forward_tensor -> kernel :11-36.
+ * texture_dims (Q,3) int32 {h, w, start} of the chart each query reads, uvs (Q,2), texture (T,C) -> out (Q,C),
+ * every element written.  uv is clamped to [0,1]^2 (texture_sample.py:29-31).  Forward only: the reference's
+ * autograd backward returns no gradients (texture_sample.py:77-86). */
+int gstex_texture_sample_forward(int num_queries, int channels, const int32_t* texture_dims, const float* uvs,
+                                 const float* texture, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -23,7 +23,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _BUILD = os.path.join(_HERE, "_build")
 _SO = os.path.join(_BUILD, "libgstex_oracle.so")
 _SRCS = [os.path.join(_HERE, "gstex_oracle.c"), os.path.join(_HERE, "gstex_oracle_raster.c"),
-         os.path.join(_HERE, "gstex_oracle_sh.c")]
+         os.path.join(_HERE, "gstex_oracle_sh.c"), os.path.join(_HERE, "gstex_oracle_sample.c")]
 
 _lib = None
 
@@ -198,4 +198,20 @@ def spherical_harmonics_vjp(degrees_to_use: int, num_bases: int, viewdirs: np.nd
     f = ctypes.POINTER(ctypes.c_float)
     lib().orc_sh_backward(ctypes.c_int(n), ctypes.c_int(deg_from_sh(num_bases)), ctypes.c_int(int(degrees_to_use)),
                           viewdirs.ctypes.data_as(f), v_colors.ctypes.data_as(f), out.ctypes.data_as(f))
+    return out
+
+
+# ---- jagged-texture sampling (gstex_cuda/texture_sample.py:13-86 -> cuda/csrc/texture_sample.cu) ---------------
+
+def texture_sample(texture_info, texture_dims: np.ndarray, texture: np.ndarray, uvs: np.ndarray) -> np.ndarray:
+    """out (Q, C); ref: texture_sample.py:13-48 -> texture_sample_forward (texture_sample.cu:11-36)."""
+    texture_dims = np.ascontiguousarray(texture_dims, np.int32)
+    texture = np.ascontiguousarray(texture, np.float32)
+    uvs = np.ascontiguousarray(uvs, np.float32)
+    C = int(texture_info[2])
+    q = uvs.shape[0]
+    out = np.empty((q, C), np.float32)
+    f = ctypes.POINTER(ctypes.c_float)
+    lib().orc_texture_sample(ctypes.c_int(q), ctypes.c_int(C), texture_dims.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)),
+                             uvs.ctypes.data_as(f), texture.ctypes.data_as(f), out.ctypes.data_as(f))
     return out
