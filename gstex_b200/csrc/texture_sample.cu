@@ -1,5 +1,5 @@
 // texture_sample.cu -- bilinear sampling of a jagged texture at arbitrary (chart, uv) queries: the kernel behind the
-// reference's re-charting step (NS/models/gstex.py:841-895 resamples every texel of
+// reference's re-charting step (NS/models/jagged_texture.py:116-143 resamples every texel of
 // the new charts from the old ones).  Replaces texture_sample_forward (gstex_cuda/cuda/csrc/texture_sample.cu:11-36,
 // wrapper :77-110; helpers texture_helpers.cuh:155-237; Python gstex_cuda/texture_sample.py:13-86).  sm_100a.
 //

@@ -1,6 +1,6 @@
 """`texture_sample`, the drop-in for the reference's `gstex_cuda/texture_sample.py`
 (/root/reference/submodules/GStex_cuda/gstex_cuda/texture_sample.py:13-86): bilinear queries into a jagged texture,
-used by the model's re-charting (nerfstudio/models/gstex.py:841-895).  SURVEY.md section 8f, rank 3.
+used by the model's re-charting (nerfstudio/models/jagged_texture.py:116-143).  SURVEY.md section 8f, rank 3.
 """
 from __future__ import annotations
 
