@@ -27,7 +27,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-from gstex_b200.multiview import allreduce_gradients, shard_views  # noqa: E402
+from gstex_b200.multiview import GradientBucket, shard_views  # noqa: E402
 
 METRIC = "fwd+bwd Mpix/s, 1M textured splats @800x800 (project+bin+sort+forward+backward)"
 UNIT = "Mpix/s"
@@ -143,6 +143,7 @@ class Workload:
         self.H, self.W, self.bw = s["H"], s["W"], 16
         self.last_I = 0
         self.feeder = None
+        self.bucket = None  # multi-GPU: one flat gradient buffer, one all-reduce per step
 
     def prep_view(self, viewmat):
         """Projection + the asynchronous half of the binning of one view (no host synchronisation)."""
@@ -169,22 +170,31 @@ class Workload:
         self.torch.autograd.backward(list(outs), [v["v_out_img"], v["v_out_depth"], v["v_out_reg"], v["v_out_alpha"],
                                                   v["v_out_texture"], v["v_out_normal"]])
 
-    def zero_grad(self):
+    def zero_grad(self, world=1):
+        if world > 1:
+            if self.bucket is None:
+                self.bucket = GradientBucket(list(self.params.values()))
+            self.bucket.zero_()
+            return
         for p in self.params.values():
             p.grad = None
+
+    def reduce_grads(self, world):
+        if world > 1:
+            self.bucket.allreduce(world)
 
     def step(self, world):
         """All local views, fwd+bwd through the public API.  View i+1's projection and binning counts are launched
         between view i's forward and backward, so the host reads view i+1's `num_intersects` while the backward runs
         (the reference's blocking `.item()` per view would drain the GPU each time)."""
-        self.zero_grad()
+        self.zero_grad(world)
         nv = len(self.viewmats)
         pre = self.prep_view(self.viewmats[0])
         for i in range(nv):
             outs = self.forward_view(pre, self.viewmats[i], self.c2ws[i])
             pre = self.prep_view(self.viewmats[i + 1]) if i + 1 < nv else None
             self.backward_view(outs, self.v)
-        allreduce_gradients([p.grad for p in self.params.values()], world)
+        self.reduce_grads(world)
 
     def step_e2e(self, world, host):
         """Same step, but every view's inputs (camera, upstream-gradient images) come from pinned HOST memory
@@ -195,7 +205,7 @@ class Workload:
 
             self.feeder = HostViewFeeder(self.dev)
         fd, nv = self.feeder, len(self.viewmats)
-        self.zero_grad()
+        self.zero_grad(world)
         view_in = lambda i: {"vm": host["viewmats"][i], "c2w": host["c2ws"][i], "v": host["v"]}
         fd.prefetch(view_in(0))
         d = fd.take()
@@ -212,7 +222,7 @@ class Workload:
             fd.send_back(outs[0].detach(), host["out_img"][i])
             fd.send_back(outs[3].detach().sum(), host["scalar"][i])
             d = d_next
-        allreduce_gradients([p.grad for p in self.params.values()], world)
+        self.reduce_grads(world)
         fd.finish()  # the host consumes the result every step
 
     def make_host(self):
@@ -347,6 +357,8 @@ def main():
     if world > 1:
         import torch.distributed as dist
 
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner out of stdout: rank 0 prints ONE JSON line
         dist.init_process_group("nccl", device_id=dev)
 
     def barrier():
@@ -438,7 +450,7 @@ def main():
                                f"fwd+bwd, settings {s['settings']}", "views_per_gpu": args.views_per_gpu,
                    "intersections_view0": I, "mean_tile_list": I / tiles, "ms_per_view": ms_per_step / args.views_per_gpu,
                    "l2": "working set (texture+texel grads+records ~400 MB) exceeds the 126 MB L2; no explicit flush",
-                   "parallelism": f"views sharded over {world} GPU(s), NCCL all-reduce of 9 gradient tensors" if world > 1
+                   "parallelism": f"views sharded over {world} GPU(s), one NCCL all-reduce of the flat gradient bucket (9 tensors)" if world > 1
                    else "single GPU"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_ms, "wall_ms_per_step": wall * 1e3 / args.steps,

@@ -50,7 +50,20 @@ def _worker(rank, world, port, out_dir):
     for view in shard_views(NUM_VIEWS, rank, world):
         g = _view_grads(s, v, view)
         acc = g if acc is None else [a + b for a, b in zip(acc, g)]
+    # the same sums through the flat bucket: autograd accumulates into views of one buffer, one all-reduce
+    from gstex_b200.multiview import GradientBucket
+
+    params = [torch.zeros_like(a).requires_grad_(True) for a in acc]
+    bucket = GradientBucket(params)
+    bucket.zero_()
+    for view in shard_views(NUM_VIEWS, rank, world):
+        g = _view_grads(s, v, view)
+        torch.autograd.backward([(p * gi).sum() for p, gi in zip(params, g)])  # d/dp = gi, accumulated in place
+    assert all(p.grad is v for p, v in zip(params, bucket.views))
+    bucket.allreduce(world)
     allreduce_gradients(acc, world)
+    for p, a in zip(params, acc):
+        assert torch.allclose(p.grad, a, rtol=1e-12, atol=1e-14)
     torch.save(acc, os.path.join(out_dir, f"rank{rank}.pt"))
     dist.barrier()
     dist.destroy_process_group()
