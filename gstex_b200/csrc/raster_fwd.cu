@@ -21,6 +21,7 @@
 //   * REC kernels append one 32-byte item per contributing pair to the pair stream (pair_stream.cuh) that the
 //     stream backward consumes.
 #include <cstddef>
+#include <cstdlib>
 
 #include "pair_stream.cuh"
 #include "pipeline.cuh"
@@ -49,6 +50,7 @@ struct FwdParams {
     int32_t *final_idx, *depth_idx;
     uint32_t* unit_cursor;  // zeroed before the launch
     int units_per_tile, num_units;
+    int force_nocull;  // debugging / tests (GSTEX_DBG bit 4): evaluate every list entry for every unit
     StreamView sv;  // pair stream (REC kernels only)
 };
 
@@ -133,7 +135,7 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
         // ---- list walk state: cursor = next list position to test; ring indices are monotonic
         int cursor = range.x, last_pos = range.x - 1;
         int q_head = 0, q_issue = 0, q_tail = 0;
-        bool nocull = false, danger = false;
+        bool nocull = p.force_nocull != 0, danger = false;
         int gid_pf, gid_pf2;
         float4 box_pf;
         auto prime = [&]() {  // ids two rounds ahead, support boxes one round ahead of the round being tested
@@ -277,7 +279,7 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
                 // `danger` is warp-uniform and refreshed whenever a transmittance changed (a pixel that finishes
                 // without one may leave it set a little longer, which only delays the return to culling).
                 if (danger && !nocull) { flush = true; break; }
-                if (!danger) nocull = false;
+                if (!danger) nocull = p.force_nocull != 0;
                 const SplatRec& r = ws.rec[cur][i];
                 const int q = (q_head + i) & (kQueue - 1);
                 const float4 r0 = r.q[0], r1 = r.q[1], r2 = r.q[2], r3 = r.q[3], r4 = r.q[4];
@@ -489,6 +491,10 @@ extern "C" int gstex_texture_forward(int img_height, int img_width, int block_wi
     p.unit_cursor = ws_counters(workspace);
     p.units_per_tile = p.g.threads / 32;
     p.num_units = p.g.tiles_x * p.g.tiles_y * p.units_per_tile;
+    {
+        const char* env = getenv("GSTEX_DBG");
+        p.force_nocull = (env && (atoi(env) & 16)) ? 1 : 0;
+    }
     // persistent grid: enough CTAs to fill every SM at the kernels' occupancy, never more than there are units
     int grid = 148 * kFwdCtasPerSm;
     if (grid > (p.num_units + kFwdWarps - 1) / kFwdWarps) grid = (p.num_units + kFwdWarps - 1) / kFwdWarps;

@@ -230,3 +230,36 @@ def test_prepared_binning_gives_identical_results():
     ref = G.bin_gaussians_to_tiles(s["N"], centers, extents, depths, nth, tb, bw)
     assert ref[0] == r1[0] and torch.equal(ref[1], r1[1]) and torch.equal(ref[2], r1[2])
     assert junk.numel() == 1 << 22
+
+
+@pytest.mark.parametrize("cfg", [dict(name="cfg2", n=30000, size=320), dict(name="cfg5", n=250000, size=400),
+                                 dict(name="cfg1", n=3000, size=200)], ids=lambda c: c["name"])
+def test_culling_never_changes_a_result(cfg, monkeypatch):
+    """The support-box / live-rectangle culling of the forward is claimed to be exact: with culling
+    forced off (GSTEX_DBG bit 4: every list entry evaluated for every pixel block) every output must be
+    bit-identical, the index outputs included."""
+    import gstex_b200 as G
+    from gstex_b200.synthetic import make_scene
+
+    s = make_scene(cfg["name"], n=cfg["n"], width=cfg["size"], height=cfg["size"])
+    sd = {k: (x.cuda() if isinstance(x, torch.Tensor) else x) for k, x in s.items()}
+    intr = (s["fx"], s["fy"], s["cx"], s["cy"])
+    H, W, bw = s["H"], s["W"], 16
+    _, depths, centers, extents, nth = G.project_bounds(sd["means"], sd["scales"], 1, sd["quats"], sd["viewmat"], intr,
+                                                        H, W, bw)
+    args = (s["texture_info"], sd["texture_dims"], centers, extents, depths, nth, sd["colors"], sd["opacities"],
+            sd["means"], sd["scales"], 1, sd["quats"], sd["uv0"], sd["umap"], sd["vmap"], sd["texture"], sd["viewmat"],
+            sd["c2w"], *intr, H, W, bw, s["settings"], sd["background"])
+    culled = G.texture_gaussians(*args)
+    monkeypatch.setenv("GSTEX_DBG", "16")
+    plain = G.texture_gaussians(*args)
+    monkeypatch.delenv("GSTEX_DBG")
+    names = ["out_img", "out_depth", "out_reg", "out_alpha", "out_texture", "out_normal"]
+    for nm, a, b in zip(names, culled, plain):
+        assert torch.equal(a, b), f"{nm}: {int((a != b).sum())} elements differ between culled and unculled forward"
+
+
+def test_graft_smoke_entry():
+    import __graft_entry__ as g
+
+    g.smoke()
