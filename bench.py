@@ -143,7 +143,7 @@ class Workload:
         self.H, self.W, self.bw = s["H"], s["W"], 16
         self.last_I = 0
         self.feeder = None
-        self.bucket = None  # multi-GPU: one flat gradient buffer, one all-reduce per step
+        self.bucket = None  # one flat gradient buffer: fused accumulation, one all-reduce per step
 
     def prep_view(self, viewmat):
         """Projection + the asynchronous half of the binning of one view (no host synchronisation)."""
@@ -171,17 +171,15 @@ class Workload:
                                                   v["v_out_texture"], v["v_out_normal"]])
 
     def zero_grad(self, world=1):
-        if world > 1:
-            if self.bucket is None:
-                self.bucket = GradientBucket(list(self.params.values()))
-            self.bucket.zero_()
-            return
-        for p in self.params.values():
-            p.grad = None
+        """Gradients of all nine parameter tensors live in one flat bucket; the backward of every view adds into it
+        (GradientTargets), the step ends with one all-reduce when there are several ranks."""
+        if self.bucket is None:
+            self.bucket = GradientBucket(list(self.params.values()))
+            self.bucket.register()
+        self.bucket.zero_()
 
     def reduce_grads(self, world):
-        if world > 1:
-            self.bucket.allreduce(world)
+        self.bucket.allreduce(world)
 
     def step(self, world):
         """All local views, fwd+bwd through the public API.  View i+1's projection and binning counts are launched

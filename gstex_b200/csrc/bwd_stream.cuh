@@ -24,6 +24,7 @@ struct StreamBwdParams {
     float4 *tex_acc, *splat_acc;
     int n;
     long long num_texels;
+    int accumulate;  // unpack adds to the gradient tensors instead of overwriting them (zero_fill == 2)
 };
 
 static inline size_t grad_scratch_bytes(int n, long long num_texels) {

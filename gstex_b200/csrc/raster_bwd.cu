@@ -352,7 +352,7 @@ extern "C" int gstex_texture_backward(
         return GSTEX_E_BADARG;
     // zero_fill: the caller passed uninitialised gradient buffers (the reference allocates them with torch::zeros)
     auto zero = [&](bool also_stream_outputs) -> int {
-        if (!zero_fill || n == 0) return GSTEX_OK;
+        if (zero_fill != 1 || n == 0) return GSTEX_OK;  // 0: zeroed by the caller, 2: running sums to add to
         const size_t f = sizeof(float);
         GSTEX_CUDA_TRY(cudaMemsetAsync(v_uv0, 0, (size_t)n * 2 * f, st));
         GSTEX_CUDA_TRY(cudaMemsetAsync(v_umap, 0, (size_t)n * 3 * f, st));
@@ -405,7 +405,7 @@ extern "C" int gstex_texture_backward(
         sp.v_output_alpha = v_output_alpha; sp.v_output_texture = v_output_texture; sp.v_output_normal = v_output_normal;
         sp.v_colors = v_colors; sp.v_opacity = v_opacity; sp.v_means = v_means; sp.v_scales = v_scales;
         sp.v_quats = v_quats; sp.v_texture = v_texture;
-        sp.n = n; sp.num_texels = num_texels;
+        sp.n = n; sp.num_texels = num_texels; sp.accumulate = (zero_fill == 2);
         sp.tex_acc = reinterpret_cast<float4*>(grad_scratch); sp.splat_acc = sp.tex_acc + num_texels;
         // the unpack kernel of the stream path overwrites colors/opacity/means/scales/quats/texture gradients
         int rc = zero(false);

@@ -282,7 +282,9 @@ __global__ void __launch_bounds__(kStreamWarps * 32, 2) texture_backward_stream_
     }
 }
 
-// Unpacks the padded accumulators into the reference's gradient tensors (overwrites them).
+// Unpacks the padded accumulators into the reference's gradient tensors: overwrites them, or (ACC) adds to what they
+// hold -- the caller's running sum over the views of a step, which saves autograd's separate accumulation pass.
+template <bool ACC>
 __global__ void __launch_bounds__(256) unpack_grads_kernel(const float4* __restrict__ tex_acc, long long num_texels, int C,
                                                            const float4* __restrict__ splat_acc, int n,
                                                            float* __restrict__ v_texture, float* __restrict__ v_colors,
@@ -290,21 +292,25 @@ __global__ void __launch_bounds__(256) unpack_grads_kernel(const float4* __restr
                                                            float* __restrict__ v_scales, float* __restrict__ v_quats) {
     const long long stride = (long long)gridDim.x * blockDim.x;
     const long long t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    auto put = [](float* o, float v) { *o = ACC ? *o + v : v; };
     for (long long i = t0; i < num_texels; i += stride) {
         const float4 a = __ldcs(tex_acc + i);
         float* o = v_texture + i * C;
-        o[0] = a.x;
-        if (C > 1) o[1] = a.y;
-        if (C > 2) o[2] = a.z;
+        put(o, a.x);
+        if (C > 1) put(o + 1, a.y);
+        if (C > 2) put(o + 2, a.z);
     }
     for (long long i = t0; i < n; i += stride) {
         const float4 a = __ldcs(splat_acc + 4 * i), b = __ldcs(splat_acc + 4 * i + 1), c = __ldcs(splat_acc + 4 * i + 2),
                      d = __ldcs(splat_acc + 4 * i + 3);
-        v_colors[3 * i] = a.x; v_colors[3 * i + 1] = a.y; v_colors[3 * i + 2] = a.z;
-        v_opacity[i] = a.w;
-        v_means[3 * i] = b.x; v_means[3 * i + 1] = b.y; v_means[3 * i + 2] = b.z;
-        v_scales[3 * i] = c.x; v_scales[3 * i + 1] = c.y; v_scales[3 * i + 2] = 0.f;
-        reinterpret_cast<float4*>(v_quats)[i] = d;
+        put(v_colors + 3 * i, a.x); put(v_colors + 3 * i + 1, a.y); put(v_colors + 3 * i + 2, a.z);
+        put(v_opacity + i, a.w);
+        put(v_means + 3 * i, b.x); put(v_means + 3 * i + 1, b.y); put(v_means + 3 * i + 2, b.z);
+        put(v_scales + 3 * i, c.x); put(v_scales + 3 * i + 1, c.y);
+        if (!ACC) v_scales[3 * i + 2] = 0.f;
+        float4* q = reinterpret_cast<float4*>(v_quats) + i;
+        if (ACC) { const float4 o = *q; *q = make_float4(o.x + d.x, o.y + d.y, o.z + d.z, o.w + d.w); }
+        else *q = d;
     }
 }
 
@@ -319,8 +325,12 @@ int launch_backward_stream(const StreamBwdParams& p, cudaStream_t st) {
     const char* env = getenv("GSTEX_DBG");
     texture_backward_stream_kernel<<<blocks, kStreamWarps * 32, 0, st>>>(p, env ? atoi(env) : 0);
     GSTEX_LAUNCH_CHECK();
-    unpack_grads_kernel<<<148 * 8, 256, 0, st>>>(p.tex_acc, p.num_texels, p.C, p.splat_acc, p.n, p.v_texture, p.v_colors,
-                                                 p.v_opacity, p.v_means, p.v_scales, p.v_quats);
+    if (p.accumulate)
+        unpack_grads_kernel<true><<<148 * 8, 256, 0, st>>>(p.tex_acc, p.num_texels, p.C, p.splat_acc, p.n, p.v_texture,
+                                                           p.v_colors, p.v_opacity, p.v_means, p.v_scales, p.v_quats);
+    else
+        unpack_grads_kernel<false><<<148 * 8, 256, 0, st>>>(p.tex_acc, p.num_texels, p.C, p.splat_acc, p.n, p.v_texture,
+                                                            p.v_colors, p.v_opacity, p.v_means, p.v_scales, p.v_quats);
     GSTEX_LAUNCH_CHECK();
     return GSTEX_OK;
 }

@@ -152,6 +152,13 @@ class GradientBucket:
             if p.grad is not v:
                 p.grad = v
 
+    def register(self) -> None:
+        """Let `texture_gaussians`' backward add each view's gradients straight into the bucket
+        (`texture.GradientTargets`) instead of handing them to autograd's accumulation pass."""
+        from .texture import GradientTargets
+
+        GradientTargets.set(self.params, self.views)
+
     def allreduce(self, world: int, group=None) -> None:
         """Sum over the ranks (no-op for one rank).  Gradients produced outside autograd's in-place accumulation
         (a `p.grad` that was replaced) are copied back into the bucket first."""

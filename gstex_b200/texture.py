@@ -62,6 +62,46 @@ class PairStreamPolicy:
         st["pending"] = (host, ev)
 
 
+class GradientTargets:
+    """Opt-in fused gradient accumulation for multi-view steps (no counterpart in the reference).
+
+    `GradientTargets.set(params, grads)` registers, for leaf tensors passed to `texture_gaussians` as colors / opacity /
+    means / scales / quats / uv0 / umap / vmap / texture, the tensor their gradient is accumulated in (normally their
+    `.grad`, e.g. the views of a `multiview.GradientBucket`).  When all nine inputs of a call are registered, the
+    backward ADDS the view's gradients to those tensors inside its own unpack kernel (C ABI `zero_fill = 2`) and
+    returns `None` for them, so autograd's AccumulateGrad -- nine extra read-modify-write passes over 208 MB per view
+    at the headline size -- has nothing left to do.  The sums are bit-identical to autograd's.  `clear()` restores
+    the plain behaviour."""
+
+    _map = {}
+
+    @classmethod
+    def set(cls, params, grads) -> None:
+        m = {}
+        for p, g in zip(params, grads):
+            if g.shape != p.shape or g.dtype != torch.float32 or not g.is_contiguous() or g.device != p.device:
+                raise ValueError("GradientTargets: each target must be a contiguous fp32 tensor shaped like its parameter")
+            m[(p.data_ptr(), tuple(p.shape))] = g
+        cls._map = m
+
+    @classmethod
+    def clear(cls) -> None:
+        cls._map = {}
+
+    @classmethod
+    def lookup(cls, tensors):
+        """The nine targets if every tensor is registered, else None."""
+        if not cls._map:
+            return None
+        out = []
+        for t in tensors:
+            g = cls._map.get((t.data_ptr(), tuple(t.shape)))
+            if g is None:
+                return None
+            out.append(g)
+        return out
+
+
 def texture_gaussians(
     texture_info: Tuple[int, int, int],
     texture_dims: Tensor,
@@ -205,6 +245,9 @@ class _TextureGaussians(Function):
         ctx.settings = settings
         ctx.workspace = ws  # packed per-view records, valid as long as the inputs are unchanged
         ctx.pair_stream = pairs  # contributing pairs recorded by the forward (None: the backward recomputes)
+        # fused accumulation (GradientTargets): only when every gradient is wanted and every input is registered
+        ctx.grad_targets = (GradientTargets.lookup((colors, opacity, means, scales, quats, uv0, umap, vmap, texture))
+                            if all(ctx.needs_input_grad[i] for i in (6, 7, 8, 9, 11, 12, 13, 14, 15)) else None)
         ctx.save_for_backward(texture_dims, gaussian_ids_sorted, tile_bins, colors, opacity, means, scales, quats,
                               uv0, umap, vmap, texture, viewmat, c2w, background, final_Ts, final_idx, depth_idx,
                               out_reg_s)
@@ -231,16 +274,20 @@ class _TextureGaussians(Function):
         v_out_texture = grad_or_zero(v_out_texture, (H, W, C))
         v_out_normal = grad_or_zero(v_out_normal, (H, W, 3))
 
+        targets = ctx.grad_targets
+        if targets is not None:
+            (v_colors, v_opacity, v_means, v_scales, v_quats, v_uv0, v_umap, v_vmap, v_texture) = targets
         # uninitialised: the library defines every element (zero_fill=1), which saves nine memsets on the stream path
-        v_colors = torch.empty_like(colors)
-        v_opacity = torch.empty_like(opacity)
-        v_means = torch.empty_like(means)
-        v_scales = torch.empty_like(scales)
-        v_quats = torch.empty_like(quats)
-        v_uv0 = torch.empty_like(uv0)
-        v_umap = torch.empty_like(umap)
-        v_vmap = torch.empty_like(vmap)
-        v_texture = torch.empty_like(texture)
+        else:
+            v_colors = torch.empty_like(colors)
+            v_opacity = torch.empty_like(opacity)
+            v_means = torch.empty_like(means)
+            v_scales = torch.empty_like(scales)
+            v_quats = torch.empty_like(quats)
+            v_uv0 = torch.empty_like(uv0)
+            v_umap = torch.empty_like(umap)
+            v_vmap = torch.empty_like(vmap)
+            v_texture = torch.empty_like(texture)
         lib = _lib.load()
         ws = ctx.workspace
         p = _lib.ptr
@@ -259,7 +306,10 @@ class _TextureGaussians(Function):
                 p(v_out_alpha), p(v_out_texture), p(v_out_normal), p(v_colors), p(v_opacity), p(v_means),
                 p(v_scales), p(v_quats), p(v_uv0), p(v_umap), p(v_vmap), p(v_texture), p(ws), ws.numel(), 1,
                 p(pairs), pairs.numel() if pairs is not None else 0, p(scratch),
-                scratch.numel() if scratch is not None else 0, int(texture.shape[0]), 1, _lib.stream_ptr(dev))
+                scratch.numel() if scratch is not None else 0, int(texture.shape[0]), 2 if targets is not None else 1,
+                _lib.stream_ptr(dev))
         _lib.check(rc, "gstex_texture_backward")
+        if targets is not None:  # already added to the registered tensors
+            return (None,) * 28
         return (None, None, None, None, None, None, v_colors, v_opacity, v_means, v_scales, None, v_quats, v_uv0,
                 v_umap, v_vmap, v_texture, None, None, None, None, None, None, None, None, None, None, None, None)

@@ -161,8 +161,10 @@ int gstex_texture_forward(int img_height, int img_width, int block_width, int ch
  * `grad_scratch` (gstex_grad_scratch_bytes(n, num_texels) bytes, 16-byte aligned; needed by the stream path,
  * may be NULL otherwise): padded accumulators the stream kernel reduces into with 16-byte vector atomics before
  * an unpack kernel writes the reference's gradient tensors.  num_texels = rows of `texture`.
- * zero_fill != 0: the nine gradient buffers are uninitialised on entry and the library defines every element
- * (memsets what a kernel does not overwrite); zero_fill == 0: they are zero-filled by the caller.  With the
+ * zero_fill == 1: the nine gradient buffers are uninitialised on entry and the library defines every element
+ * (memsets what a kernel does not overwrite); zero_fill == 0: they are zero-filled by the caller; zero_fill == 2:
+ * they hold running sums (a multi-view step's accumulated gradients) and this view's gradients are ADDED to them
+ * -- what autograd's AccumulateGrad would do in a separate pass over all nine tensors.  With zero_fill 0/1 and the
  * stream path the colors/opacity/means/scales/quats/texture gradients are overwritten, not accumulated into
  * (on the zero-filled buffers the contract asks for, that is the same thing). */
 size_t gstex_grad_scratch_bytes(int n, long long num_texels);

@@ -263,3 +263,53 @@ def test_graft_smoke_entry():
     import __graft_entry__ as g
 
     g.smoke()
+
+
+def test_fused_gradient_accumulation_matches_autograd():
+    """GradientTargets / GradientBucket: two views accumulated by the backward's own unpack kernel (zero_fill = 2)
+    give the sums autograd's AccumulateGrad gives over the same two views (the additions are the same; the backward
+    itself reduces with floating-point atomics, so two runs agree to rounding, not bit for bit)."""
+    import gstex_b200 as G
+    from gstex_b200.multiview import GradientBucket
+    from gstex_b200.synthetic import make_scene, make_upstream_grads
+    from gstex_b200.texture import GradientTargets
+
+    s = make_scene("cfg2", n=20000, width=256, height=256, views=2)
+    v = {k: x.cuda() for k, x in make_upstream_grads(s).items()}
+    sd = {k: (x.cuda() if isinstance(x, torch.Tensor) else x) for k, x in s.items()}
+    intr = (s["fx"], s["fy"], s["cx"], s["cy"])
+    H, W, bw = s["H"], s["W"], 16
+    keys = ["colors", "opacities", "means", "scales", "quats", "uv0", "umap", "vmap", "texture"]
+
+    def run(fused):
+        params = [sd[k].clone().requires_grad_(True) for k in keys]
+        pd = dict(zip(keys, params))
+        bucket = None
+        if fused:
+            bucket = GradientBucket(params)
+            bucket.zero_()
+            bucket.register()
+        for i in range(2):
+            vm, c2w = s["viewmats"][i].cuda().contiguous(), s["c2ws"][i].cuda().contiguous()
+            _, depths, centers, extents, nth = G.project_bounds(pd["means"].detach(), pd["scales"].detach(), 1,
+                                                                pd["quats"].detach(), vm, intr, H, W, bw)
+            outs = G.texture_gaussians(s["texture_info"], sd["texture_dims"], centers, extents, depths, nth, pd["colors"],
+                                       pd["opacities"], pd["means"], pd["scales"], 1, pd["quats"], pd["uv0"], pd["umap"],
+                                       pd["vmap"], pd["texture"], vm, c2w, *intr, H, W, bw, s["settings"], sd["background"])
+            torch.autograd.backward(list(outs), [v["v_out_img"], v["v_out_depth"], v["v_out_reg"], v["v_out_alpha"],
+                                                 v["v_out_texture"], v["v_out_normal"]])
+        if fused:
+            assert all(p.grad is g for p, g in zip(params, bucket.views))
+            bucket.allreduce(1)
+        GradientTargets.clear()
+        return [p.grad.clone() for p in params]
+
+    try:
+        plain, fused = run(False), run(True)
+    finally:
+        GradientTargets.clear()
+    for k, a, b in zip(keys, plain, fused):
+        scale = float(a.abs().max())
+        err = float((a - b).abs().max())
+        assert err <= 2e-5 * scale + 1e-30, f"{k}: fused accumulation differs from autograd's ({err:.3e} at scale {scale:.3e})"
+    assert float(plain[8].abs().max()) > 0 and float(plain[2].abs().max()) > 0
