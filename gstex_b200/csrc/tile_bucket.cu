@@ -403,12 +403,13 @@ extern "C" int gstex_tile_bucket_sort(int n, int num_intersects, int max_list, c
     while (id_bits < 32 && (1ll << id_bits) < (long long)n) ++id_bits;
     const int2* bins = reinterpret_cast<const int2*>(tile_bins);
     const unsigned long long* k64 = reinterpret_cast<const unsigned long long*>(keys);
-    // size classes, so that the many short lists do not pay the shared memory / registers of the longest one
-    {
-        const int hi = max_list < kLsSmallCap ? max_list : kLsSmallCap;
+    // size classes: a view whose lists are all short takes the 8-warp kernel (24 KB of shared memory per block); a
+    // view with long lists takes one 16-warp launch for all tiles -- the short lists then fill the tail the long
+    // ones leave (two launches, one per class, measured 20 us slower at the headline size)
+    if (max_list <= kLsSmallCap) {
         tile_local_sort_kernel<kLsSmallW, kLsSmallK>
             <<<(int)num_tiles, kLsSmallW * 32, ls_smem_bytes(kLsSmallW, kLsSmallK), st>>>(bins, k64, gaussian_ids_sorted,
-                                                                                          id_bits, 1, hi);
+                                                                                          id_bits, 1, max_list);
         GSTEX_LAUNCH_CHECK();
     }
     if (max_list > kLsSmallCap) {
@@ -418,7 +419,7 @@ extern "C" int gstex_tile_bucket_sort(int n, int num_intersects, int max_list, c
         GSTEX_CUDA_TRY(cudaFuncSetAttribute(tile_local_sort_kernel<kLsLargeW, KK>,                                     \
                                             cudaFuncAttributeMaxDynamicSharedMemorySize, ls_smem_bytes(kLsLargeW, KK))); \
         tile_local_sort_kernel<kLsLargeW, KK><<<(int)num_tiles, kLsLargeW * 32, ls_smem_bytes(kLsLargeW, KK), st>>>(   \
-            bins, k64, gaussian_ids_sorted, id_bits, kLsSmallCap + 1, max_list);                                       \
+            bins, k64, gaussian_ids_sorted, id_bits, 1, max_list);                                       \
     } while (0)
         if (max_list <= kLsLargeW * 32 * 12) GSTEX_LS_LAUNCH(12);
         else if (max_list <= kLsLargeW * 32 * 16) GSTEX_LS_LAUNCH(16);
