@@ -72,6 +72,7 @@ struct FwdWarpShared {
 struct FwdShared {
     FwdWarpShared w[kFwdWarps];
     Camera cam;
+    float4 origin;  // camera position: re-read from here in every pair evaluation instead of living in registers
 };
 
 template <int CMAX, bool REC>
@@ -84,6 +85,7 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     FwdWarpShared& ws = sm.w[warp];
     load_camera(sm.cam, p.viewmat, p.c2w, p.fx, p.fy, p.cx, p.cy);
+    if (threadIdx.x == 32) sm.origin = make_float4(__ldg(p.c2w + 3), __ldg(p.c2w + 7), __ldg(p.c2w + 11), 0.f);
     if (lane == 0) {
         mbar_init(&ws.bar[0], 1);
         mbar_init(&ws.bar[1], 1);
@@ -96,7 +98,6 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
     const int C = p.C;
     const unsigned lt_mask = (1u << lane) - 1u;
     const float4 no_box = make_float4(1.f, 1.f, 0.f, 0.f);
-    const float bg0 = __ldg(p.background), bg1 = __ldg(p.background + 1), bg2 = __ldg(p.background + 2);
     unsigned phase = 0;  // bit b: parity to wait for on bar[b]
     bool rec_ok = REC && (*(volatile uint32_t*)&p.sv.hdr->overflow == 0u);
 
@@ -119,7 +120,6 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
             X0 = (float)(tile_x * g.bw + x0) + 0.5f; X1 = (float)(tile_x * g.bw + x1) + 0.5f;
             Y0 = (float)(tile_y * g.bw + y0) + 0.5f; Y1 = (float)(tile_y * g.bw + y1) + 0.5f;
         }
-        const int ipx = tile_x * g.bw + lx, ipy = tile_y * g.bw + ly;
 
         bool done = !pix.inside;
         float T = 1.f;
@@ -283,7 +283,18 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
                 const SplatRec& r = ws.rec[cur][i];
                 const int q = (q_head + i) & (kQueue - 1);
                 const float4 r0 = r.q[0], r1 = r.q[1], r2 = r.q[2], r3 = r.q[3], r4 = r.q[4];
-                const PairEval e = eval_pair(pix, r0, r1, r2, r3, r4, use_blur);
+                // The ray origin is the same for every pixel; keeping its three floats alive across the whole loop cost
+                // a local-memory spill whose reload stalled every iteration (7 % of the kernel's stall samples).  A
+                // volatile shared-memory read at the top of the iteration keeps them short-lived instead.
+                Pixel pe = pix;
+                {
+                    float ox, oy, oz, ow;
+                    asm volatile("ld.volatile.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                                 : "=f"(ox), "=f"(oy), "=f"(oz), "=f"(ow)
+                                 : "r"((unsigned)__cvta_generic_to_shared(&sm.origin)));
+                    pe.origin = make_float3(ox, oy, oz);
+                }
+                const PairEval e = eval_pair(pe, r0, r1, r2, r3, r4, use_blur);
                 const float next_T = T * (1.f - e.alpha);
 #ifdef GSTEX_STATS
                 {
@@ -384,6 +395,7 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
             cur ^= 1;
             {   // cull the rest of the list against the rectangle of the pixels that are still alive
                 const int big = 1 << 30;
+                const int ipx = (int)pix.px, ipy = (int)pix.py;  // pixel centre = index + 0.5
                 const int ax0 = __reduce_min_sync(0xffffffffu, done ? big : ipx), ax1 = __reduce_max_sync(0xffffffffu, done ? -big : ipx);
                 const int ay0 = __reduce_min_sync(0xffffffffu, done ? big : ipy), ay1 = __reduce_max_sync(0xffffffffu, done ? -big : ipy);
                 X0 = (float)ax0 + 0.5f; X1 = (float)ax1 + 0.5f; Y0 = (float)ay0 + 0.5f; Y1 = (float)ay1 + 0.5f;
@@ -400,6 +412,7 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
             if (w == 0 && lane >= p.units_per_tile && lane < kUnitsPerTile) p.sv.units[unit0 + lane] = make_int2(-1, 0);
         }
         if (pix.inside) {
+            const float bg0 = __ldg(p.background), bg1 = __ldg(p.background + 1), bg2 = __ldg(p.background + 2);
             const int id = pix.pix_id;
             p.final_Ts[id] = T;
             p.final_idx[id] = cur_idx;
