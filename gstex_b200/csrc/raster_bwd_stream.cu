@@ -198,7 +198,16 @@ __global__ void __launch_bounds__(kStreamWarps * 32, 2) texture_backward_stream_
             // Only pairs of the SAME pixel must be ordered: rank them within their pixel (later lane = later in the
             // list = processed first) and take one step per rank instead of one per segment.
             {
-                const unsigned same = __match_any_sync(0xffffffffu, valid ? pl : 32 + lane);
+                // lanes holding a pair of the same pixel: five ballots (MATCH.ANY stalled this point for ~5 % of the
+                // kernel's samples)
+                unsigned same = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+                for (int bit = 0; bit < 5; ++bit) {
+                    const bool on = (pl >> bit) & 1;
+                    const unsigned bal = __ballot_sync(0xffffffffu, on);
+                    same &= on ? bal : ~bal;
+                }
+                if (!valid) same = 1u << lane;
                 const int rank = __popc(lane == 31 ? 0u : (same >> (lane + 1)));
                 const int steps = __reduce_max_sync(0xffffffffu, rank) + 1;
                 for (int s = 0; s < ((dbg & 4) ? 1 : steps); ++s) {
