@@ -35,13 +35,26 @@ enum PixField {
     F_VDEP, F_VREG, F_TS0, F_TS1, F_TS2, F_DFINAL, F_VTRUN, F_COUNT
 };
 
+constexpr int kRecQuads = 8;  // staged per splat: SplatRec quads 0..5 + SplatRecBwd (quat, aux)
+
 struct StreamShared {
     Camera cam;
     float tab[kStreamWarps][F_COUNT][32];
+    // records of the splats of the current / next batch, one slot per segment (run of lanes holding the same
+    // splat), filled one batch ahead with cp.async by the segment's head lane
+    float4 rs[kStreamWarps][2][32][kRecQuads];
 };
 
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all_but_one() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+
 __global__ void __launch_bounds__(kStreamWarps * 32, 2) texture_backward_stream_kernel(const StreamBwdParams p, const int dbg) {
-    __shared__ StreamShared sm;
+    extern __shared__ __align__(16) unsigned char stream_smem[];
+    StreamShared& sm = *reinterpret_cast<StreamShared*>(stream_smem);
     if (*(volatile uint32_t*)&p.sv.hdr->overflow != 0u) return;  // the recompute kernel handles this view
     const RasterGeom g = p.g;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -53,6 +66,7 @@ __global__ void __launch_bounds__(kStreamWarps * 32, 2) texture_backward_stream_
     const int C = p.C;
     const float3 origin = make_float3(sm.cam.c2w[3], sm.cam.c2w[7], sm.cam.c2w[11]);
     float (*tab)[32] = sm.tab[warp];
+    float4 (*rs)[32][kRecQuads] = sm.rs[warp];
     const float bg0 = __ldg(p.background), bg1 = __ldg(p.background + 1), bg2 = __ldg(p.background + 2);
 
     while (true) {
@@ -111,31 +125,52 @@ __global__ void __launch_bounds__(kStreamWarps * 32, 2) texture_backward_stream_
             if ((load_b & 3) == 0 && load_b > 0) load_chunk = __ldg(p.sv.chunk_prev + load_chunk);
             --load_b;
         };
+        // Segments = runs of lanes holding the same splat (same sorted-list position).  The segment structure of a
+        // batch is worked out one batch ahead, when its items are already in registers, and each segment's head
+        // lane starts the copy of the splat's record into the slot of that segment (cp.async, 8 x 16 B), so the
+        // gather latency overlaps the previous batch's math instead of stalling the first use of the record.
+        auto stage = [&](const float4& it0, int buf, int& seg_o, unsigned& heads_o) {
+            const int idx_n = __float_as_int(it0.y);  // invalid lanes: distinct negative values (own segments)
+            const int idx_p = __shfl_up_sync(0xffffffffu, idx_n, 1);
+            const bool head_n = (lane == 0) || (idx_n != idx_p);
+            heads_o = __ballot_sync(0xffffffffu, head_n);
+            seg_o = __popc(heads_o & (0xffffffffu >> (31 - lane))) - 1;
+            if (head_n && idx_n >= 0) {
+                const uint32_t g_n = __float_as_uint(it0.x) >> 5;
+                const SplatRec* src = p.recs + g_n;
+                const SplatRecBwd* srb = p.recs_bwd + g_n;
+                float4* dst = rs[buf][seg_o];
+#pragma unroll
+                for (int k = 0; k < 6; ++k) cp_async16(dst + k, &src->q[k]);
+                cp_async16(dst + 6, &srb->quat);
+                cp_async16(dst + 7, &srb->aux);
+            }
+            cp_async_commit();
+        };
         fetch(n0[0], n1[0]);
         fetch(n0[1], n1[1]);
+        int buf = 0, seg = 0, seg_nxt = 0;
+        unsigned heads = 0u, heads_nxt = 0u;
+        __syncwarp();  // the previous unit's reads of the record slots are done
+        stage(n0[0], buf, seg, heads);
         for (int b = (cnt - 1) >> 5; b >= 0; --b) {
             const int i = (b << 5) + lane;
             const bool valid = i < cnt;
             const float4 w0 = n0[0], w1 = n1[0];
             n0[0] = n0[1]; n1[0] = n1[1];
-            if (b > 0 && __float_as_int(n0[0].y) >= 0) {  // records of batch b-1 -> L1
-                const uint32_t g_next = __float_as_uint(n0[0].x) >> 5;
-                prefetch_l1(p.recs + g_next);
-                prefetch_l1(p.recs_bwd + g_next);
-            }
+            if (b > 0) stage(n0[0], buf ^ 1, seg_nxt, heads_nxt);  // records of batch b-1
+            else cp_async_commit();                                 // keeps the group count uniform
             fetch(n0[1], n1[1]);
             const uint32_t gl = __float_as_uint(w0.x);
             const int pl = (int)(gl & 31u), gid = (int)(gl >> 5);
-            const int idx = __float_as_int(w0.y);  // invalid lanes: distinct negative values (own segments)
+            const int idx = __float_as_int(w0.y);
             const float T = w0.z, u = w0.w, vv = w1.x;
-
-            // segments = runs of lanes holding the same splat (same sorted-list position)
-            const int idx_prev = __shfl_up_sync(0xffffffffu, idx, 1);
-            const bool head = (lane == 0) || (idx != idx_prev);
-            const unsigned heads = __ballot_sync(0xffffffffu, head);
-            const int seg = __popc(heads & (0xffffffffu >> (31 - lane))) - 1;
+            const bool head = (heads >> lane) & 1u;
             const unsigned later = (lane == 31) ? 0u : (heads >> (lane + 1));
             const int seg_end = later ? lane + __ffs(later) - 1 : 31;
+            cp_async_wait_all_but_one();  // this batch's records have landed (the next batch's may be in flight)
+            __syncwarp();
+            const float4* rq = rs[buf][valid ? seg : 0];
 
             float v[13];
 #pragma unroll
@@ -143,9 +178,7 @@ __global__ void __launch_bounds__(kStreamWarps * 32, 2) texture_backward_stream_
             // values the sequential step needs
             float alpha = 0.f, v_vis = 0.f, v_weight = 0.f, v_alpha = 0.f;
             // record + pixel (gathered; lanes of one segment read the same record)
-            const SplatRec* rp = p.recs + (valid ? gid : 0);
-            const float4 r0 = __ldg(&rp->q[0]), r1 = __ldg(&rp->q[1]), r2 = __ldg(&rp->q[2]), r3 = __ldg(&rp->q[3]),
-                         r4 = __ldg(&rp->q[4]), r5 = __ldg(&rp->q[5]);
+            const float4 r0 = rq[0], r1 = rq[1], r2 = rq[2], r3 = rq[3], r4 = rq[4], r5 = rq[5];
             Pixel pix;
             pix.origin = origin;
             pix.ray = make_float3(tab[F_RAYX][pl], tab[F_RAYY][pl], tab[F_RAYZ][pl]);
@@ -223,8 +256,7 @@ __global__ void __launch_bounds__(kStreamWarps * 32, 2) texture_backward_stream_
                 }
             }
             if (valid) {
-                const SplatRecBwd* rbp = p.recs_bwd + gid;
-                const float4 rbq = __ldg(&rbp->quat), rba = __ldg(&rbp->aux);
+                const float4 rbq = rq[6], rba = rq[7];
                 const float3 v_normal_local = make_float3(vis * v_out_normal.x, vis * v_out_normal.y, vis * v_out_normal.z);
                 // texture.cu:672-707
                 const float v_sigma = e.blur ? 0.f : -r1.w * e.ex * v_alpha;
@@ -287,6 +319,8 @@ __global__ void __launch_bounds__(kStreamWarps * 32, 2) texture_backward_stream_
                 red_add_v4(acc + 2, v[7], v[8], 0.f, 0.f);
                 red_add_v4(acc + 3, v[9], v[10], v[11], v[12]);
             }
+            __syncwarp();  // every lane has read this batch's record slots before they are refilled
+            buf ^= 1; seg = seg_nxt; heads = heads_nxt;
         }
     }
 }
@@ -332,7 +366,9 @@ int launch_backward_stream(const StreamBwdParams& p, cudaStream_t st) {
     if (blocks > need) blocks = need;
     if (blocks < 1) blocks = 1;
     const char* env = getenv("GSTEX_DBG");
-    texture_backward_stream_kernel<<<blocks, kStreamWarps * 32, 0, st>>>(p, env ? atoi(env) : 0);
+    GSTEX_CUDA_TRY(cudaFuncSetAttribute(texture_backward_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)sizeof(StreamShared)));
+    texture_backward_stream_kernel<<<blocks, kStreamWarps * 32, sizeof(StreamShared), st>>>(p, env ? atoi(env) : 0);
     GSTEX_LAUNCH_CHECK();
     if (p.accumulate)
         unpack_grads_kernel<true><<<148 * 8, 256, 0, st>>>(p.tex_acc, p.num_texels, p.C, p.splat_acc, p.n, p.v_texture,
