@@ -21,10 +21,11 @@ struct StreamBwdParams {
     StreamView sv;
     // padded accumulators (grad scratch): texel gradients as (T,4), splat gradients as (N,16) floats:
     // [colors3 opacity | means3 - | scales.xy - - | quats4]
+    // The scratch is all-zero between calls: the unpack kernel clears exactly what the stream kernel wrote.
     float4 *tex_acc, *splat_acc;
     int n;
     long long num_texels;
-    int accumulate;  // unpack adds to the gradient tensors instead of overwriting them (zero_fill == 2)
+    int scratch_clean;  // the caller vouches the scratch is as a previous call left it: skip the clear
 };
 
 static inline size_t grad_scratch_bytes(int n, long long num_texels) {

@@ -347,6 +347,9 @@ extern "C" int gstex_texture_backward(
         return GSTEX_E_BADARG;
     if (settings & ~GSTEX_SETTINGS_SUPPORTED) return GSTEX_E_UNSUPPORTED;
     if (channels < 1 || channels > GSTEX_MAX_CHANNELS) return GSTEX_E_UNSUPPORTED;
+    if (zero_fill < 0 || zero_fill > 7 || (zero_fill & 3) == 3) return GSTEX_E_BADARG;
+    const int scratch_clean = (zero_fill & GSTEX_SCRATCH_CLEAN) != 0;
+    zero_fill &= 3;
     if (zero_fill && (num_texels < 0 || (n > 0 && (!v_colors || !v_opacity || !v_means || !v_scales || !v_quats ||
                                                     !v_uv0 || !v_umap || !v_vmap || !v_texture))))
         return GSTEX_E_BADARG;
@@ -405,10 +408,10 @@ extern "C" int gstex_texture_backward(
         sp.v_output_alpha = v_output_alpha; sp.v_output_texture = v_output_texture; sp.v_output_normal = v_output_normal;
         sp.v_colors = v_colors; sp.v_opacity = v_opacity; sp.v_means = v_means; sp.v_scales = v_scales;
         sp.v_quats = v_quats; sp.v_texture = v_texture;
-        sp.n = n; sp.num_texels = num_texels; sp.accumulate = (zero_fill == 2);
+        sp.n = n; sp.num_texels = num_texels; sp.scratch_clean = scratch_clean;
         sp.tex_acc = reinterpret_cast<float4*>(grad_scratch); sp.splat_acc = sp.tex_acc + num_texels;
-        // the unpack kernel of the stream path overwrites colors/opacity/means/scales/quats/texture gradients
-        int rc = zero(false);
+        // the unpack kernel of the stream path adds to the gradients wherever this view contributed
+        int rc = zero(true);
         if (rc != GSTEX_OK) return rc;
         rc = launch_backward_stream(sp, st);
         if (rc != GSTEX_OK) return rc;

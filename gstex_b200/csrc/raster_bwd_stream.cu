@@ -325,42 +325,48 @@ __global__ void __launch_bounds__(kStreamWarps * 32, 2) texture_backward_stream_
     }
 }
 
-// Unpacks the padded accumulators into the reference's gradient tensors: overwrites them, or (ACC) adds to what they
-// hold -- the caller's running sum over the views of a step, which saves autograd's separate accumulation pass.
-template <bool ACC>
-__global__ void __launch_bounds__(256) unpack_grads_kernel(const float4* __restrict__ tex_acc, long long num_texels, int C,
-                                                           const float4* __restrict__ splat_acc, int n,
+// Moves the padded accumulators into the reference's gradient tensors and hands the scratch back all-zero.  The
+// accumulators are swept once, coalesced; only words that are non-zero -- a view reaches about a third of the splats
+// and of their texels -- are cleared again and ADDED to the gradient tensors, which hold zeros (zero_fill 0/1) or the
+// caller's running sum over the views of a step (zero_fill 2).  So no full-size clear precedes the stream kernel and
+// the gradient tensors are only touched where this view has something to add.
+__global__ void __launch_bounds__(256) unpack_grads_kernel(float4* __restrict__ tex_acc, long long num_texels, int C,
+                                                           float4* __restrict__ splat_acc, int n,
                                                            float* __restrict__ v_texture, float* __restrict__ v_colors,
                                                            float* __restrict__ v_opacity, float* __restrict__ v_means,
                                                            float* __restrict__ v_scales, float* __restrict__ v_quats) {
     const long long stride = (long long)gridDim.x * blockDim.x;
     const long long t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    auto put = [](float* o, float v) { *o = ACC ? *o + v : v; };
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    auto any = [](const float4& a) { return a.x != 0.f || a.y != 0.f || a.z != 0.f || a.w != 0.f; };
     for (long long i = t0; i < num_texels; i += stride) {
-        const float4 a = __ldcs(tex_acc + i);
+        const float4 a = tex_acc[i];
+        if (!any(a)) continue;
+        tex_acc[i] = z;
         float* o = v_texture + i * C;
-        put(o, a.x);
-        if (C > 1) put(o + 1, a.y);
-        if (C > 2) put(o + 2, a.z);
+        o[0] += a.x;
+        if (C > 1) o[1] += a.y;
+        if (C > 2) o[2] += a.z;
     }
     for (long long i = t0; i < n; i += stride) {
-        const float4 a = __ldcs(splat_acc + 4 * i), b = __ldcs(splat_acc + 4 * i + 1), c = __ldcs(splat_acc + 4 * i + 2),
-                     d = __ldcs(splat_acc + 4 * i + 3);
-        put(v_colors + 3 * i, a.x); put(v_colors + 3 * i + 1, a.y); put(v_colors + 3 * i + 2, a.z);
-        put(v_opacity + i, a.w);
-        put(v_means + 3 * i, b.x); put(v_means + 3 * i + 1, b.y); put(v_means + 3 * i + 2, b.z);
-        put(v_scales + 3 * i, c.x); put(v_scales + 3 * i + 1, c.y);
-        if (!ACC) v_scales[3 * i + 2] = 0.f;
+        float4* acc = splat_acc + 4 * i;
+        const float4 a = acc[0], b = acc[1], c = acc[2], d = acc[3];
+        if (!(any(a) || any(b) || any(c) || any(d))) continue;
+        acc[0] = z; acc[1] = z; acc[2] = z; acc[3] = z;
+        v_colors[3 * i] += a.x; v_colors[3 * i + 1] += a.y; v_colors[3 * i + 2] += a.z;
+        v_opacity[i] += a.w;
+        v_means[3 * i] += b.x; v_means[3 * i + 1] += b.y; v_means[3 * i + 2] += b.z;
+        v_scales[3 * i] += c.x; v_scales[3 * i + 1] += c.y;
         float4* q = reinterpret_cast<float4*>(v_quats) + i;
-        if (ACC) { const float4 o = *q; *q = make_float4(o.x + d.x, o.y + d.y, o.z + d.z, o.w + d.w); }
-        else *q = d;
+        const float4 o = *q;
+        *q = make_float4(o.x + d.x, o.y + d.y, o.z + d.z, o.w + d.w);
     }
 }
 
 int launch_backward_stream(const StreamBwdParams& p, cudaStream_t st) {
     // the work counter is the only state the backward owns in the header
     GSTEX_CUDA_TRY(cudaMemsetAsync(&p.sv.hdr->next_unit, 0, sizeof(uint32_t), st));
-    GSTEX_CUDA_TRY(cudaMemsetAsync(p.tex_acc, 0, grad_scratch_bytes(p.n, p.num_texels), st));
+    if (!p.scratch_clean) GSTEX_CUDA_TRY(cudaMemsetAsync(p.tex_acc, 0, grad_scratch_bytes(p.n, p.num_texels), st));
     int blocks = 148 * 2;
     const int need = (p.sv.num_units + kStreamWarps - 1) / kStreamWarps;
     if (blocks > need) blocks = need;
@@ -370,12 +376,8 @@ int launch_backward_stream(const StreamBwdParams& p, cudaStream_t st) {
                                         (int)sizeof(StreamShared)));
     texture_backward_stream_kernel<<<blocks, kStreamWarps * 32, sizeof(StreamShared), st>>>(p, env ? atoi(env) : 0);
     GSTEX_LAUNCH_CHECK();
-    if (p.accumulate)
-        unpack_grads_kernel<true><<<148 * 8, 256, 0, st>>>(p.tex_acc, p.num_texels, p.C, p.splat_acc, p.n, p.v_texture,
-                                                           p.v_colors, p.v_opacity, p.v_means, p.v_scales, p.v_quats);
-    else
-        unpack_grads_kernel<false><<<148 * 8, 256, 0, st>>>(p.tex_acc, p.num_texels, p.C, p.splat_acc, p.n, p.v_texture,
-                                                            p.v_colors, p.v_opacity, p.v_means, p.v_scales, p.v_quats);
+    unpack_grads_kernel<<<148 * 8, 256, 0, st>>>(p.tex_acc, p.num_texels, p.C, p.splat_acc, p.n, p.v_texture, p.v_colors,
+                                                  p.v_opacity, p.v_means, p.v_scales, p.v_quats);
     GSTEX_LAUNCH_CHECK();
     return GSTEX_OK;
 }

@@ -17,6 +17,9 @@ from torch.autograd import Function
 from . import _lib
 from .utils import TileBinning, bin_gaussians_to_tiles, finish_binning
 
+_SCRATCH_CLEAN = 4   # GSTEX_SCRATCH_CLEAN, include/gstex_b200.h
+_GRAD_SCRATCH = {}   # (device index, stream, bytes) -> all-zero gradient scratch left by the last backward
+
 SUPPORTED_SETTINGS = (1 << 2) | (1 << 8) | (1 << 9) | (1 << 10)
 
 
@@ -292,10 +295,18 @@ class _TextureGaussians(Function):
         ws = ctx.workspace
         p = _lib.ptr
         pairs = ctx.pair_stream
-        scratch = None
+        # The gradient scratch leaves every backward all-zero (the unpack kernel clears what the stream kernel
+        # wrote), so one buffer per (device, stream, size) is kept and its 200 MB clear paid once.  It is taken out
+        # of the cache for the duration of the call: a call that raises never puts a half-written buffer back.
+        scratch, scratch_key, clean = None, None, 0
         if pairs is not None:
-            scratch = torch.empty((lib.gstex_grad_scratch_bytes(means.shape[0], texture.shape[0]),),
-                                  dtype=torch.uint8, device=dev)
+            nbytes = lib.gstex_grad_scratch_bytes(means.shape[0], texture.shape[0])
+            scratch_key = (dev.index, torch.cuda.current_stream(dev).cuda_stream, nbytes)
+            scratch = _GRAD_SCRATCH.pop(scratch_key, None)
+            if scratch is None:
+                scratch = torch.empty((nbytes,), dtype=torch.uint8, device=dev)
+            else:
+                clean = _SCRATCH_CLEAN
         with torch.cuda.device(dev):
             rc = lib.gstex_texture_backward(
                 int(H), int(W), int(ctx.block_width), C, means.shape[0], max(int(ctx.num_intersects), 0),
@@ -306,9 +317,13 @@ class _TextureGaussians(Function):
                 p(v_out_alpha), p(v_out_texture), p(v_out_normal), p(v_colors), p(v_opacity), p(v_means),
                 p(v_scales), p(v_quats), p(v_uv0), p(v_umap), p(v_vmap), p(v_texture), p(ws), ws.numel(), 1,
                 p(pairs), pairs.numel() if pairs is not None else 0, p(scratch),
-                scratch.numel() if scratch is not None else 0, int(texture.shape[0]), 2 if targets is not None else 1,
-                _lib.stream_ptr(dev))
+                scratch.numel() if scratch is not None else 0, int(texture.shape[0]),
+                (2 if targets is not None else 1) | clean, _lib.stream_ptr(dev))
         _lib.check(rc, "gstex_texture_backward")
+        if scratch is not None:
+            if len(_GRAD_SCRATCH) >= 4:  # a handful of model sizes at most; do not hoard memory
+                _GRAD_SCRATCH.clear()
+            _GRAD_SCRATCH[scratch_key] = scratch
         if targets is not None:  # already added to the registered tensors
             return (None,) * 28
         return (None, None, None, None, None, None, v_colors, v_opacity, v_means, v_scales, None, v_quats, v_uv0,

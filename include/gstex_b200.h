@@ -159,14 +159,16 @@ int gstex_texture_forward(int img_height, int img_width, int block_width, int ch
  * `workspace` may be the one the forward of the same view filled (records_valid != 0 skips re-packing).
  * `pair_stream`: the buffer the forward of the same view recorded into, or NULL to recompute.
  * `grad_scratch` (gstex_grad_scratch_bytes(n, num_texels) bytes, 16-byte aligned; needed by the stream path,
- * may be NULL otherwise): padded accumulators the stream kernel reduces into with 16-byte vector atomics before
- * an unpack kernel writes the reference's gradient tensors.  num_texels = rows of `texture`.
- * zero_fill == 1: the nine gradient buffers are uninitialised on entry and the library defines every element
- * (memsets what a kernel does not overwrite); zero_fill == 0: they are zero-filled by the caller; zero_fill == 2:
- * they hold running sums (a multi-view step's accumulated gradients) and this view's gradients are ADDED to them
- * -- what autograd's AccumulateGrad would do in a separate pass over all nine tensors.  With zero_fill 0/1 and the
- * stream path the colors/opacity/means/scales/quats/texture gradients are overwritten, not accumulated into
- * (on the zero-filled buffers the contract asks for, that is the same thing). */
+ * may be NULL otherwise): padded accumulators the stream kernel reduces into with 16-byte vector atomics; an
+ * unpack kernel then adds every non-zero accumulator word to the reference's gradient tensors and clears it
+ * again, so the scratch LEAVES every call all-zero.
+ * num_texels = rows of `texture`.
+ * zero_fill, low two bits -- 1: the nine gradient buffers are uninitialised on entry and the library clears them
+ * first; 0: they are zero-filled by the caller; 2: they hold running sums (a multi-view step's accumulated
+ * gradients) and this view's gradients are ADDED to them -- what autograd's AccumulateGrad would do in a separate
+ * pass over all nine tensors.  OR-ing in GSTEX_SCRATCH_CLEAN vouches that `grad_scratch` is exactly as an earlier
+ * call of this function left it (or was zero-filled by the caller) and skips the clear of the scratch. */
+#define GSTEX_SCRATCH_CLEAN 4
 size_t gstex_grad_scratch_bytes(int n, long long num_texels);
 int gstex_texture_backward(int img_height, int img_width, int block_width, int channels, int n, int num_intersects,
                            const int32_t* texture_dims, const int32_t* gaussian_ids_sorted, const int32_t* tile_bins,

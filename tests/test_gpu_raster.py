@@ -313,3 +313,48 @@ def test_fused_gradient_accumulation_matches_autograd():
         err = float((a - b).abs().max())
         assert err <= 2e-5 * scale + 1e-30, f"{k}: fused accumulation differs from autograd's ({err:.3e} at scale {scale:.3e})"
     assert float(plain[8].abs().max()) > 0 and float(plain[2].abs().max()) > 0
+
+
+def test_gradient_scratch_is_returned_all_zero(backward_path):
+    """The backward's scratch (padded accumulators + touched flags) is cached across calls and never cleared again:
+    every call must hand it back all-zero, over views that touch different splats, and repeated backward passes over
+    the cached buffer must reproduce the first one (to the rounding of the floating-point atomics)."""
+    import gstex_b200 as G
+    from gstex_b200 import texture as T
+    from gstex_b200.synthetic import make_scene, make_upstream_grads
+
+    s = make_scene("cfg2", n=20000, width=256, height=256, views=3)
+    v = {k: x.cuda() for k, x in make_upstream_grads(s).items()}
+    sd = {k: (x.cuda() if isinstance(x, torch.Tensor) else x) for k, x in s.items()}
+    intr = (s["fx"], s["fy"], s["cx"], s["cy"])
+    H, W, bw = s["H"], s["W"], 16
+    keys = ["colors", "opacities", "means", "scales", "quats", "uv0", "umap", "vmap", "texture"]
+    T._GRAD_SCRATCH.clear()
+
+    def grads(i):
+        params = [sd[k].clone().requires_grad_(True) for k in keys]
+        pd = dict(zip(keys, params))
+        vm, c2w = s["viewmats"][i].cuda().contiguous(), s["c2ws"][i].cuda().contiguous()
+        _, depths, centers, extents, nth = G.project_bounds(pd["means"].detach(), pd["scales"].detach(), 1,
+                                                            pd["quats"].detach(), vm, intr, H, W, bw)
+        outs = G.texture_gaussians(s["texture_info"], sd["texture_dims"], centers, extents, depths, nth, pd["colors"],
+                                   pd["opacities"], pd["means"], pd["scales"], 1, pd["quats"], pd["uv0"], pd["umap"],
+                                   pd["vmap"], pd["texture"], vm, c2w, *intr, H, W, bw, s["settings"], sd["background"])
+        torch.autograd.backward(list(outs), [v["v_out_img"], v["v_out_depth"], v["v_out_reg"], v["v_out_alpha"],
+                                             v["v_out_texture"], v["v_out_normal"]])
+        return [p.grad.clone() for p in params]
+
+    first = grads(0)                       # fresh scratch: cleared by the library
+    if backward_path == "recompute":       # no pair stream, no scratch
+        assert len(T._GRAD_SCRATCH) == 0
+        return
+    assert len(T._GRAD_SCRATCH) == 1
+    for i in (1, 2, 0):                    # cached scratch, other views in between
+        again = grads(i)
+        (buf,) = T._GRAD_SCRATCH.values()
+        assert int(torch.count_nonzero(buf)) == 0, f"view {i}: the scratch came back with non-zero bytes"
+    for k, a, b in zip(keys, first, again):
+        scale = float(a.abs().max())
+        err = float((a - b).abs().max())
+        assert err <= 2e-5 * scale + 1e-30, f"{k}: backward over the cached scratch differs ({err:.3e} at scale {scale:.3e})"
+    assert float(first[8].abs().max()) > 0
