@@ -303,14 +303,19 @@ __global__ void __launch_bounds__(kStreamWarps * 32, 2) texture_backward_stream_
                 v[3] = e.ex * v_alpha;
             }
             // segmented reduction: after the loop the head lane of each segment holds its totals
+            // (a step of offset `off` is only needed when some segment is longer than `off` lanes, i.e. when the
+            // head mask has a run of `off` non-head lanes: warp-uniform, so whole steps are skipped)
+            unsigned run = ~heads;
 #pragma unroll
             for (int off = 1; off < 32; off <<= 1) {
+                if (run == 0u) break;
                 const bool take = lane + off <= seg_end;
 #pragma unroll
                 for (int k = 0; k < 13; ++k) {
                     const float t = __shfl_down_sync(0xffffffffu, v[k], off);
                     if (take) v[k] += t;
                 }
+                run &= run >> off;
             }
             if (head && valid && !(dbg & 2)) {  // four 16-byte vector reductions per (unit, splat)
                 float4* acc = p.splat_acc + (size_t)gid * 4;

@@ -12,7 +12,7 @@ python bench.py --impl reference --steps 2 --warmup 1 > $OUT/bench_ref_$TAG.json
 cat $OUT/bench_ref_$TAG.json
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/launches_$TAG.csv \
   python bench.py --steps 1 --warmup 1 --views-per-gpu 2 --no-ref-cuda --no-cpu-baseline > $OUT/ncu_launch_$TAG.log 2>&1; echo "ncu launches rc=$?"
-ncu --set full --clock-control none --import-source on -k regex:'texture_(forward_kernel|backward_stream_kernel)' -s 4 -c 2 \
+ncu --set full --clock-control none --import-source on -k regex:'texture_(forward_kernel|backward_stream_kernel)|unpack_grads' -s 6 -c 3 \
   -o $OUT/raster_$TAG -f python bench.py --steps 1 --warmup 1 --views-per-gpu 2 --no-ref-cuda --no-cpu-baseline > $OUT/ncu_full_$TAG.log 2>&1; echo "ncu full rc=$?"
 ncu --set full --clock-control none --import-source on -k regex:'tile_(count|colscan|scan|emit|local_sort)' -s 6 -c 6 \
   -o $OUT/sort_$TAG -f python bench.py --steps 1 --warmup 1 --views-per-gpu 2 --no-ref-cuda --no-cpu-baseline > $OUT/ncu_sort_$TAG.log 2>&1; echo "ncu sort rc=$?"
