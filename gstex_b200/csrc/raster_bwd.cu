@@ -252,11 +252,11 @@ __global__ void __launch_bounds__(kMaxTileThreads + 32, 2) texture_backward_kern
                 const float t_view = e.t * pix.view_depth;
                 float v_t = 0.f, v_t_view = 0.f;
                 {
-                    const float d = use_ndc ? (kFar * t_view - kFar * kNear) / ((kFar - kNear) * t_view) : e.t;
+                    const float d = use_ndc ? div_normal(kFar * t_view - kFar * kNear, (kFar - kNear) * t_view) : e.t;
                     // distortion_vjp, helpers.cuh:266-269, with the FINAL sums
                     const float v_d = 2.f * (vis * d * ts_final.x - vis * ts_final.y) * v_out_reg;
                     const float v_weight = (d * d * ts_final.x - 2.f * d * ts_final.y + ts_final.z) * v_out_reg;
-                    if (use_ndc) v_t_view += (kFar * kNear) / ((kFar - kNear) * t_view * t_view) * v_d;
+                    if (use_ndc) v_t_view += div_normal(kFar * kNear, (kFar - kNear) * t_view * t_view) * v_d;
                     else v_t += v_d;
                     v_alpha += v_weight * T;
                     v_T_cur += v_weight * alpha;
@@ -286,7 +286,7 @@ __global__ void __launch_bounds__(kMaxTileThreads + 32, 2) texture_backward_kern
                 }
                 // compute_tt_vjp, texture_helpers.cuh:315-334
                 const float den = clamp_tt_denom(r1.x * pix.ray.x + r1.y * pix.ray.y + r1.z * pix.ray.z);
-                const float vt_den = v_t / den;
+                const float vt_den = div_normal(v_t, den);
                 const float3 v_normal_tt = make_float3((r0.x - pix.origin.x - pix.ray.x * e.t) * vt_den,
                                                        (r0.y - pix.origin.y - pix.ray.y * e.t) * vt_den,
                                                        (r0.z - pix.origin.z - pix.ray.z * e.t) * vt_den);

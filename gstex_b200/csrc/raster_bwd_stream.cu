@@ -219,10 +219,10 @@ __global__ void __launch_bounds__(kStreamWarps * 32, 2) texture_backward_stream_
                     }
                 }
                 {   // distortion_vjp, helpers.cuh:266-269, with the FINAL sums
-                    const float d = use_ndc ? (kFar * t_view - kFar * kNear) / ((kFar - kNear) * t_view) : e.t;
+                    const float d = use_ndc ? div_normal(kFar * t_view - kFar * kNear, (kFar - kNear) * t_view) : e.t;
                     const float v_d = 2.f * (vis * d * ts_final.x - vis * ts_final.y) * v_out_reg;
                     v_weight = (d * d * ts_final.x - 2.f * d * ts_final.y + ts_final.z) * v_out_reg;
-                    if (use_ndc) v_t_view += (kFar * kNear) / ((kFar - kNear) * t_view * t_view) * v_d;
+                    if (use_ndc) v_t_view += div_normal(kFar * kNear, (kFar - kNear) * t_view * t_view) * v_d;
                     else v_t += v_d;
                 }
             }
@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(kStreamWarps * 32, 2) texture_backward_stream_
                 }
                 // compute_tt_vjp, texture_helpers.cuh:315-334
                 const float den = clamp_tt_denom(r1.x * pix.ray.x + r1.y * pix.ray.y + r1.z * pix.ray.z);
-                const float vt_den = v_t / den;
+                const float vt_den = div_normal(v_t, den);
                 const float3 v_normal_tt = make_float3((r0.x - pix.origin.x - pix.ray.x * e.t) * vt_den,
                                                        (r0.y - pix.origin.y - pix.ray.y * e.t) * vt_den,
                                                        (r0.z - pix.origin.z - pix.ray.z * e.t) * vt_den);
@@ -344,15 +344,20 @@ __global__ void __launch_bounds__(256) unpack_grads_kernel(float4* __restrict__ 
     const long long t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
     auto any = [](const float4& a) { return a.x != 0.f || a.y != 0.f || a.z != 0.f || a.w != 0.f; };
-    for (long long i = t0; i < num_texels; i += stride) {
-        const float4 a = tex_acc[i];
-        if (!any(a)) continue;
+    auto texel = [&](long long i, const float4 a) {  // by value: `a` must not alias the word cleared below
+        if (!any(a)) return;
         tex_acc[i] = z;
         float* o = v_texture + i * C;
         o[0] += a.x;
         if (C > 1) o[1] += a.y;
         if (C > 2) o[2] += a.z;
+    };
+    long long i = t0;
+    for (; i + 3 * stride < num_texels; i += 4 * stride) {  // four independent loads in flight per thread
+        const float4 a0 = tex_acc[i], a1 = tex_acc[i + stride], a2 = tex_acc[i + 2 * stride], a3 = tex_acc[i + 3 * stride];
+        texel(i, a0); texel(i + stride, a1); texel(i + 2 * stride, a2); texel(i + 3 * stride, a3);
     }
+    for (; i < num_texels; i += stride) texel(i, tex_acc[i]);
     for (long long i = t0; i < n; i += stride) {
         float4* acc = splat_acc + 4 * i;
         const float4 a = acc[0], b = acc[1], c = acc[2], d = acc[3];

@@ -347,7 +347,7 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
                             pix_depth_index = idx;
                         }
                         float d = e.t;
-                        if (use_ndc) d = (kFar * t_view - kFar * kNear) / ((kFar - kNear) * t_view);
+                        if (use_ndc) d = div_normal(kFar * t_view - kFar * kNear, (kFar - kNear) * t_view);
                         pix_reg += vis * (d * d * ts.x + ts.z - 2.f * d * ts.y);  // distortion(), helpers.cuh:259-264
                         ts.x += vis; ts.y += vis * d; ts.z += vis * d * d;
                         T = next_T;
