@@ -60,7 +60,7 @@ constexpr int kTbMaxTiles = 50 * 1024;  // 200 KB of shared memory
 // block_counts[b * num_tiles + t] = intersections of block b's splats with tile t
 __global__ void __launch_bounds__(kTbThreads)
 tile_count_kernel(int n, int chunk, const float2* __restrict__ centers, const float2* __restrict__ extents,
-                  const int32_t* __restrict__ cum_tiles_hit, int tiles_x, int tiles_y, float fbw,
+                  const int32_t* __restrict__ num_tiles_hit, int tiles_x, int tiles_y, float fbw,
                   int32_t* __restrict__ block_counts) {
     extern __shared__ int tb_smem[];
     const int num_tiles = tiles_x * tiles_y;
@@ -68,7 +68,7 @@ tile_count_kernel(int n, int chunk, const float2* __restrict__ centers, const fl
     __syncthreads();
     const int begin = blockIdx.x * chunk, end = min(begin + chunk, n);
     for (int idx = begin + threadIdx.x; idx < end; idx += kTbThreads) {
-        int left = cum_tiles_hit[idx] - ((idx == 0) ? 0 : cum_tiles_hit[idx - 1]);  // slots reserved by stage a3
+        int left = num_tiles_hit[idx];  // slots stage a3 reserves for this splat
         if (left <= 0) continue;
         const TileRect r = tile_rect(centers[idx], extents[idx], fbw, tiles_x, tiles_y);
         if (r.emits) {
@@ -136,7 +136,7 @@ tile_scan_kernel(int num_tiles, int2* __restrict__ tile_bins, int32_t* __restric
 // blocks before b with t), so no two blocks ever touch the same slot and all atomics stay in shared memory.
 __global__ void __launch_bounds__(kTbThreads)
 tile_emit_kernel(int n, int chunk, const float2* __restrict__ centers, const float2* __restrict__ extents,
-                 const float* __restrict__ depths, const int32_t* __restrict__ cum_tiles_hit, int tiles_x, int tiles_y,
+                 const float* __restrict__ depths, const int32_t* __restrict__ num_tiles_hit, int tiles_x, int tiles_y,
                  float fbw, const int32_t* __restrict__ tile_start, const int32_t* __restrict__ block_counts,
                  unsigned long long* __restrict__ keys) {
     extern __shared__ int tb_smem[];
@@ -146,7 +146,7 @@ tile_emit_kernel(int n, int chunk, const float2* __restrict__ centers, const flo
     __syncthreads();
     const int begin = blockIdx.x * chunk, end = min(begin + chunk, n);
     for (int idx = begin + threadIdx.x; idx < end; idx += kTbThreads) {
-        int left = cum_tiles_hit[idx] - ((idx == 0) ? 0 : cum_tiles_hit[idx - 1]);
+        int left = num_tiles_hit[idx];
         if (left <= 0) continue;
         const TileRect r = tile_rect(centers[idx], extents[idx], fbw, tiles_x, tiles_y);
         if (r.emits) {
@@ -357,19 +357,19 @@ extern "C" size_t gstex_tile_bucket_scratch_bytes(int num_tiles) {
 
 static inline int tb_chunk(int n) { return (n + kTbBlocks - 1) / kTbBlocks; }
 
-extern "C" int gstex_tile_bucket_count(int n, const float* centers, const float* extents, const int32_t* cum_tiles_hit,
+extern "C" int gstex_tile_bucket_count(int n, const float* centers, const float* extents, const int32_t* num_tiles_hit,
                                        int tiles_x, int tiles_y, int block_width, int32_t* block_counts,
                                        int32_t* tile_bins, int32_t* tile_start, int32_t* stats, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     if (n < 0 || block_width < 2 || block_width > 16 || tiles_x <= 0 || tiles_y <= 0) return GSTEX_E_BADARG;
     if (!block_counts || !tile_bins || !tile_start || !stats) return GSTEX_E_BADARG;
-    if (n > 0 && (!centers || !extents || !cum_tiles_hit)) return GSTEX_E_BADARG;
+    if (n > 0 && (!centers || !extents || !num_tiles_hit)) return GSTEX_E_BADARG;
     const long long num_tiles = (long long)tiles_x * tiles_y;
     if (num_tiles > kTbMaxTiles) return GSTEX_E_UNSUPPORTED;
     const size_t smem = (size_t)num_tiles * sizeof(int);
     GSTEX_CUDA_TRY(cudaFuncSetAttribute(tile_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTbMaxTiles * 4));
     tile_count_kernel<<<kTbBlocks, kTbThreads, smem, st>>>(
-        n, tb_chunk(n), reinterpret_cast<const float2*>(centers), reinterpret_cast<const float2*>(extents), cum_tiles_hit,
+        n, tb_chunk(n), reinterpret_cast<const float2*>(centers), reinterpret_cast<const float2*>(extents), num_tiles_hit,
         tiles_x, tiles_y, (float)block_width, block_counts);
     GSTEX_LAUNCH_CHECK();
     tile_colscan_kernel<<<div_up(num_tiles * 32, 256), 256, 0, st>>>((int)num_tiles, kTbBlocks, block_counts, tile_start);
@@ -380,7 +380,7 @@ extern "C" int gstex_tile_bucket_count(int n, const float* centers, const float*
 }
 
 extern "C" int gstex_tile_bucket_sort(int n, int num_intersects, int max_list, const float* centers,
-                                      const float* extents, const float* depths, const int32_t* cum_tiles_hit,
+                                      const float* extents, const float* depths, const int32_t* num_tiles_hit,
                                       int tiles_x, int tiles_y, int block_width, const int32_t* block_counts,
                                       const int32_t* tile_start, const int32_t* tile_bins, void* keys,
                                       int32_t* gaussian_ids_sorted, void* stream) {
@@ -390,13 +390,13 @@ extern "C" int gstex_tile_bucket_sort(int n, int num_intersects, int max_list, c
     if (num_intersects == 0 || n == 0) return GSTEX_OK;
     const long long num_tiles = (long long)tiles_x * tiles_y;
     if (max_list > kLsMaxList || num_tiles > kTbMaxTiles) return GSTEX_E_UNSUPPORTED;
-    if (!centers || !extents || !depths || !cum_tiles_hit || !block_counts || !tile_start || !tile_bins || !keys ||
+    if (!centers || !extents || !depths || !num_tiles_hit || !block_counts || !tile_start || !tile_bins || !keys ||
         !gaussian_ids_sorted)
         return GSTEX_E_BADARG;
     GSTEX_CUDA_TRY(cudaFuncSetAttribute(tile_emit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTbMaxTiles * 4));
     tile_emit_kernel<<<kTbBlocks, kTbThreads, (size_t)num_tiles * sizeof(int), st>>>(
         n, tb_chunk(n), reinterpret_cast<const float2*>(centers), reinterpret_cast<const float2*>(extents), depths,
-        cum_tiles_hit, tiles_x, tiles_y, (float)block_width, tile_start, block_counts,
+        num_tiles_hit, tiles_x, tiles_y, (float)block_width, tile_start, block_counts,
         reinterpret_cast<unsigned long long*>(keys));
     GSTEX_LAUNCH_CHECK();
     int id_bits = 1;

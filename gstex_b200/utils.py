@@ -120,13 +120,13 @@ def bin_and_sort_gaussians(num_points: int, num_intersects: int, centers: Tensor
 
 
 class TileBinning:
-    """State of a binning request between `begin_binning` (asynchronous: prefix sum, per-tile counts, a pinned
+    """State of a binning request between `begin_binning` (asynchronous: per-tile counts, a pinned
     read-back of `num_intersects` and the longest tile list) and `finish_binning` (waits for that read-back only,
     then emits and sorts).  Splitting the two lets a multi-view step launch view i+1's `begin_binning` between
     view i's forward and backward: the host learns view i+1's sizes while the backward still runs, so the one
     host synchronisation of the stage (the reference's `.item()`, utils.py:58) no longer drains the GPU."""
 
-    __slots__ = ("num_points", "centers", "extents", "depths", "cum", "total", "tile_bounds", "block_size", "num_tiles",
+    __slots__ = ("num_points", "centers", "extents", "depths", "nth", "cum", "total", "tile_bounds", "block_size", "num_tiles",
                  "block_counts", "tile_start", "tile_bins", "stats_host", "event", "fast", "result")
 
 
@@ -160,10 +160,11 @@ def begin_binning(num_points: int, centers: Tensor, extents: Tensor, depths: Ten
     if nth.numel() == 0:
         b.result = (0, torch.zeros((0,), **i32), torch.zeros((b.num_tiles, 2), **i32))
         return b
-    b.cum, b.total = cumsum_i32(nth)
+    b.nth, b.cum, b.total = nth, None, None
     lib = _lib.load()
     b.fast = b.num_tiles <= lib.gstex_tile_bucket_max_tiles()
     if not b.fast:
+        b.cum, b.total = cumsum_i32(nth)
         return b
     b.block_counts = _workspace(lib.gstex_tile_bucket_scratch_bytes(b.num_tiles), dev)
     small = torch.empty((b.num_tiles + 2,), **i32)  # tile_start | stats
@@ -171,7 +172,7 @@ def begin_binning(num_points: int, centers: Tensor, extents: Tensor, depths: Ten
     b.tile_bins = torch.empty((b.num_tiles, 2), **i32)
     p, st = _lib.ptr, _lib.stream_ptr(dev)
     with torch.cuda.device(dev):
-        rc = lib.gstex_tile_bucket_count(b.num_points, p(centers), p(extents), p(b.cum), int(tile_bounds[0]),
+        rc = lib.gstex_tile_bucket_count(b.num_points, p(centers), p(extents), p(nth), int(tile_bounds[0]),
                                          int(tile_bounds[1]), b.block_size, p(b.block_counts), p(b.tile_bins),
                                          p(b.tile_start), p(stats), st)
     _lib.check(rc, "gstex_tile_bucket_count")
@@ -194,6 +195,8 @@ def finish_binning(b: TileBinning):
     def general(num_intersects):
         if num_intersects < 1:
             return num_intersects, torch.zeros((0,), **i32), torch.zeros((b.num_tiles, 2), **i32)
+        if b.cum is None:  # the tile-bucket path needs no prefix sum; the general one does
+            b.cum, b.total = cumsum_i32(b.nth)
         (_, _, _, ids_sorted, bins) = bin_and_sort_gaussians(b.num_points, num_intersects, b.centers, b.extents, b.depths,
                                                              b.cum, b.tile_bounds, b.block_size)
         return num_intersects, ids_sorted, bins
@@ -211,7 +214,7 @@ def finish_binning(b: TileBinning):
     p = _lib.ptr
     with torch.cuda.device(dev):
         rc = lib.gstex_tile_bucket_sort(b.num_points, int(num_intersects), int(max_list), p(b.centers), p(b.extents),
-                                        p(b.depths), p(b.cum), int(b.tile_bounds[0]), int(b.tile_bounds[1]), b.block_size,
+                                        p(b.depths), p(b.nth), int(b.tile_bounds[0]), int(b.tile_bounds[1]), b.block_size,
                                         p(b.block_counts), p(b.tile_start), p(b.tile_bins), p(keys), p(ids_sorted),
                                         _lib.stream_ptr(dev))
     _lib.check(rc, "gstex_tile_bucket_sort")

@@ -111,15 +111,16 @@ int gstex_get_tile_bin_edges(int num_intersects, const int64_t* isect_ids_sorted
  *     scratch) and sorts every tile's range by (depth bits, splat id) in shared memory.  max_list = stats[1]
  *     read back by the host; returns GSTEX_E_UNSUPPORTED when it exceeds gstex_tile_bucket_max_list() (the
  *     caller then takes the general path above).  Depths of emitted splats must be non-negative (they are:
- *     splats with z <= 0.01 are clipped and emit nothing, get_aabb_2d.cu:25). */
+ *     splats with z <= 0.01 are clipped and emit nothing, get_aabb_2d.cu:25).
+ *   Both take num_tiles_hit (stage a3's per-splat counts) as it is: the path needs no prefix sum over splats. */
 int gstex_tile_bucket_max_list(void);
 int gstex_tile_bucket_max_tiles(void);
 size_t gstex_tile_bucket_scratch_bytes(int num_tiles);
-int gstex_tile_bucket_count(int n, const float* centers, const float* extents, const int32_t* cum_tiles_hit,
+int gstex_tile_bucket_count(int n, const float* centers, const float* extents, const int32_t* num_tiles_hit,
                             int tiles_x, int tiles_y, int block_width, int32_t* block_counts, int32_t* tile_bins,
                             int32_t* tile_start, int32_t* stats, void* stream);
 int gstex_tile_bucket_sort(int n, int num_intersects, int max_list, const float* centers, const float* extents,
-                           const float* depths, const int32_t* cum_tiles_hit, int tiles_x, int tiles_y,
+                           const float* depths, const int32_t* num_tiles_hit, int tiles_x, int tiles_y,
                            int block_width, const int32_t* block_counts, const int32_t* tile_start,
                            const int32_t* tile_bins, void* keys, int32_t* gaussian_ids_sorted, void* stream);
 
