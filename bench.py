@@ -341,6 +341,12 @@ def ncu_traffic(kernel_key):
 
 def main():
     args = parse_args()
+    # stdout carries ONE JSON line and nothing else: libraries that log to file descriptor 1 (NCCL's version banner and
+    # NCCL_DEBUG output go to stdout) are sent to stderr for the whole run, the line is written to the saved descriptor
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, "w", buffering=1)
     if args.impl == "reference":
         run_reference_arm(args)
         return
@@ -355,8 +361,6 @@ def main():
     if world > 1:
         import torch.distributed as dist
 
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-            os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner out of stdout: rank 0 prints ONE JSON line
         dist.init_process_group("nccl", device_id=dev)
 
     def barrier():
