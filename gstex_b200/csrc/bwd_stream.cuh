@@ -25,6 +25,8 @@ struct StreamBwdParams {
     float4 *tex_acc, *splat_acc;
     int n;
     long long num_texels;
+    const int32_t* order;         // the forward's tile order (longest list first) and its validity flag
+    const uint32_t* order_valid;  // (workspace counters[1]); units are taken in that order when set
     int scratch_clean;  // the caller vouches the scratch is as a previous call left it: skip the clear
 };
 

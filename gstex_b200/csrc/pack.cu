@@ -21,6 +21,9 @@ struct PackParams {
     SplatRecBwd* recs_bwd;
     float4* boxes;
     uint32_t* counters;
+    const int2* tile_bins;  // when set, the block after the last splat block orders the tiles by list length
+    int num_tiles;
+    int32_t* order;
 };
 
 // Support box.  alpha = opac*exp(-sigma) >= 1/255  <=>  sigma <= smax = ln(255*opac), sigma = (u^2+v^2)/2 in
@@ -69,10 +72,50 @@ __device__ __forceinline__ float4 support_box(const double a[3], const double b[
     return box;
 }
 
+// Longest-processing-time-first order for the forward's and the stream backward's unit cursors: a persistent grid
+// that meets its heaviest tiles last idles through a tail as long as one of them (a unit of a dense tile runs for
+// hundreds of microseconds).  64 buckets by list length, longest first; the order inside a bucket is arbitrary and
+// only ever affects scheduling.
+__device__ void order_tiles_by_length(const PackParams& p) {
+    __shared__ int s_max, s_hist[64];
+    const int t = threadIdx.x;
+    if (t == 0) s_max = 0;
+    if (t < 64) s_hist[t] = 0;
+    __syncthreads();
+    int mx = 0;
+    for (int k = t; k < p.num_tiles; k += blockDim.x) {
+        const int2 r = p.tile_bins[k];
+        mx = max(mx, r.y - r.x);
+    }
+    atomicMax(&s_max, mx);
+    __syncthreads();
+    const long long denom = (long long)s_max + 1;
+    auto bucket = [&](int k) {
+        const int2 r = p.tile_bins[k];
+        const int len = max(r.y - r.x, 0);
+        return 63 - (int)(((long long)len * 64) / denom);
+    };
+    for (int k = t; k < p.num_tiles; k += blockDim.x) atomicAdd(&s_hist[bucket(k)], 1);
+    __syncthreads();
+    if (t == 0) {
+        int run = 0;
+        for (int b = 0; b < 64; ++b) { const int c = s_hist[b]; s_hist[b] = run; run += c; }
+    }
+    __syncthreads();
+    for (int k = t; k < p.num_tiles; k += blockDim.x) p.order[atomicAdd(&s_hist[bucket(k)], 1)] = k;
+}
+
 __global__ void __launch_bounds__(kThreads1D) pack_records_kernel(const PackParams p) {
+    if (p.tile_bins != nullptr && blockIdx.x == gridDim.x - 1) {
+        order_tiles_by_length(p);
+        return;
+    }
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= p.n) return;
-    if (i == 0) p.counters[0] = 0u;  // unit cursor of the forward kernel that follows on the stream
+    if (i == 0) {
+        p.counters[0] = 0u;  // unit cursor of the forward kernel that follows on the stream
+        p.counters[1] = p.tile_bins != nullptr ? 1u : 0u;  // the tile order beside the records is valid
+    }
     const float mx = p.means[3 * i], my = p.means[3 * i + 1], mz = p.means[3 * i + 2];
     const float4 qt = reinterpret_cast<const float4*>(p.quats)[i];
     const float w = qt.x, x = qt.y, y = qt.z, z = qt.w;
@@ -128,16 +171,19 @@ int launch_pack_records(int n, const int32_t* texture_dims, const float* colors,
                         const float* means, const float* scales, float glob_scale, const float* quats,
                         const float* uv0, const float* umap, const float* vmap, const float* viewmat,
                         const float* c2w, float fx, float fy, float cx, float cy, int settings, void* workspace,
-                        cudaStream_t st) {
+                        cudaStream_t st, const int32_t* tile_bins, int num_tiles) {
     if (n <= 0) return GSTEX_OK;
     PackParams p;
+    const bool order = tile_bins != nullptr && num_tiles > 0 && num_tiles <= kOrderMaxTiles;
+    p.tile_bins = order ? reinterpret_cast<const int2*>(tile_bins) : nullptr;
+    p.num_tiles = num_tiles; p.order = ws_order(workspace, n);
     p.n = n; p.texture_dims = texture_dims; p.colors = colors; p.opacities = opacities; p.means = means;
     p.scales = scales; p.quats = quats; p.uv0 = uv0; p.umap = umap; p.vmap = vmap; p.viewmat = viewmat; p.c2w = c2w;
     p.glob_scale = glob_scale; p.fx = fx; p.fy = fy; p.cx = cx; p.cy = cy;
     p.use_blur = (settings & GSTEX_SET_BLUR) ? 1 : 0;
     p.recs = ws_recs(workspace); p.recs_bwd = ws_recs_bwd(workspace, n); p.boxes = ws_boxes(workspace, n);
     p.counters = ws_counters(workspace);
-    pack_records_kernel<<<div_up(n, kThreads1D), kThreads1D, 0, st>>>(p);
+    pack_records_kernel<<<div_up(n, kThreads1D) + (order ? 1 : 0), kThreads1D, 0, st>>>(p);
     GSTEX_LAUNCH_CHECK();
     return GSTEX_OK;
 }

@@ -409,6 +409,7 @@ extern "C" int gstex_texture_backward(
         sp.v_colors = v_colors; sp.v_opacity = v_opacity; sp.v_means = v_means; sp.v_scales = v_scales;
         sp.v_quats = v_quats; sp.v_texture = v_texture;
         sp.n = n; sp.num_texels = num_texels; sp.scratch_clean = scratch_clean;
+        sp.order = ws_order(workspace, n); sp.order_valid = ws_counters(workspace) + 1;
         sp.tex_acc = reinterpret_cast<float4*>(grad_scratch); sp.splat_acc = sp.tex_acc + num_texels;
         // the unpack kernel of the stream path adds to the gradients wherever this view contributed
         int rc = zero(true);

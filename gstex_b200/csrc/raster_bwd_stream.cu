@@ -69,11 +69,14 @@ __global__ void __launch_bounds__(kStreamWarps * 32, 2) texture_backward_stream_
     float4 (*rs)[32][kRecQuads] = sm.rs[warp];
     const float bg0 = __ldg(p.background), bg1 = __ldg(p.background + 1), bg2 = __ldg(p.background + 2);
 
+    const int32_t* order = (p.order_valid != nullptr && __ldg(p.order_valid) != 0u) ? p.order : nullptr;
+
     while (true) {
         int unit = 0;
         if (lane == 0) unit = (int)atomicAdd(&p.sv.hdr->next_unit, 1u);
         unit = __shfl_sync(0xffffffffu, unit, 0);
         if (unit >= p.sv.num_units) break;
+        if (order) unit = __ldg(order + unit / kUnitsPerTile) * kUnitsPerTile + unit % kUnitsPerTile;
         const int2 uc = p.sv.units[unit];
         const int cnt = uc.y;
         if (cnt <= 0) continue;

@@ -49,6 +49,7 @@ struct FwdParams {
     float *out_img, *out_depth, *out_reg, *out_texture, *out_normal, *final_Ts, *out_reg_s;
     int32_t *final_idx, *depth_idx;
     uint32_t* unit_cursor;  // zeroed before the launch
+    const int32_t* order;   // tiles, longest list first (nullptr: natural order)
     int units_per_tile, num_units;
     int force_nocull;  // debugging / tests (GSTEX_DBG bit 4): evaluate every list entry for every unit
     StreamView sv;  // pair stream (REC kernels only)
@@ -106,7 +107,8 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
         if (lane == 0) unit = (int)atomicAdd(p.unit_cursor, 1u);
         unit = __shfl_sync(0xffffffffu, unit, 0);
         if (unit >= p.num_units) break;
-        const int tile_id = unit / p.units_per_tile, w = unit - tile_id * p.units_per_tile;
+        const int slot = unit / p.units_per_tile, w = unit - slot * p.units_per_tile;
+        const int tile_id = p.order ? __ldg(p.order + slot) : slot;
         const int tile_x = tile_id % g.tiles_x, tile_y = tile_id / g.tiles_x;
         const int2 range = p.tile_bins[tile_id];
         int lx, ly;
@@ -483,9 +485,11 @@ extern "C" int gstex_texture_forward(int img_height, int img_width, int block_wi
         return GSTEX_E_BADARG;
     if (num_intersects > 0 && !gaussian_ids_sorted) return GSTEX_E_BADARG;
     if (workspace_bytes < ws_bytes(n)) return GSTEX_E_WORKSPACE;
+    const int num_tiles = ((img_width + block_width - 1) / block_width) * ((img_height + block_width - 1) / block_width);
     if (n > 0) {
         const int rc = launch_pack_records(n, texture_dims, colors, opacities, means, scales, glob_scale, quats, uv0, umap,
-                                           vmap, viewmat, c2w, fx, fy, cx, cy, settings, workspace, st);
+                                           vmap, viewmat, c2w, fx, fy, cx, cy, settings, workspace, st, tile_bins,
+                                           num_tiles);
         if (rc != GSTEX_OK) return rc;
     } else {  // the pack kernel zeroes the unit cursor; without splats nobody did
         GSTEX_CUDA_TRY(cudaMemsetAsync(ws_counters(workspace), 0, sizeof(uint32_t), st));
@@ -502,6 +506,7 @@ extern "C" int gstex_texture_forward(int img_height, int img_width, int block_wi
     p.out_normal = out_normal; p.final_Ts = final_Ts; p.out_reg_s = out_reg_s; p.final_idx = final_idx;
     p.depth_idx = depth_idx;
     p.unit_cursor = ws_counters(workspace);
+    p.order = (n > 0 && tile_bins != nullptr && num_tiles <= kOrderMaxTiles) ? ws_order(workspace, n) : nullptr;
     p.units_per_tile = p.g.threads / 32;
     p.num_units = p.g.tiles_x * p.g.tiles_y * p.units_per_tile;
     {
