@@ -431,12 +431,13 @@ def main():
     ab = alg_bytes(N, I, T, C, P, tiles)
     entry_ms = {k: (sum(x) / len(x), len(x), sum(x)) for k, x in per_call.items() if x}
     dom = max(entry_ms, key=lambda k: entry_ms[k][2])
-    key = {"gstex_texture_backward": "backward", "gstex_texture_forward": "forward", "gstex_sort_isects": "sort"}.get(dom, "total")
+    base = dom[:-4] if dom.endswith("_act") else dom  # the `_act` entry points run the same kernels (scale 1, bias 0)
+    key = {"gstex_texture_backward": "backward", "gstex_texture_forward": "forward", "gstex_sort_isects": "sort"}.get(base, "total")
     peak, peak_src = measured_peak_gbs()
     achieved = ab[key] / (entry_ms[dom][0] * 1e-3) / 1e9
     step_ms_kernels = sum(x[2] for x in entry_ms.values()) / args.steps
     roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": ncu_traffic(dom), "peak_source": peak_src, "alg_bytes_per_launch": ab[key],
+                "traffic": ncu_traffic(base), "peak_source": peak_src, "alg_bytes_per_launch": ab[key],
                 "avg_launch_ms": entry_ms[dom][0],
                 "share_of_step": entry_ms[dom][2] / args.steps / ms_per_step,
                 "whole_path": {"alg_bytes_per_view": ab["total"],

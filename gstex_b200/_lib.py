@@ -44,6 +44,10 @@ _SIGNATURES = {
                               [P, SZ, P, SZ, P]),
     "gstex_texture_backward": (I, [I, I, I, I, I, I] + [P] * 7 + [F] + [P] * 7 + [F, F, F, F, I] + [P] * 11 + [P] * 9 +
                                [P, SZ, I, P, SZ, P, SZ, ctypes.c_longlong, I, P]),
+    "gstex_texture_forward_act": (I, [I, I, I, I, I, I] + [P] * 7 + [F] + [P] * 5 + [F, F] + [P] * 2 + [F, F, F, F, I] +
+                                  [P] * 10 + [P, SZ, P, SZ, P]),
+    "gstex_texture_backward_act": (I, [I, I, I, I, I, I] + [P] * 7 + [F] + [P] * 5 + [F, F] + [P] * 2 + [F, F, F, F, I] +
+                                   [P] * 11 + [P] * 9 + [P, SZ, I, P, SZ, P, SZ, ctypes.c_longlong, I, P]),
     "gstex_grad_scratch_bytes": (SZ, [I, ctypes.c_longlong]),
     "gstex_compute_sh_forward": (I, [I, I, I, P, P, P, P]),
     "gstex_compute_sh_backward": (I, [I, I, I, P, P, P, P]),

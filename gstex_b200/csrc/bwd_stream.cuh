@@ -27,6 +27,7 @@ struct StreamBwdParams {
     long long num_texels;
     const int32_t* order;         // the forward's tile order (longest list first) and its validity flag
     const uint32_t* order_valid;  // (workspace counters[1]); units are taken in that order when set
+    float tex_scale;    // slope of the forward's texel activation: the unpack sweep multiplies texel gradients by it
     int scratch_clean;  // the caller vouches the scratch is as a previous call left it: skip the clear
 };
 

@@ -44,6 +44,7 @@ struct BwdParams {
     const int32_t* ids;
     const int2* tile_bins;
     const float* texture;
+    float tex_scale, tex_bias;  // texel activation of the forward (tex_scale * texel + tex_bias)
     const float *viewmat, *c2w, *background;
     float fx, fy, cx, cy;
     int settings;
@@ -223,15 +224,18 @@ __global__ void __launch_bounds__(kMaxTileThreads + 32, 2) texture_backward_kern
 #pragma unroll
                     for (int k = 0; k < CMAX; ++k) {
                         if (k < C) {
-                            const float t00 = __ldg(p.texture + o00 + k), t01 = __ldg(p.texture + o01 + k);
-                            const float t10 = __ldg(p.texture + o10 + k), t11 = __ldg(p.texture + o11 + k);
+                            const float t00 = fmaf(p.tex_scale, __ldg(p.texture + o00 + k), p.tex_bias);
+                            const float t01 = fmaf(p.tex_scale, __ldg(p.texture + o01 + k), p.tex_bias);
+                            const float t10 = fmaf(p.tex_scale, __ldg(p.texture + o10 + k), p.tex_bias);
+                            const float t11 = fmaf(p.tex_scale, __ldg(p.texture + o11 + k), p.tex_bias);
                             const float val = q.w00 * t00 + q.w01 * t01 + q.w10 * t10 + q.w11 * t11;
                             const float v_val = vis * v_tex[k];
-                            // query_jagged_chart_vjp, texture_helpers.cuh:252-260
-                            atomicAdd(p.v_texture + o00 + k, q.w00 * v_val);
-                            atomicAdd(p.v_texture + o01 + k, q.w01 * v_val);
-                            atomicAdd(p.v_texture + o10 + k, q.w10 * v_val);
-                            atomicAdd(p.v_texture + o11 + k, q.w11 * v_val);
+                            // query_jagged_chart_vjp, texture_helpers.cuh:252-260 (times the activation's slope)
+                            const float v_raw = v_val * p.tex_scale;
+                            atomicAdd(p.v_texture + o00 + k, q.w00 * v_raw);
+                            atomicAdd(p.v_texture + o01 + k, q.w01 * v_raw);
+                            atomicAdd(p.v_texture + o10 + k, q.w10 * v_raw);
+                            atomicAdd(p.v_texture + o11 + k, q.w11 * v_raw);
                             if (UV && bilinear) {  // texture_helpers.cuh:262-299
                                 v_u += (float)th * (v_val * (-(1.f - q.fy) * t00 - q.fy * t01 + (1.f - q.fy) * t10 + q.fy * t11));
                                 v_v += (float)tw * (v_val * (-(1.f - q.fx) * t00 + (1.f - q.fx) * t01 - q.fx * t10 + q.fx * t11));
@@ -330,11 +334,11 @@ extern "C" int gstex_pair_stream_supported(int channels, int n, int settings);
 
 extern "C" size_t gstex_grad_scratch_bytes(int n, long long num_texels) { return grad_scratch_bytes(n, num_texels); }
 
-extern "C" int gstex_texture_backward(
+extern "C" int gstex_texture_backward_act(
     int img_height, int img_width, int block_width, int channels, int n, int num_intersects,
     const int32_t* texture_dims, const int32_t* gaussian_ids_sorted, const int32_t* tile_bins, const float* colors,
     const float* opacities, const float* means, const float* scales, float glob_scale, const float* quats,
-    const float* uv0, const float* umap, const float* vmap, const float* texture, const float* viewmat,
+    const float* uv0, const float* umap, const float* vmap, const float* texture, float tex_scale, float tex_bias, const float* viewmat,
     const float* c2w, float fx, float fy, float cx, float cy, int settings, const float* background,
     const float* final_Ts, const int32_t* final_idx, const int32_t* depth_idx, const float* final_s,
     const float* v_output, const float* v_output_depth, const float* v_output_reg, const float* v_output_alpha,
@@ -386,7 +390,7 @@ extern "C" int gstex_texture_backward(
     p.g = make_raster_geom(img_height, img_width, block_width);
     p.C = channels; p.recs = ws_recs(workspace); p.recs_bwd = ws_recs_bwd(workspace, n); p.boxes = ws_boxes(workspace, n);
     p.ids = gaussian_ids_sorted;
-    p.tile_bins = reinterpret_cast<const int2*>(tile_bins); p.texture = texture; p.viewmat = viewmat; p.c2w = c2w;
+    p.tile_bins = reinterpret_cast<const int2*>(tile_bins); p.texture = texture; p.tex_scale = tex_scale; p.tex_bias = tex_bias; p.viewmat = viewmat; p.c2w = c2w;
     p.background = background; p.fx = fx; p.fy = fy; p.cx = cx; p.cy = cy; p.settings = settings;
     p.final_Ts = final_Ts; p.final_s = final_s; p.final_idx = final_idx; p.depth_idx = depth_idx;
     p.v_output = v_output; p.v_output_depth = v_output_depth; p.v_output_reg = v_output_reg;
@@ -408,7 +412,7 @@ extern "C" int gstex_texture_backward(
         sp.v_output_alpha = v_output_alpha; sp.v_output_texture = v_output_texture; sp.v_output_normal = v_output_normal;
         sp.v_colors = v_colors; sp.v_opacity = v_opacity; sp.v_means = v_means; sp.v_scales = v_scales;
         sp.v_quats = v_quats; sp.v_texture = v_texture;
-        sp.n = n; sp.num_texels = num_texels; sp.scratch_clean = scratch_clean;
+        sp.n = n; sp.num_texels = num_texels; sp.scratch_clean = scratch_clean; sp.tex_scale = tex_scale;
         sp.order = ws_order(workspace, n); sp.order_valid = ws_counters(workspace) + 1;
         sp.tex_acc = reinterpret_cast<float4*>(grad_scratch); sp.splat_acc = sp.tex_acc + num_texels;
         // the unpack kernel of the stream path adds to the gradients wherever this view contributed
@@ -427,4 +431,19 @@ extern "C" int gstex_texture_backward(
     else launch_bwd<GSTEX_MAX_CHANNELS>(p, uv, st);
     GSTEX_LAUNCH_CHECK();
     return GSTEX_OK;
+}
+
+extern "C" int gstex_texture_backward(
+    int img_height, int img_width, int block_width, int channels, int n, int num_intersects,
+    const int32_t* texture_dims, const int32_t* gaussian_ids_sorted, const int32_t* tile_bins, const float* colors,
+    const float* opacities, const float* means, const float* scales, float glob_scale, const float* quats,
+    const float* uv0, const float* umap, const float* vmap, const float* texture, const float* viewmat,
+    const float* c2w, float fx, float fy, float cx, float cy, int settings, const float* background,
+    const float* final_Ts, const int32_t* final_idx, const int32_t* depth_idx, const float* final_s,
+    const float* v_output, const float* v_output_depth, const float* v_output_reg, const float* v_output_alpha,
+    const float* v_output_texture, const float* v_output_normal, float* v_colors, float* v_opacity, float* v_means,
+    float* v_scales, float* v_quats, float* v_uv0, float* v_umap, float* v_vmap, float* v_texture, void* workspace,
+    size_t workspace_bytes, int records_valid, void* pair_stream, size_t pair_stream_bytes, void* grad_scratch,
+    size_t grad_scratch_size, long long num_texels, int zero_fill, void* stream) {
+    return gstex_texture_backward_act(img_height, img_width, block_width, channels, n, num_intersects, texture_dims, gaussian_ids_sorted, tile_bins, colors, opacities, means, scales, glob_scale, quats, uv0, umap, vmap, texture, 1.f, 0.f, viewmat, c2w, fx, fy, cx, cy, settings, background, final_Ts, final_idx, depth_idx, final_s, v_output, v_output_depth, v_output_reg, v_output_alpha, v_output_texture, v_output_normal, v_colors, v_opacity, v_means, v_scales, v_quats, v_uv0, v_umap, v_vmap, v_texture, workspace, workspace_bytes, records_valid, pair_stream, pair_stream_bytes, grad_scratch, grad_scratch_size, num_texels, zero_fill, stream);
 }

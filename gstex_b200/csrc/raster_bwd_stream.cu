@@ -338,7 +338,7 @@ __global__ void __launch_bounds__(kStreamWarps * 32, 2) texture_backward_stream_
 // and of their texels -- are cleared again and ADDED to the gradient tensors, which hold zeros (zero_fill 0/1) or the
 // caller's running sum over the views of a step (zero_fill 2).  So no full-size clear precedes the stream kernel and
 // the gradient tensors are only touched where this view has something to add.
-__global__ void __launch_bounds__(256) unpack_grads_kernel(float4* __restrict__ tex_acc, long long num_texels, int C,
+__global__ void __launch_bounds__(256) unpack_grads_kernel(float4* __restrict__ tex_acc, long long num_texels, int C, float tex_scale,
                                                            float4* __restrict__ splat_acc, int n,
                                                            float* __restrict__ v_texture, float* __restrict__ v_colors,
                                                            float* __restrict__ v_opacity, float* __restrict__ v_means,
@@ -351,9 +351,9 @@ __global__ void __launch_bounds__(256) unpack_grads_kernel(float4* __restrict__ 
         if (!any(a)) return;
         tex_acc[i] = z;
         float* o = v_texture + i * C;
-        o[0] += a.x;
-        if (C > 1) o[1] += a.y;
-        if (C > 2) o[2] += a.z;
+        o[0] += tex_scale * a.x;
+        if (C > 1) o[1] += tex_scale * a.y;
+        if (C > 2) o[2] += tex_scale * a.z;
     };
     long long i = t0;
     for (; i + 3 * stride < num_texels; i += 4 * stride) {  // four independent loads in flight per thread
@@ -389,7 +389,7 @@ int launch_backward_stream(const StreamBwdParams& p, cudaStream_t st) {
                                         (int)sizeof(StreamShared)));
     texture_backward_stream_kernel<<<blocks, kStreamWarps * 32, sizeof(StreamShared), st>>>(p, env ? atoi(env) : 0);
     GSTEX_LAUNCH_CHECK();
-    unpack_grads_kernel<<<148 * 8, 256, 0, st>>>(p.tex_acc, p.num_texels, p.C, p.splat_acc, p.n, p.v_texture, p.v_colors,
+    unpack_grads_kernel<<<148 * 8, 256, 0, st>>>(p.tex_acc, p.num_texels, p.C, p.tex_scale, p.splat_acc, p.n, p.v_texture, p.v_colors,
                                                   p.v_opacity, p.v_means, p.v_scales, p.v_quats);
     GSTEX_LAUNCH_CHECK();
     return GSTEX_OK;

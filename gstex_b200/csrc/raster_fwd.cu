@@ -50,6 +50,7 @@ struct FwdParams {
     int32_t *final_idx, *depth_idx;
     uint32_t* unit_cursor;  // zeroed before the launch
     const int32_t* order;   // tiles, longest list first (nullptr: natural order)
+    float tex_scale, tex_bias;  // every fetched sample is tex_scale * sample + tex_bias (1, 0: the reference's call)
     int units_per_tile, num_units;
     int force_nocull;  // debugging / tests (GSTEX_DBG bit 4): evaluate every list entry for every unit
     StreamView sv;  // pair stream (REC kernels only)
@@ -211,6 +212,10 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
                 val0 = tq.w00 * __ldg(t00) + tq.w01 * __ldg(t01) + tq.w10 * __ldg(t10) + tq.w11 * __ldg(t11);
                 if (C > 1) val1 = tq.w00 * __ldg(t00 + 1) + tq.w01 * __ldg(t01 + 1) + tq.w10 * __ldg(t10 + 1) + tq.w11 * __ldg(t11 + 1);
                 if (C > 2) val2 = tq.w00 * __ldg(t00 + 2) + tq.w01 * __ldg(t01 + 2) + tq.w10 * __ldg(t10 + 2) + tq.w11 * __ldg(t11 + 2);
+                // affine texel activation (SH2RGB of the caller folded into the fetch; the weights sum to one)
+                val0 = fmaf(p.tex_scale, val0, p.tex_bias);
+                if (C > 1) val1 = fmaf(p.tex_scale, val1, p.tex_bias);
+                if (C > 2) val2 = fmaf(p.tex_scale, val2, p.tex_bias);
             }
             if (REC && rec_ok) {  // the m pairs are consecutive items of the unit's stream, list order
                 int new_chunk = cur_chunk;
@@ -338,8 +343,8 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
 #pragma unroll
                             for (int k = 0; k < CMAX; ++k) {
                                 if (k < C) {
-                                    const float val = tq.w00 * __ldg(t00 + k) + tq.w01 * __ldg(t01 + k) +
-                                                      tq.w10 * __ldg(t10 + k) + tq.w11 * __ldg(t11 + k);
+                                    const float val = fmaf(p.tex_scale, tq.w00 * __ldg(t00 + k) + tq.w01 * __ldg(t01 + k) +
+                                                      tq.w10 * __ldg(t10 + k) + tq.w11 * __ldg(t11 + k), p.tex_bias);
                                     tex[k] += vis * val;
                                 }
                             }
@@ -460,12 +465,12 @@ extern "C" size_t gstex_pair_stream_bytes(int img_height, int img_width, int blo
     return stream_fixed_bytes((int)units) + 256 + chunks * (sizeof(PairItem) * kChunkItems + sizeof(int32_t)) + 128;
 }
 
-extern "C" int gstex_texture_forward(int img_height, int img_width, int block_width, int channels, int n,
+extern "C" int gstex_texture_forward_act(int img_height, int img_width, int block_width, int channels, int n,
                                      int num_intersects, const int32_t* texture_dims,
                                      const int32_t* gaussian_ids_sorted, const int32_t* tile_bins, const float* colors,
                                      const float* opacities, const float* means, const float* scales, float glob_scale,
                                      const float* quats, const float* uv0, const float* umap, const float* vmap,
-                                     const float* texture, const float* viewmat, const float* c2w, float fx, float fy,
+                                     const float* texture, float tex_scale, float tex_bias, const float* viewmat, const float* c2w, float fx, float fy,
                                      float cx, float cy, int settings, const float* background, float* out_img,
                                      float* out_depth, float* out_reg, float* out_texture, float* out_normal,
                                      float* final_Ts, int32_t* final_idx, int32_t* depth_idx, float* out_reg_s,
@@ -506,6 +511,7 @@ extern "C" int gstex_texture_forward(int img_height, int img_width, int block_wi
     p.out_normal = out_normal; p.final_Ts = final_Ts; p.out_reg_s = out_reg_s; p.final_idx = final_idx;
     p.depth_idx = depth_idx;
     p.unit_cursor = ws_counters(workspace);
+    p.tex_scale = tex_scale; p.tex_bias = tex_bias;
     p.order = (n > 0 && tile_bins != nullptr && num_tiles <= kOrderMaxTiles) ? ws_order(workspace, n) : nullptr;
     p.units_per_tile = p.g.threads / 32;
     p.num_units = p.g.tiles_x * p.g.tiles_y * p.units_per_tile;
@@ -540,4 +546,18 @@ extern "C" int gstex_texture_forward(int img_height, int img_width, int block_wi
 #undef GSTEX_FWD_LAUNCH
     GSTEX_LAUNCH_CHECK();
     return GSTEX_OK;
+}
+
+extern "C" int gstex_texture_forward(int img_height, int img_width, int block_width, int channels, int n,
+                                     int num_intersects, const int32_t* texture_dims,
+                                     const int32_t* gaussian_ids_sorted, const int32_t* tile_bins, const float* colors,
+                                     const float* opacities, const float* means, const float* scales, float glob_scale,
+                                     const float* quats, const float* uv0, const float* umap, const float* vmap,
+                                     const float* texture, const float* viewmat, const float* c2w, float fx, float fy,
+                                     float cx, float cy, int settings, const float* background, float* out_img,
+                                     float* out_depth, float* out_reg, float* out_texture, float* out_normal,
+                                     float* final_Ts, int32_t* final_idx, int32_t* depth_idx, float* out_reg_s,
+                                     void* workspace, size_t workspace_bytes, void* pair_stream,
+                                     size_t pair_stream_bytes, void* stream) {
+    return gstex_texture_forward_act(img_height, img_width, block_width, channels, n, num_intersects, texture_dims, gaussian_ids_sorted, tile_bins, colors, opacities, means, scales, glob_scale, quats, uv0, umap, vmap, texture, 1.f, 0.f, viewmat, c2w, fx, fy, cx, cy, settings, background, out_img, out_depth, out_reg, out_texture, out_normal, final_Ts, final_idx, depth_idx, out_reg_s, workspace, workspace_bytes, pair_stream, pair_stream_bytes, stream);
 }

@@ -136,12 +136,19 @@ def texture_gaussians(
     use_torch_impl: bool = False,
     *,
     binning: Optional[TileBinning] = None,
+    texture_affine: Optional[Tuple[float, float]] = None,
 ):
     """Rasterizes textured 2D gaussians (ref: texture.py:14-150).
 
     `binning` (not in the reference): a request started earlier with `gstex_b200.utils.begin_binning` on the same
     `centers / extents / depths / num_tiles_hit`; the call then only waits for that request's sizes instead of
-    synchronising the stream (multi-view pipelining, see `TileBinning`)."""
+    synchronising the stream (multi-view pipelining, see `TileBinning`).
+
+    `texture_affine=(scale, bias)` (not in the reference): `texture` holds RAW texels and every fetched sample is
+    `scale * sample + bias`; the gradient returned for `texture` is with respect to the raw texels.  With
+    `(C0, 0.5)` = `SH2RGB` this replaces the caller's `texture[:, 0:3] = SH2RGB(texture_dc)` (NS/models/gstex.py:
+    1091-1121) -- two passes over all texels forward and two more backward per view -- by one multiply-add per
+    fetched sample."""
     assert block_width > 1 and block_width <= 16, "block_width must be between 2 and 16"
     if use_torch_impl:
         raise NotImplementedError("gstex_b200 has no PyTorch/CPU rasterizer: the CUDA kernels are the only path")
@@ -164,12 +171,13 @@ def texture_gaussians(
         num_tiles_hit.contiguous(), colors.contiguous(), opacity.contiguous(), means.contiguous(),
         scales.contiguous(), glob_scale, quats.contiguous(), uv0.contiguous(), umap.contiguous(), vmap.contiguous(),
         texture.contiguous(), viewmat.contiguous(), c2w.contiguous(), fx, fy, cx, cy, img_height, img_width,
-        block_width, settings, background.contiguous(), binning)
+        block_width, settings, background.contiguous(), binning,
+        (1.0, 0.0) if texture_affine is None else (float(texture_affine[0]), float(texture_affine[1])))
 
 
 def _raster_forward(texture_info, texture_dims, gaussian_ids_sorted, tile_bins, colors, opacity, means, scales,
                     glob_scale, quats, uv0, umap, vmap, texture, viewmat, c2w, fx, fy, cx, cy, img_height, img_width,
-                    block_width, settings, background, num_intersects, record_pairs=False):
+                    block_width, settings, background, num_intersects, record_pairs=False, texture_affine=(1.0, 0.0)):
     """ref: `_C.texture_forward` (cuda/csrc/texture.cu:762-901).  Returns the 9 tensors + the workspace
     holding the per-view packed records (re-used by the backward)."""
     dev = _lib.require_cuda(texture_dims, colors, opacity, means, scales, quats, uv0, umap, vmap, texture, viewmat,
@@ -203,10 +211,11 @@ def _raster_forward(texture_info, texture_dims, gaussian_ids_sorted, tile_bins, 
         pairs = torch.empty((nbytes,), dtype=torch.uint8, device=dev)
     p = _lib.ptr
     with torch.cuda.device(dev):
-        rc = lib.gstex_texture_forward(
+        rc = lib.gstex_texture_forward_act(
             H, W, int(block_width), C, n, int(num_intersects), p(texture_dims), p(gaussian_ids_sorted), p(tile_bins),
             p(colors), p(opacity), p(means), p(scales), float(glob_scale), p(quats), p(uv0), p(umap), p(vmap),
-            p(texture), p(viewmat), p(c2w), float(fx), float(fy), float(cx), float(cy), int(settings), p(background),
+            p(texture), float(texture_affine[0]), float(texture_affine[1]), p(viewmat), p(c2w), float(fx), float(fy),
+            float(cx), float(cy), int(settings), p(background),
             p(out_img), p(out_depth), p(out_reg), p(out_texture), p(out_normal), p(final_Ts), p(final_idx),
             p(depth_idx), p(out_reg_s), p(ws), ws.numel(), p(pairs), pairs.numel() if pairs is not None else 0,
             _lib.stream_ptr(dev))
@@ -222,7 +231,7 @@ class _TextureGaussians(Function):
     @staticmethod
     def forward(ctx, texture_info, texture_dims, centers, extents, depths, num_tiles_hit, colors, opacity, means,
                 scales, glob_scale, quats, uv0, umap, vmap, texture, viewmat, c2w, fx, fy, cx, cy, img_height,
-                img_width, block_width, settings, background=None, binning=None):
+                img_width, block_width, settings, background=None, binning=None, texture_affine=(1.0, 0.0)):
         num_points = centers.size(0)
         tile_bounds = ((img_width + block_width - 1) // block_width, (img_height + block_width - 1) // block_width, 1)
         dev = centers.device
@@ -237,7 +246,7 @@ class _TextureGaussians(Function):
                                              opacity, means, scales, glob_scale, quats, uv0, umap, vmap, texture,
                                              viewmat, c2w, fx, fy, cx, cy, img_height, img_width, block_width,
                                              settings, background, max(num_intersects, 0),
-                                             record_pairs=any(ctx.needs_input_grad))
+                                             record_pairs=any(ctx.needs_input_grad), texture_affine=texture_affine)
         out_img, out_depth, out_reg, out_texture, out_normal, final_Ts, final_idx, depth_idx, out_reg_s = outputs
         ctx.img_width, ctx.img_height = img_width, img_height
         ctx.texture_info = texture_info
@@ -246,6 +255,7 @@ class _TextureGaussians(Function):
         ctx.num_intersects = num_intersects
         ctx.block_width = block_width
         ctx.settings = settings
+        ctx.texture_affine = texture_affine
         ctx.workspace = ws  # packed per-view records, valid as long as the inputs are unchanged
         ctx.pair_stream = pairs  # contributing pairs recorded by the forward (None: the backward recomputes)
         # fused accumulation (GradientTargets): only when every gradient is wanted and every input is registered
@@ -308,10 +318,11 @@ class _TextureGaussians(Function):
             else:
                 clean = _SCRATCH_CLEAN
         with torch.cuda.device(dev):
-            rc = lib.gstex_texture_backward(
+            rc = lib.gstex_texture_backward_act(
                 int(H), int(W), int(ctx.block_width), C, means.shape[0], max(int(ctx.num_intersects), 0),
                 p(texture_dims), p(gaussian_ids_sorted), p(tile_bins), p(colors), p(opacity), p(means), p(scales),
-                float(ctx.glob_scale), p(quats), p(uv0), p(umap), p(vmap), p(texture), p(viewmat), p(c2w),
+                float(ctx.glob_scale), p(quats), p(uv0), p(umap), p(vmap), p(texture), float(ctx.texture_affine[0]),
+                float(ctx.texture_affine[1]), p(viewmat), p(c2w),
                 float(ctx.fx), float(ctx.fy), float(ctx.cx), float(ctx.cy), int(ctx.settings), p(background),
                 p(final_Ts), p(final_idx), p(depth_idx), p(out_reg_s), p(v_out_img), p(v_out_depth), p(v_out_reg),
                 p(v_out_alpha), p(v_out_texture), p(v_out_normal), p(v_colors), p(v_opacity), p(v_means),
@@ -325,6 +336,6 @@ class _TextureGaussians(Function):
                 _GRAD_SCRATCH.clear()
             _GRAD_SCRATCH[scratch_key] = scratch
         if targets is not None:  # already added to the registered tensors
-            return (None,) * 28
+            return (None,) * 29
         return (None, None, None, None, None, None, v_colors, v_opacity, v_means, v_scales, None, v_quats, v_uv0,
-                v_umap, v_vmap, v_texture, None, None, None, None, None, None, None, None, None, None, None, None)
+                v_umap, v_vmap, v_texture, None, None, None, None, None, None, None, None, None, None, None, None, None)

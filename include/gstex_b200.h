@@ -185,6 +185,36 @@ int gstex_texture_backward(int img_height, int img_width, int block_width, int c
                            float* v_texture, void* workspace, size_t workspace_bytes, int records_valid,
                            void* pair_stream, size_t pair_stream_bytes, void* grad_scratch, size_t grad_scratch_size,
                            long long num_texels, int zero_fill, void* stream);
+/* Next row, the texel half of the caller's colour stage: the reference trainer
+ * builds `texture = SH2RGB(texture_dc)` = 0.28209479 * texture_dc + 0.5 over all T texels before every call
+ * (NS/models/gstex.py:1091-1121, two passes over T*C floats forward and two more in autograd's backward).  The
+ * `_act` entry points take the raw texels and apply `tex_scale * sample + tex_bias` to every fetched bilinear
+ * sample instead (exact for an affine map: the four weights sum to one); the backward returns the gradient with
+ * respect to the RAW texels (times tex_scale, applied where the texel gradients are unpacked).  (1, 0) is the plain
+ * entry point, bit for bit. */
+int gstex_texture_forward_act(int img_height, int img_width, int block_width, int channels, int n, int num_intersects,
+                          const int32_t* texture_dims, const int32_t* gaussian_ids_sorted, const int32_t* tile_bins,
+                          const float* colors, const float* opacities, const float* means, const float* scales,
+                          float glob_scale, const float* quats, const float* uv0, const float* umap,
+                          const float* vmap, const float* texture, float tex_scale, float tex_bias, const float* viewmat, const float* c2w, float fx,
+                          float fy, float cx, float cy, int settings, const float* background, float* out_img,
+                          float* out_depth, float* out_reg, float* out_texture, float* out_normal, float* final_Ts,
+                          int32_t* final_idx, int32_t* depth_idx, float* out_reg_s, void* workspace,
+                          size_t workspace_bytes, void* pair_stream, size_t pair_stream_bytes, void* stream);
+int gstex_texture_backward_act(int img_height, int img_width, int block_width, int channels, int n, int num_intersects,
+                           const int32_t* texture_dims, const int32_t* gaussian_ids_sorted, const int32_t* tile_bins,
+                           const float* colors, const float* opacities, const float* means, const float* scales,
+                           float glob_scale, const float* quats, const float* uv0, const float* umap,
+                           const float* vmap, const float* texture, float tex_scale, float tex_bias, const float* viewmat, const float* c2w, float fx,
+                           float fy, float cx, float cy, int settings, const float* background,
+                           const float* final_Ts, const int32_t* final_idx, const int32_t* depth_idx,
+                           const float* final_s, const float* v_output, const float* v_output_depth,
+                           const float* v_output_reg, const float* v_output_alpha, const float* v_output_texture,
+                           const float* v_output_normal, float* v_colors, float* v_opacity, float* v_means,
+                           float* v_scales, float* v_quats, float* v_uv0, float* v_umap, float* v_vmap,
+                           float* v_texture, void* workspace, size_t workspace_bytes, int records_valid,
+                           void* pair_stream, size_t pair_stream_bytes, void* grad_scratch, size_t grad_scratch_size,
+                           long long num_texels, int zero_fill, void* stream);
 
 /* ---- next row: per-splat colour from spherical harmonics -------------------- */
 

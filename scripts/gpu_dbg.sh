@@ -6,6 +6,6 @@ for d in "$@"; do
 import json
 d=json.load(open("gpurun_out/dbg_$d.json"))
 e=d["roofline"]["per_entry_ms_per_view"]
-print("dbg=$d ms/view",round(d["config"]["ms_per_view"],3),"fwd",round(e["gstex_texture_forward"],3),"bwd",round(e["gstex_texture_backward"],3))
+print("dbg=$d ms/view",round(d["config"]["ms_per_view"],3),"fwd",round(e.get("gstex_texture_forward_act", e.get("gstex_texture_forward")),3),"bwd",round(e.get("gstex_texture_backward_act", e.get("gstex_texture_backward")),3))
 PY
 done

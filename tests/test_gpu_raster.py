@@ -358,3 +358,45 @@ def test_gradient_scratch_is_returned_all_zero(backward_path):
         err = float((a - b).abs().max())
         assert err <= 2e-5 * scale + 1e-30, f"{k}: backward over the cached scratch differs ({err:.3e} at scale {scale:.3e})"
     assert float(first[8].abs().max()) > 0
+
+
+def test_texture_affine_matches_activated_texture(backward_path):
+    """`texture_affine=(C0, 0.5)` on raw texels == the reference caller's `texture = SH2RGB(texture_dc)` followed by
+    the plain call (NS/models/gstex.py:1091-1121), forward and -- through the chain rule -- backward."""
+    import gstex_b200 as G
+    from gstex_b200.synthetic import make_scene, make_upstream_grads
+
+    C0 = 0.28209479177387814
+    s = make_scene("cfg2", n=20000, width=256, height=256)
+    v = {k: x.cuda() for k, x in make_upstream_grads(s).items()}
+    sd = {k: (x.cuda() if isinstance(x, torch.Tensor) else x) for k, x in s.items()}
+    intr = (s["fx"], s["fy"], s["cx"], s["cy"])
+    H, W, bw = s["H"], s["W"], 16
+    keys = ["colors", "opacities", "means", "scales", "quats", "uv0", "umap", "vmap", "texture"]
+    raw = (sd["texture"] - 0.5) / C0          # texture_dc whose SH2RGB is the scene's texture
+    vm, c2w = s["viewmats"][0].cuda().contiguous(), s["c2ws"][0].cuda().contiguous()
+
+    def run(fused):
+        params = [sd[k].clone().requires_grad_(True) for k in keys]
+        pd = dict(zip(keys, params))
+        pd["texture"] = params[8] = raw.clone().requires_grad_(True)
+        tex = pd["texture"] if fused else pd["texture"] * C0 + 0.5
+        _, depths, centers, extents, nth = G.project_bounds(pd["means"].detach(), pd["scales"].detach(), 1,
+                                                            pd["quats"].detach(), vm, intr, H, W, bw)
+        outs = G.texture_gaussians(s["texture_info"], sd["texture_dims"], centers, extents, depths, nth, pd["colors"],
+                                   pd["opacities"], pd["means"], pd["scales"], 1, pd["quats"], pd["uv0"], pd["umap"],
+                                   pd["vmap"], tex, vm, c2w, *intr, H, W, bw, s["settings"], sd["background"],
+                                   texture_affine=(C0, 0.5) if fused else None)
+        torch.autograd.backward(list(outs), [v["v_out_img"], v["v_out_depth"], v["v_out_reg"], v["v_out_alpha"],
+                                             v["v_out_texture"], v["v_out_normal"]])
+        return [o.detach() for o in outs], [p.grad for p in params]
+
+    (o_ref, g_ref), (o_fus, g_fus) = run(False), run(True)
+    for nm, a, b in zip(["out_img", "out_depth", "out_reg", "out_alpha", "out_texture", "out_normal"], o_ref, o_fus):
+        err = float((a - b).abs().max())
+        assert err <= 2e-6 * max(float(a.abs().max()), 1e-30), f"{nm}: {err:.3e}"
+    for k, a, b in zip(keys, g_ref, g_fus):
+        scale = float(a.abs().max())
+        err = float((a - b).abs().max())
+        assert err <= 3e-5 * scale + 1e-30, f"{k}: fused activation differs ({err:.3e} at scale {scale:.3e})"
+    assert float(g_ref[8].abs().max()) > 0
