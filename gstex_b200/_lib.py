@@ -52,6 +52,9 @@ _SIGNATURES = {
     "gstex_compute_sh_forward": (I, [I, I, I, P, P, P, P]),
     "gstex_compute_sh_backward": (I, [I, I, I, P, P, P, P]),
     "gstex_texture_sample_forward": (I, [I, I, P, P, P, P, P]),
+    "gstex_photometric_loss_scratch_bytes": (SZ, [I, I]),
+    "gstex_photometric_loss_forward": (I, [I, I, I, P, P, P, P, P, P, F, I, F, P, P, P, P, SZ, P]),
+    "gstex_photometric_loss_backward": (I, [I, I, I, P, P, P, P, P, P, F, I, F, P, P, P, P, P, P]),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)

@@ -239,6 +239,32 @@ int gstex_compute_sh_backward(int n, int degree, int degrees_to_use, const float
 int gstex_texture_sample_forward(int num_queries, int channels, const int32_t* texture_dims, const float* uvs,
                                  const float* texture, float* out, void* stream);
 
+/* ---- next row: compositing + photometric loss on the far side of the path ------- */
+
+/* ref: nerfstudio/models/gstex.py:1204-1205 (rgb = clamp(out_img + out_texture[:,:,0:3] + (1 - out_alpha) * background,
+ * 0, 1)), :1297-1302 (optional mask on both images; Ll1 = mean |gt - rgb|; SSIM(gt, rgb)) and :1319 (main_loss =
+ * (1 - ssim_lambda) * Ll1 + ssim_lambda * (1 - SSIM)).  SSIM = pytorch_msssim.SSIM(data_range=1, size_average=True,
+ * channel=3) (gstex.py:33,351; third-party, unpinned in pyproject.toml:60): win_size taps of a Gaussian (win_sigma),
+ * no padding, K = (0.01, 0.03); only win_size == 11 is built, img_height and img_width must be >= 11.
+ * out_img (H,W,3), out_texture (H,W,C>=3), out_alpha (H,W), background (3), gt_img (H,W,3) already composited with
+ * the background, mask (H,W) or NULL.  Outputs: rgb (H,W,3); losses[3] = {Ll1, SSIM, main_loss}; ssim_maps
+ * (3,H,W,3) partial derivatives kept for the backward, or NULL when no gradient is wanted.  scratch: per-block
+ * partial sums, gstex_photometric_loss_scratch_bytes(H, W) bytes; they are added in a fixed order (deterministic). */
+size_t gstex_photometric_loss_scratch_bytes(int img_height, int img_width);
+int gstex_photometric_loss_forward(int img_height, int img_width, int channels, const float* out_img,
+                                   const float* out_texture, const float* out_alpha, const float* background,
+                                   const float* gt_img, const float* mask, float ssim_lambda, int win_size,
+                                   float win_sigma, float* rgb, float* losses, float* ssim_maps, void* scratch,
+                                   size_t scratch_bytes, void* stream);
+/* Gradients of main_loss (times *v_main_loss, a DEVICE scalar; NULL = 1) with respect to the three rendered layers:
+ * v_out_img (H,W,3), v_out_texture (H,W,C; channels >= 3 zero), v_out_alpha (H,W); every element written.  This is
+ * what autograd produces from gstex.py:1204-1205,1301-1319 and hands to _TextureGaussians.backward. */
+int gstex_photometric_loss_backward(int img_height, int img_width, int channels, const float* out_img,
+                                    const float* out_texture, const float* out_alpha, const float* background,
+                                    const float* gt_img, const float* mask, float ssim_lambda, int win_size,
+                                    float win_sigma, const float* ssim_maps, const float* v_main_loss, float* v_out_img,
+                                    float* v_out_texture, float* v_out_alpha, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

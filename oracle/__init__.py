@@ -23,7 +23,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _BUILD = os.path.join(_HERE, "_build")
 _SO = os.path.join(_BUILD, "libgstex_oracle.so")
 _SRCS = [os.path.join(_HERE, "gstex_oracle.c"), os.path.join(_HERE, "gstex_oracle_raster.c"),
-         os.path.join(_HERE, "gstex_oracle_sh.c"), os.path.join(_HERE, "gstex_oracle_sample.c")]
+         os.path.join(_HERE, "gstex_oracle_sh.c"), os.path.join(_HERE, "gstex_oracle_sample.c"),
+         os.path.join(_HERE, "gstex_oracle_loss.c")]
 
 _lib = None
 
@@ -214,4 +215,41 @@ def texture_sample(texture_info, texture_dims: np.ndarray, texture: np.ndarray, 
     f = ctypes.POINTER(ctypes.c_float)
     lib().orc_texture_sample(ctypes.c_int(q), ctypes.c_int(C), texture_dims.ctypes.data_as(ctypes.POINTER(ctypes.c_int32)),
                              uvs.ctypes.data_as(f), texture.ctypes.data_as(f), out.ctypes.data_as(f))
+    return out
+
+
+# ---- compositing + photometric loss (nerfstudio/models/gstex.py:1204-1205, 1297-1302, 1319) -------------------
+
+def photometric_loss(out_img: np.ndarray, out_texture: np.ndarray, out_alpha: np.ndarray, background: np.ndarray,
+                     gt_img: np.ndarray, ssim_lambda: float = 0.2, mask=None, v_main: float = 1.0, grads: bool = True):
+    """Returns dict(rgb, Ll1, ssim, main_loss[, v_out_img, v_out_texture, v_out_alpha]); SSIM as pytorch_msssim's
+    `SSIM(data_range=1.0, size_average=True, channel=3)` (gstex.py:351), window 11 / sigma 1.5."""
+    out_img = np.ascontiguousarray(out_img, np.float32)
+    out_texture = np.ascontiguousarray(out_texture, np.float32)
+    out_alpha = np.ascontiguousarray(out_alpha, np.float32)
+    background = np.ascontiguousarray(background, np.float32)
+    gt_img = np.ascontiguousarray(gt_img, np.float32)
+    H, W, C = out_texture.shape
+    f = ctypes.POINTER(ctypes.c_float)
+    null = ctypes.cast(None, f)
+    if mask is not None:
+        mask = np.ascontiguousarray(np.asarray(mask, np.float32).reshape(H, W))
+    rgb = np.empty((H, W, 3), np.float32)
+    losses = np.empty(3, np.float32)
+    v_img = np.empty((H, W, 3), np.float32) if grads else None
+    v_tex = np.empty((H, W, C), np.float32) if grads else None
+    v_alpha = np.empty((H, W), np.float32) if grads else None
+    fn = lib().orc_photometric_loss
+    fn.restype = ctypes.c_int
+    rc = fn(ctypes.c_int(H), ctypes.c_int(W), ctypes.c_int(C), out_img.ctypes.data_as(f), out_texture.ctypes.data_as(f),
+            out_alpha.ctypes.data_as(f), background.ctypes.data_as(f), gt_img.ctypes.data_as(f),
+            mask.ctypes.data_as(f) if mask is not None else null, ctypes.c_float(ssim_lambda), ctypes.c_float(1.5),
+            ctypes.c_float(v_main), rgb.ctypes.data_as(f), losses.ctypes.data_as(f),
+            v_img.ctypes.data_as(f) if grads else null, v_tex.ctypes.data_as(f) if grads else null,
+            v_alpha.ctypes.data_as(f) if grads else null)
+    if rc != 0:
+        raise ValueError("photometric_loss: image smaller than the 11x11 window, or fewer than 3 texture channels")
+    out = dict(rgb=rgb, Ll1=float(losses[0]), ssim=float(losses[1]), main_loss=float(losses[2]))
+    if grads:
+        out.update(v_out_img=v_img, v_out_texture=v_tex, v_out_alpha=v_alpha)
     return out
