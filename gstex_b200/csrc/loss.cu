@@ -17,7 +17,7 @@
 // the SSIM algebra + the three partial-derivative maps the backward needs), a one-block reduction of the per-block
 // partial sums in a fixed order (deterministic), and one backward kernel that pulls the derivative maps back through
 // the window (again separably in shared memory) and writes v_out_img / v_out_texture / v_out_alpha in the same pass.
-// HBM-bound by contract: forward reads 4*(10 + C) B and writes 48 B per pixel, backward reads 4*(19 + C) B and writes
+// By contract an HBM stream: forward reads 4*(10 + C) B and writes 48 B per pixel, backward reads 4*(19 + C) B and writes
 // 4*(4 + C) B.  sm_100a.
 #include "common.cuh"
 
@@ -26,7 +26,8 @@ namespace gstex {
 constexpr int kWin = 11;              // pytorch_msssim default win_size
 constexpr int kLossTile = 16;         // owned pixels per block edge
 constexpr int kHalo = kLossTile + kWin - 1;  // 26
-constexpr int kPitch = kHalo + 1;     // shared-memory row pitch (odd: column walks do not conflict)
+constexpr int kHaloE = kHalo * 3;     // floats per halo row (three interleaved channels)
+constexpr int kRowPitch = 80;         // shared-memory row pitch: 16 banks from row to row
 
 struct LossWindow { float g[kWin]; };
 
@@ -34,17 +35,6 @@ struct LossDims {
     int H, W, C;       // image size, channels of out_texture (>= 3; only the first three are composited)
     int Hv, Wv;        // valid SSIM positions: H - 10, W - 10
 };
-
-// compose one pixel's three channels exactly as torch evaluates gstex.py:1204-1205 (no contraction: every product
-// and sum rounded on its own), returns the pre-clamp values
-__device__ __forceinline__ void compose_pixel(const float* __restrict__ out_img, const float* __restrict__ out_texture,
-                                              const float* __restrict__ out_alpha, const float bg[3], int C, size_t pix,
-                                              float pre[3]) {
-    const float om = __fsub_rn(1.f, out_alpha[pix]);
-#pragma unroll
-    for (int k = 0; k < 3; ++k)
-        pre[k] = __fadd_rn(__fadd_rn(out_img[pix * 3 + k], out_texture[pix * C + k]), __fmul_rn(om, bg[k]));
-}
 
 __device__ __forceinline__ float clamp_unit(float v) { return fminf(fmaxf(v, 0.f), 1.f); }
 
@@ -64,6 +54,11 @@ __device__ __forceinline__ float block_sum_256(float v, float* red) {
 // One block = 16x16 owned pixels (the SSIM positions whose window STARTS there) + the 26x26 pixels their windows cover.
 // maps: [3][H][W][3] = d ssim / d mu_pred, d ssim / d E[pred^2], d ssim / d E[gt*pred] per position and channel,
 // zero where the position is not a valid window start (written only when maps != nullptr).
+// Shared-memory traffic is what bounds a naive version (one output per thread = 2 loads per 5 FMAs; ncu: L1/shared
+// pipe 87 % busy, mio_throttle the top stall), so both passes are register-tiled: a pass-1 thread walks 18 rows of one
+// (column, channel) and produces 8 output rows of all five moments (36 loads for 440 FMAs), a pass-2 thread walks 14
+// columns and produces 4 outputs (70 loads for 220 FMAs).  Pixels stay channel-interleaved in shared memory, as in
+// HBM, so the global loads/stores are contiguous row segments and consecutive threads hit consecutive banks.
 __global__ void __launch_bounds__(256) loss_forward_kernel(LossDims d, LossWindow win, const float* __restrict__ out_img,
                                                            const float* __restrict__ out_texture,
                                                            const float* __restrict__ out_alpha,
@@ -71,82 +66,113 @@ __global__ void __launch_bounds__(256) loss_forward_kernel(LossDims d, LossWindo
                                                            const float* __restrict__ gt, const float* __restrict__ mask,
                                                            float* __restrict__ rgb, float* __restrict__ maps,
                                                            float2* __restrict__ partials) {
-    __shared__ float sx[3][kHalo][kPitch];  // gt (masked)
-    __shared__ float sy[3][kHalo][kPitch];  // predicted (masked)
-    __shared__ float st[5][kLossTile][kPitch];
+    __shared__ float sx[kHalo][kRowPitch];             // gt (masked), [row][column * 3 + channel]
+    __shared__ float sy[kHalo][kRowPitch];             // predicted (masked)
+    __shared__ float st[5][kLossTile][kRowPitch];      // the five moments after pass 1
     __shared__ float red[8];
     const int i0 = blockIdx.y * kLossTile, j0 = blockIdx.x * kLossTile;
-    const float bg[3] = {background[0], background[1], background[2]};
     float l1 = 0.f;
-    for (int t = threadIdx.x; t < kHalo * kHalo; t += 256) {
-        const int r = t / kHalo, c = t - r * kHalo;
+    for (int t = threadIdx.x; t < kHalo * kHaloE; t += 256) {
+        const int r = t / kHaloE, e = t - r * kHaloE, c = e / 3, k = e - c * 3;
         const int gi = i0 + r, gj = j0 + c;
-        float x[3] = {0.f, 0.f, 0.f}, y[3] = {0.f, 0.f, 0.f};
+        float x = 0.f, y = 0.f;
         if (gi < d.H && gj < d.W) {
             const size_t pix = (size_t)gi * d.W + gj;
-            float pre[3];
-            compose_pixel(out_img, out_texture, out_alpha, bg, d.C, pix, pre);
-            const float m = mask ? mask[pix] : 1.f;
-            const bool owned = r < kLossTile && c < kLossTile;
-#pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                const float v = clamp_unit(pre[k]);
-                if (owned) rgb[pix * 3 + k] = v;
-                x[k] = __fmul_rn(gt[pix * 3 + k], m);  // gstex.py:1297-1298 (gt_img * mask, pred_img * mask)
-                y[k] = __fmul_rn(v, m);
-                if (owned) l1 += fabsf(x[k] - y[k]);
+            // gstex.py:1204-1205 as torch evaluates it (no contraction: every product and sum rounded on its own)
+            const float om = __fsub_rn(1.f, __ldg(out_alpha + pix));
+            const float pre = __fadd_rn(__fadd_rn(__ldg(out_img + pix * 3 + k), __ldg(out_texture + pix * d.C + k)),
+                                        __fmul_rn(om, __ldg(background + k)));
+            const float v = clamp_unit(pre);
+            const float m = mask ? __ldg(mask + pix) : 1.f;
+            x = __fmul_rn(__ldg(gt + pix * 3 + k), m);  // gstex.py:1297-1298 (gt_img * mask, pred_img * mask)
+            y = __fmul_rn(v, m);
+            if (r < kLossTile && c < kLossTile) {
+                rgb[pix * 3 + k] = v;
+                l1 += fabsf(x - y);
             }
         }
-#pragma unroll
-        for (int k = 0; k < 3; ++k) { sx[k][r][c] = x[k]; sy[k][r][c] = y[k]; }
+        sx[r][e] = x; sy[r][e] = y;
     }
     __syncthreads();
-    const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;  // (K1 * data_range)^2, (K2 * data_range)^2
-    const int pr = threadIdx.x >> 4, pc = threadIdx.x & 15;  // this thread's owned position
-    const int gi = i0 + pr, gj = j0 + pc;
-    const bool valid = gi < d.Hv && gj < d.Wv;
+    // pass 1, along H (pytorch_msssim filters dim 2 first)
+    if (threadIdx.x < 2 * kHaloE) {
+        const int half = threadIdx.x / kHaloE, e = threadIdx.x - half * kHaloE, r0 = half * 8;
+        float acc[8][5];
+#pragma unroll
+        for (int o = 0; o < 8; ++o)
+#pragma unroll
+            for (int m = 0; m < 5; ++m) acc[o][m] = 0.f;
+#pragma unroll
+        for (int rin = 0; rin < 8 + kWin - 1; ++rin) {
+            const float x = sx[r0 + rin][e], y = sy[r0 + rin][e];
+            const float xx = x * x, yy = y * y, xy = x * y;
+#pragma unroll
+            for (int o = 0; o < 8; ++o) {
+                const int q = rin - o;
+                if (q >= 0 && q < kWin) {
+                    const float g = win.g[q];
+                    acc[o][0] = fmaf(g, x, acc[o][0]); acc[o][1] = fmaf(g, y, acc[o][1]);
+                    acc[o][2] = fmaf(g, xx, acc[o][2]); acc[o][3] = fmaf(g, yy, acc[o][3]);
+                    acc[o][4] = fmaf(g, xy, acc[o][4]);
+                }
+            }
+        }
+#pragma unroll
+        for (int o = 0; o < 8; ++o)
+#pragma unroll
+            for (int m = 0; m < 5; ++m) st[m][r0 + o][e] = acc[o][m];
+    }
+    __syncthreads();
+    // pass 2, along W, then the SSIM algebra (_ssim of pytorch_msssim/ssim.py); 4 positions of one channel per thread
     float ssim = 0.f;
-    for (int k = 0; k < 3; ++k) {
-        // pass 1, along H (pytorch_msssim filters dim 2 first): rows 0..15, columns 0..25
-        for (int t = threadIdx.x; t < kLossTile * kHalo; t += 256) {
-            const int r = t / kHalo, c = t - r * kHalo;
-            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f;
+    if (threadIdx.x < 3 * 4 * kLossTile) {
+        const int k = threadIdx.x % 3, cg = (threadIdx.x / 3) & 3, r = threadIdx.x / 12;
+        float acc[4][5];
 #pragma unroll
-            for (int q = 0; q < kWin; ++q) {
-                const float x = sx[k][r + q][c], y = sy[k][r + q][c], g = win.g[q];
-                a0 = fmaf(g, x, a0); a1 = fmaf(g, y, a1);
-                a2 = fmaf(g, x * x, a2); a3 = fmaf(g, y * y, a3); a4 = fmaf(g, x * y, a4);
-            }
-            st[0][r][c] = a0; st[1][r][c] = a1; st[2][r][c] = a2; st[3][r][c] = a3; st[4][r][c] = a4;
-        }
-        __syncthreads();
-        // pass 2, along W, then the SSIM algebra (_ssim of pytorch_msssim/ssim.py)
-        float mu1 = 0.f, mu2 = 0.f, exx = 0.f, eyy = 0.f, exy = 0.f;
+        for (int o = 0; o < 4; ++o)
 #pragma unroll
-        for (int q = 0; q < kWin; ++q) {
-            const float g = win.g[q];
-            mu1 = fmaf(g, st[0][pr][pc + q], mu1); mu2 = fmaf(g, st[1][pr][pc + q], mu2);
-            exx = fmaf(g, st[2][pr][pc + q], exx); eyy = fmaf(g, st[3][pr][pc + q], eyy);
-            exy = fmaf(g, st[4][pr][pc + q], exy);
-        }
-        const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
-        const float s1 = exx - mu1_sq, s2 = eyy - mu2_sq, s12 = exy - mu12;
-        const float A1 = 2.f * mu12 + C1, A2 = 2.f * s12 + C2, B1 = mu1_sq + mu2_sq + C1, B2 = s1 + s2 + C2;
-        const float rB1 = 1.f / B1, rB2 = 1.f / B2;
-        const float cs = A2 * rB2, lum = A1 * rB1;
-        if (valid) ssim += lum * cs;
-        if (maps != nullptr && gi < d.H && gj < d.W) {
-            // partial derivatives of lum*cs with E[y], E[y^2], E[xy] as the independent moments of the prediction y
-            float dmu = 0.f, dyy = 0.f, dxy = 0.f;
-            if (valid) {
-                dyy = -lum * cs * rB2;
-                dxy = 2.f * lum * rB2;
-                dmu = 2.f * rB1 * (mu1 * cs - mu2 * lum * cs) - 2.f * mu2 * dyy - mu1 * dxy;
+            for (int m = 0; m < 5; ++m) acc[o][m] = 0.f;
+#pragma unroll
+        for (int cin = 0; cin < 4 + kWin - 1; ++cin) {
+            float v[5];
+#pragma unroll
+            for (int m = 0; m < 5; ++m) v[m] = st[m][r][(4 * cg + cin) * 3 + k];
+#pragma unroll
+            for (int o = 0; o < 4; ++o) {
+                const int q = cin - o;
+                if (q >= 0 && q < kWin) {
+                    const float g = win.g[q];
+#pragma unroll
+                    for (int m = 0; m < 5; ++m) acc[o][m] = fmaf(g, v[m], acc[o][m]);
+                }
             }
-            const size_t plane = (size_t)d.H * d.W * 3, o = ((size_t)gi * d.W + gj) * 3 + k;
-            maps[o] = dmu; maps[plane + o] = dyy; maps[2 * plane + o] = dxy;
         }
-        __syncthreads();
+        const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;  // (K1 * data_range)^2, (K2 * data_range)^2
+        const int gi = i0 + r;
+        const size_t plane = (size_t)d.H * d.W * 3;
+#pragma unroll
+        for (int o = 0; o < 4; ++o) {
+            const int gj = j0 + 4 * cg + o;
+            const bool valid = gi < d.Hv && gj < d.Wv;
+            const float mu1 = acc[o][0], mu2 = acc[o][1];
+            const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
+            const float s1 = acc[o][2] - mu1_sq, s2 = acc[o][3] - mu2_sq, s12 = acc[o][4] - mu12;
+            const float A1 = 2.f * mu12 + C1, A2 = 2.f * s12 + C2, B1 = mu1_sq + mu2_sq + C1, B2 = s1 + s2 + C2;
+            const float rB1 = 1.f / B1, rB2 = 1.f / B2;
+            const float cs = A2 * rB2, lum = A1 * rB1;
+            if (valid) ssim += lum * cs;
+            if (maps != nullptr && gi < d.H && gj < d.W) {
+                // partial derivatives of lum*cs with E[y], E[y^2], E[xy] as the independent moments of the prediction y
+                float dmu = 0.f, dyy = 0.f, dxy = 0.f;
+                if (valid) {
+                    dyy = -lum * cs * rB2;
+                    dxy = 2.f * lum * rB2;
+                    dmu = 2.f * rB1 * (mu1 * cs - mu2 * lum * cs) - 2.f * mu2 * dyy - mu1 * dxy;
+                }
+                const size_t idx = ((size_t)gi * d.W + gj) * 3 + k;
+                maps[idx] = dmu; maps[plane + idx] = dyy; maps[2 * plane + idx] = dxy;
+            }
+        }
     }
     const float l1_sum = block_sum_256(l1, red);
     const float ssim_sum = block_sum_256(ssim, red);
@@ -174,6 +200,8 @@ __global__ void __launch_bounds__(256) loss_finalize_kernel(const float2* __rest
 }
 
 // One block = 16x16 owned pixels; the window positions that cover them start up to 10 rows/columns earlier.
+// Same register tiling as the forward; the transpose of pass 2 then of pass 1 (the window is symmetric, so the
+// adjoint is the same filter read from 10 positions earlier).
 __global__ void __launch_bounds__(256) loss_backward_kernel(LossDims d, LossWindow win, float ssim_lambda,
                                                             const float* __restrict__ v_main,
                                                             const float* __restrict__ out_img,
@@ -184,74 +212,97 @@ __global__ void __launch_bounds__(256) loss_backward_kernel(LossDims d, LossWind
                                                             const float* __restrict__ maps, float* __restrict__ v_out_img,
                                                             float* __restrict__ v_out_texture,
                                                             float* __restrict__ v_out_alpha) {
-    __shared__ float sm[3][3][kHalo][kPitch];  // [map][channel][row][col], rows/cols start at (i0 - 10, j0 - 10)
-    __shared__ float su[3][kLossTile][kPitch];
+    __shared__ float sm[3][kHalo][kRowPitch];      // [map][row][column * 3 + channel], origin (i0 - 10, j0 - 10)
+    __shared__ float su[3][kLossTile][kRowPitch];  // after the column pass
+    __shared__ float sg[kLossTile][kLossTile * 3 + 1];  // gradient * background per (pixel, channel)
     const int i0 = blockIdx.y * kLossTile, j0 = blockIdx.x * kLossTile;
     const size_t plane = (size_t)d.H * d.W * 3;
-    for (int t = threadIdx.x; t < kHalo * kHalo * 3; t += 256) {
-        const int r = t / (kHalo * 3), rem = t - r * (kHalo * 3), c = rem / 3, k = rem - c * 3;
+    for (int t = threadIdx.x; t < kHalo * kHaloE; t += 256) {
+        const int r = t / kHaloE, e = t - r * kHaloE, c = e / 3;
         const int gi = i0 - (kWin - 1) + r, gj = j0 - (kWin - 1) + c;
-        float a = 0.f, b = 0.f, e = 0.f;
+        float a = 0.f, b = 0.f, f = 0.f;
         if (gi >= 0 && gj >= 0 && gi < d.H && gj < d.W) {
-            const size_t o = ((size_t)gi * d.W + gj) * 3 + k;
-            a = __ldg(maps + o); b = __ldg(maps + plane + o); e = __ldg(maps + 2 * plane + o);
+            const size_t idx = ((size_t)gi * d.W + gj) * 3 + (e - c * 3);
+            a = __ldg(maps + idx); b = __ldg(maps + plane + idx); f = __ldg(maps + 2 * plane + idx);
         }
-        sm[0][k][r][c] = a; sm[1][k][r][c] = b; sm[2][k][r][c] = e;
+        sm[0][r][e] = a; sm[1][r][e] = b; sm[2][r][e] = f;
+    }
+    __syncthreads();
+    // position q = p - s contributes to pixel p with weight g[s]; in the local frame that is row (p - i0) + (10 - s)
+    if (threadIdx.x < 2 * kHaloE) {
+        const int half = threadIdx.x / kHaloE, e = threadIdx.x - half * kHaloE, r0 = half * 8;
+        float acc[8][3];
+#pragma unroll
+        for (int o = 0; o < 8; ++o) acc[o][0] = acc[o][1] = acc[o][2] = 0.f;
+#pragma unroll
+        for (int rin = 0; rin < 8 + kWin - 1; ++rin) {
+            const float a = sm[0][r0 + rin][e], b = sm[1][r0 + rin][e], f = sm[2][r0 + rin][e];
+#pragma unroll
+            for (int o = 0; o < 8; ++o) {
+                const int q = rin - o;
+                if (q >= 0 && q < kWin) {
+                    const float g = win.g[kWin - 1 - q];
+                    acc[o][0] = fmaf(g, a, acc[o][0]); acc[o][1] = fmaf(g, b, acc[o][1]); acc[o][2] = fmaf(g, f, acc[o][2]);
+                }
+            }
+        }
+#pragma unroll
+        for (int o = 0; o < 8; ++o) { su[0][r0 + o][e] = acc[o][0]; su[1][r0 + o][e] = acc[o][1]; su[2][r0 + o][e] = acc[o][2]; }
+    }
+    __syncthreads();
+    if (threadIdx.x < 3 * 4 * kLossTile) {
+        const int k = threadIdx.x % 3, cg = (threadIdx.x / 3) & 3, r = threadIdx.x / 12;
+        float acc[4][3];
+#pragma unroll
+        for (int o = 0; o < 4; ++o) acc[o][0] = acc[o][1] = acc[o][2] = 0.f;
+#pragma unroll
+        for (int cin = 0; cin < 4 + kWin - 1; ++cin) {
+            const int e = (4 * cg + cin) * 3 + k;
+            const float a = su[0][r][e], b = su[1][r][e], f = su[2][r][e];
+#pragma unroll
+            for (int o = 0; o < 4; ++o) {
+                const int q = cin - o;
+                if (q >= 0 && q < kWin) {
+                    const float g = win.g[kWin - 1 - q];
+                    acc[o][0] = fmaf(g, a, acc[o][0]); acc[o][1] = fmaf(g, b, acc[o][1]); acc[o][2] = fmaf(g, f, acc[o][2]);
+                }
+            }
+        }
+        const float up = v_main ? __ldg(v_main) : 1.f;
+        const float w_l1 = up * (1.f - ssim_lambda) / (3.f * (float)d.H * (float)d.W);
+        const float w_ss = -up * ssim_lambda / (3.f * (float)d.Hv * (float)d.Wv);
+        const float bgk = __ldg(background + k);
+        const int gi = i0 + r;
+#pragma unroll
+        for (int o = 0; o < 4; ++o) {
+            const int gj = j0 + 4 * cg + o;
+            float gb = 0.f;
+            if (gi < d.H && gj < d.W) {
+                const size_t pix = (size_t)gi * d.W + gj;
+                const float om = __fsub_rn(1.f, __ldg(out_alpha + pix));
+                const float pre = __fadd_rn(__fadd_rn(__ldg(out_img + pix * 3 + k), __ldg(out_texture + pix * d.C + k)),
+                                            __fmul_rn(om, bgk));
+                const float m = mask ? __ldg(mask + pix) : 1.f;
+                const float x = __fmul_rn(__ldg(gt + pix * 3 + k), m), y = __fmul_rn(clamp_unit(pre), m);
+                const float diff = x - y;  // Ll1 = mean |gt - pred|: d/dpred = -sign(gt - pred)
+                const float sgn = diff > 0.f ? -1.f : (diff < 0.f ? 1.f : 0.f);
+                float g = w_l1 * sgn + w_ss * (acc[o][0] + 2.f * y * acc[o][1] + x * acc[o][2]);
+                g *= m;                                    // pred_img * mask
+                if (!(pre >= 0.f && pre <= 1.f)) g = 0.f;  // torch.clamp passes the gradient on [min, max] only
+                v_out_img[pix * 3 + k] = g;
+                v_out_texture[pix * d.C + k] = g;
+                gb = g * bgk;  // d/d out_alpha of (1 - out_alpha) * background, summed over the channels below
+            }
+            sg[r][(4 * cg + o) * 3 + k] = gb;
+        }
     }
     __syncthreads();
     const int pr = threadIdx.x >> 4, pc = threadIdx.x & 15;
     const int gi = i0 + pr, gj = j0 + pc;
-    const bool inside = gi < d.H && gj < d.W;
-    const size_t pix = inside ? (size_t)gi * d.W + gj : 0;
-    const float up = v_main ? __ldg(v_main) : 1.f;
-    const float w_l1 = up * (1.f - ssim_lambda) / (3.f * (float)d.H * (float)d.W);
-    const float w_ss = -up * ssim_lambda / (3.f * (float)d.Hv * (float)d.Wv);
-    const float bg[3] = {background[0], background[1], background[2]};
-    float pre[3] = {0.f, 0.f, 0.f};
-    float m = 1.f;
-    if (inside) {
-        compose_pixel(out_img, out_texture, out_alpha, bg, d.C, pix, pre);
-        if (mask) m = mask[pix];
-    }
-    float v_alpha = 0.f;
-    for (int k = 0; k < 3; ++k) {
-        // transpose of pass 2 then of pass 1: position q = p - s contributes with weight g[s]; in the local frame
-        // (origin 10 rows/columns before the tile) that is rows pr + (10 - s), and the window is symmetric
-        for (int t = threadIdx.x; t < kLossTile * kHalo; t += 256) {
-            const int r = t / kHalo, c = t - r * kHalo;
-            float a0 = 0.f, a1 = 0.f, a2 = 0.f;
-#pragma unroll
-            for (int q = 0; q < kWin; ++q) {
-                const float g = win.g[kWin - 1 - q];
-                a0 = fmaf(g, sm[0][k][r + q][c], a0); a1 = fmaf(g, sm[1][k][r + q][c], a1);
-                a2 = fmaf(g, sm[2][k][r + q][c], a2);
-            }
-            su[0][r][c] = a0; su[1][r][c] = a1; su[2][r][c] = a2;
-        }
-        __syncthreads();
-        float d0 = 0.f, d1 = 0.f, d2 = 0.f;
-#pragma unroll
-        for (int q = 0; q < kWin; ++q) {
-            const float g = win.g[kWin - 1 - q];
-            d0 = fmaf(g, su[0][pr][pc + q], d0); d1 = fmaf(g, su[1][pr][pc + q], d1); d2 = fmaf(g, su[2][pr][pc + q], d2);
-        }
-        __syncthreads();
-        if (inside) {
-            const float v = clamp_unit(pre[k]);
-            const float x = __fmul_rn(gt[pix * 3 + k], m), y = __fmul_rn(v, m);
-            const float diff = x - y;  // Ll1 = mean |gt - pred|: d/dpred = -sign(gt - pred)
-            const float sgn = diff > 0.f ? -1.f : (diff < 0.f ? 1.f : 0.f);
-            float g = w_l1 * sgn + w_ss * (d0 + 2.f * y * d1 + x * d2);
-            g *= m;                                          // pred_img * mask
-            if (!(pre[k] >= 0.f && pre[k] <= 1.f)) g = 0.f;  // torch.clamp passes the gradient on [min, max] only
-            v_out_img[pix * 3 + k] = g;
-            v_out_texture[pix * d.C + k] = g;
-            v_alpha -= g * bg[k];  // d/d out_alpha of (1 - out_alpha) * background
-        }
-    }
-    if (inside) {
+    if (gi < d.H && gj < d.W) {
+        const size_t pix = (size_t)gi * d.W + gj;
         for (int k = 3; k < d.C; ++k) v_out_texture[pix * d.C + k] = 0.f;  // channels the composite does not read
-        v_out_alpha[pix] = v_alpha;
+        v_out_alpha[pix] = ((0.f - sg[pr][pc * 3]) - sg[pr][pc * 3 + 1]) - sg[pr][pc * 3 + 2];
     }
 }
 
