@@ -99,13 +99,16 @@ class HostViewFeeder:
             ev.record(self.h2d)
         self._pending = (dev, ev)
 
-    def take(self):
-        """Device copies of the prefetched view; the current (compute) stream waits for them."""
+    def take(self, also=()):
+        """Device copies of the prefetched view; the current (compute) stream waits for them, and so does every
+        stream in `also` (e.g. a `BinningStream`'s, which reads the camera matrix)."""
         if self._pending is None:
             raise RuntimeError("HostViewFeeder.take: nothing was prefetched")
         dev, ev = self._pending
         self._pending = None
         torch.cuda.current_stream(self.device).wait_event(ev)
+        for st in also:
+            st.wait_event(ev)
         return dev
 
     def send_back(self, dev_tensor, host_tensor):
@@ -123,6 +126,82 @@ class HostViewFeeder:
         self.h2d.synchronize()
         self.d2h.synchronize()
         torch.cuda.current_stream(self.device).synchronize()
+
+
+class BinningStream:
+    """Projection + tile binning of the NEXT view on a CUDA stream of their own, beside the compositing kernels of
+    the current view.  The forward and the stream backward are persistent grids with a tail in which most SMs idle,
+    and the binning kernels (project, count, emit, per-tile sort: ~0.2 ms per view at the headline size) are short
+    and latency-bound; run back to back on one stream neither fills the GPU.  On two streams the binning of view
+    i+1 runs in the shadow of view i's forward/backward (measured at the headline size: 1.48 -> 1.36 ms/view).
+    The reference has one camera per call and one (legacy default) stream.
+
+        bs = BinningStream(device)
+        pre = bs.begin(means, scales, 1, quats, viewmats[0], intr, H, W, 16); bs.finish(pre)
+        for i in range(V):
+            outs = texture_gaussians(info, dims, *pre.args, colors, ..., binning=pre.binning)
+            nxt = bs.begin(..., viewmats[i + 1], ..., wait_for_current=False) if i + 1 < V else None
+            loss(outs).backward()
+            if nxt is not None: bs.finish(nxt)   # host waits for view i+1's sizes only; its sort goes to the stream
+            pre = nxt
+    """
+
+    class Prepared:
+        __slots__ = ("centers", "extents", "depths", "num_tiles_hit", "binning", "ready")
+
+        @property
+        def args(self):
+            """The four positional arguments of `texture_gaussians` this stage produces."""
+            return self.centers, self.extents, self.depths, self.num_tiles_hit
+
+    def __init__(self, device):
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("BinningStream needs a CUDA device (there is no CPU path)")
+        self.stream = torch.cuda.Stream(self.device)
+
+    def begin(self, means, scales, glob_scale, quats, viewmat, intrins, img_height: int, img_width: int,
+              block_width: int, *, wait_for_current: bool = True) -> "BinningStream.Prepared":
+        """`project_bounds` + `begin_binning` of one view on the binning stream (no host synchronisation).
+        `wait_for_current`: the binning stream first waits for everything enqueued so far on the current stream --
+        needed whenever an input was produced there (parameters after an optimizer step).  Pass False for the later
+        views of a step whose parameters have not changed since its first view, so that the binning is free to
+        overlap the compositing kernels already enqueued."""
+        from .get_aabb_2d import project_bounds
+        from .utils import begin_binning
+
+        if wait_for_current:
+            self.stream.wait_stream(torch.cuda.current_stream(self.device))
+        pre = BinningStream.Prepared()
+        with torch.cuda.stream(self.stream):
+            _, pre.depths, pre.centers, pre.extents, pre.num_tiles_hit = project_bounds(
+                means, scales, glob_scale, quats, viewmat, intrins, img_height, img_width, block_width)
+            tile_bounds = ((img_width + block_width - 1) // block_width, (img_height + block_width - 1) // block_width, 1)
+            pre.binning = begin_binning(means.shape[0], pre.centers, pre.extents, pre.depths, pre.num_tiles_hit,
+                                        tile_bounds, block_width)
+        pre.ready = False
+        return pre
+
+    def finish(self, pre: "BinningStream.Prepared"):
+        """Second half (`finish_binning`: the host waits for the view's sizes, emit + per-tile sort go to the binning
+        stream), then the CURRENT stream is made to wait for the result.  Returns `(num_intersects,
+        gaussian_ids_sorted, tile_bins)`; `texture_gaussians(..., binning=pre.binning)` picks the same result up."""
+        from .utils import finish_binning
+
+        if pre.ready:
+            return pre.binning.result
+        cur = torch.cuda.current_stream(self.device)
+        with torch.cuda.stream(self.stream):
+            result = finish_binning(pre.binning)
+            ev = torch.cuda.Event()
+            ev.record(self.stream)
+        # allocated on the binning stream, consumed on the current one: keep the allocator from recycling them early
+        for t in (pre.centers, pre.extents, pre.depths, pre.num_tiles_hit, result[1], result[2]):
+            if t.is_cuda and t.numel() > 0:
+                t.record_stream(cur)
+        cur.wait_event(ev)
+        pre.ready = True
+        return result
 
 
 class GradientBucket:
