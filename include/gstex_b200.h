@@ -239,6 +239,27 @@ int gstex_compute_sh_backward(int n, int degree, int degrees_to_use, const float
 int gstex_texture_sample_forward(int num_queries, int channels, const int32_t* texture_dims, const float* uvs,
                                  const float* texture, float* out, void* stream);
 
+/* ---- next row: texture editing (splat-painting of a canvas into the charts) ----- */
+
+/* ref: cuda/csrc/texture_edit.cu:238-346 texture_edit_tensor -> kernel :11-236 (bound at cuda/csrc/ext.cpp, called by
+ * texture_edit.py:206-236).  Walks every pixel's sorted tile list with the forward's alpha / skip / termination rules
+ * and, for each contributing pair whose view depth t * view_depth lies in [depth_lower, depth_upper] of its pixel,
+ * adds weight * (r*m, g*m, b*m, m, 1) to channels 0..4 of the four bilinear corner texels of the pair's uv
+ * (r,g,b = updated_img (H,W,3), m = updated_alpha (H,W,1)).  `channels` = texture_info.z is the row stride of
+ * updated_texture (total_texels, channels), >= 5 (the model passes 5, NS/models/gstex.py:572); the call zero-fills
+ * it first (the reference's torch::zeros, :308-310), so every element is written.  `settings`: bit 0 = blur floor
+ * (:48; NOT the forward's bit 9), all other bits ignored as in the reference.  The reference's `background` and
+ * `texture` arguments are never read by its kernel and are not part of this signature.  `workspace`:
+ * gstex_texture_workspace_bytes(n) bytes of scratch (per-view packed records). */
+int gstex_texture_edit(int img_height, int img_width, int block_width, int channels, int n, int num_intersects,
+                       long long total_texels, const int32_t* texture_dims, const float* updated_img,
+                       const float* updated_alpha, const float* depth_lower, const float* depth_upper,
+                       const int32_t* gaussian_ids_sorted, const int32_t* tile_bins, const float* opacities,
+                       const float* means, const float* scales, float glob_scale, const float* quats,
+                       const float* uv0, const float* umap, const float* vmap, const float* viewmat,
+                       const float* c2w, float fx, float fy, float cx, float cy, int settings,
+                       float* updated_texture, void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- next row: compositing + photometric loss on the far side of the path ------- */
 
 /* ref: nerfstudio/models/gstex.py:1204-1205 (rgb = clamp(out_img + out_texture[:,:,0:3] + (1 - out_alpha) * background,

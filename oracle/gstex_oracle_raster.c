@@ -440,3 +440,72 @@ void orc_texture_backward(int tiles_x, int tiles_y, int bw, int img_w, int img_h
             }
     }
 }
+
+/* ------------------------------------------------------------------------------------------
+ * (f-4) texture_edit -- C/texture_edit.cu:11-236: the forward's traversal (same alpha, skip and
+ * termination rules, :130-177) that, instead of compositing, splats the edit canvas into the charts:
+ * every contributing pair whose view depth t*view_depth lies in [depth_lower, depth_upper] of its
+ * pixel (:180-181) adds, for the four bilinear corners of its uv (always bilinear, replicate
+ * padding: edit_jagged_chart, C/texture_helpers.cuh:239-250), weight * (r*m, g*m, b*m, m, 1) to
+ * channels 0..4 of the corner texel (:194-216; r,g,b = updated_img, m = updated_alpha).  The blur
+ * floor is settings bit 0 here (:48), not bit 9; the NDC bit (1) is read and unused.  The kernel
+ * adds with float atomics in an unspecified order; this restatement accumulates in double
+ * (`updated_texture`, (T, C) doubles, zero-initialised by the caller; C = texture_info.z >= 5).
+ * PARITY UNPINNED on the CPU: the reference has no Python twin and no test of texture_edit
+ * (texture_edit.py:117 "only a CUDA implementation was written"); it is pinned on the GPU box
+ * against the reference's own extension (tests/test_gpu_edit.py).
+ * ------------------------------------------------------------------------------------------ */
+void orc_texture_edit(int tiles_x, int tiles_y, int bw, int img_w, int img_h, int C,
+                      const int32_t* texture_dims, const float* updated_img, const float* updated_alpha,
+                      const float* depth_lower, const float* depth_upper, const int32_t* ids_sorted,
+                      const int32_t* tile_bins, const float* opacities, const float* means,
+                      const float* scales, float glob_scale, const float* quats, const float* uv0s,
+                      const float* umaps, const float* vmaps, const float* viewmat, const float* c2w,
+                      float fx, float fy, float cx, float cy, int settings, double* updated_texture,
+                      long long* pairs_in_range) {
+    const int use_blur = (settings & (1 << 0)) != 0;
+    const int ntiles = tiles_x * tiles_y;
+    long long npairs = 0;
+#pragma omp parallel for schedule(dynamic, 1) reduction(+ : npairs)
+    for (int tile = 0; tile < ntiles; ++tile) {
+        const int ty = tile / tiles_x, tx = tile % tiles_x;
+        const int r0 = tile_bins[2 * tile], r1 = tile_bins[2 * tile + 1];
+        for (int li = 0; li < bw; ++li)
+            for (int lj = 0; lj < bw; ++lj) {
+                const int bi = ty * bw + li, bj = tx * bw + lj;
+                if (bi >= img_h || bj >= img_w) continue;
+                const int pix = bi * img_w + bj;
+                const float px = (float)bj + 0.5f, py = (float)bi + 0.5f;
+                f3 origin, ray;
+                get_ray(c2w, fx, fy, cx, cy, px, py, &origin, &ray);
+                const float view_depth = viewmat[8] * ray.x + viewmat[9] * ray.y + viewmat[10] * ray.z;
+                const float m = updated_alpha[pix];
+                const float vals[5] = {updated_img[3 * pix] * m, updated_img[3 * pix + 1] * m,
+                                       updated_img[3 * pix + 2] * m, m, 1.f};
+                const float lo = depth_lower[pix], hi = depth_upper[pix];
+                float T = 1.f;
+                for (int idx = r0; idx < r1; ++idx) {
+                    const int g = ids_sorted[idx];
+                    pair_eval e;
+                    eval_pair(g, means, scales, glob_scale, quats, opacities, viewmat, fx, fy, cx, cy,
+                              origin, ray, px, py, use_blur, &e);
+                    const float next_T = T * (1.f - e.alpha);
+                    if (next_T <= 1e-4f) break;
+                    if (e.skip) continue;
+                    const float t_view = e.t * view_depth;
+                    if (t_view >= lo && t_view <= hi) {
+                        f3 um = *(const f3*)(umaps + 3 * g), vm = *(const f3*)(vmaps + 3 * g);
+                        f2 uv = {uv0s[2 * g] + dot3(um, e.delta), uv0s[2 * g + 1] + dot3(vm, e.delta)};
+                        uv.x = clamp01(uv.x); uv.y = clamp01(uv.y);
+                        texq q;
+                        texel_query(texture_dims + 3 * g, uv, 1, &q);
+                        for (int k = 0; k < 5; ++k)
+                            for (int c = 0; c < 4; ++c) dacc(updated_texture + (size_t)q.base[c] * C + k, q.w[c] * vals[k]);
+                        ++npairs;
+                    }
+                    T = next_T;
+                }
+            }
+    }
+    if (pairs_in_range) *pairs_in_range = npairs;
+}

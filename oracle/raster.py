@@ -112,3 +112,32 @@ def texture_gaussians_fwd_bwd(texture_info, texture_dims, centers, extents, dept
                                v_outs["v_out_texture"], v_outs["v_out_normal"])
         res.update(bwd)
     return res
+
+
+def texture_edit(texture_info, texture_dims, updated_img, updated_alpha, depth_lower, depth_upper, centers, extents,
+                 depths, num_tiles_hit, opacity, means, scales, glob_scale, quats, uv0, umap, vmap, viewmat, c2w, fx,
+                 fy, cx, cy, img_height, img_width, block_width, settings, background=None, return_pairs=False):
+    """gstex_cuda/texture_edit.py:14-239 on the CPU (binning as texture_gaussians, then `orc_texture_edit` =
+    C/texture_edit.cu:11-236).  Returns updated_texture (sum h*w, C) float32 [and the number of contributing pairs
+    inside their pixel's depth range]."""
+    H, W, C = int(img_height), int(img_width), int(texture_info[2])
+    assert C >= 5, "texture_edit writes channels 0..4 (C/texture_edit.cu:194)"
+    tb = tile_bounds_of(H, W, block_width)
+    n = np.asarray(centers).shape[0]
+    td = _i32(texture_dims)
+    total = int((td[:, 0].astype(np.int64) * td[:, 1].astype(np.int64)).sum())
+    num_intersects, cum = compute_cumulative_intersects(num_tiles_hit)
+    assert num_intersects >= 1  # texture_edit.py:183-184
+    _, _, _, gids_s, bins = bin_and_sort_gaussians(n, num_intersects, centers, extents, depths, cum, tb, block_width)
+    out = np.zeros((total, C), np.float64)
+    a = [td, _f32(updated_img), _f32(updated_alpha), _f32(depth_lower), _f32(depth_upper), _i32(gids_s), _i32(bins),
+         _f32(opacity), _f32(means), _f32(scales)]
+    b = [_f32(quats), _f32(uv0), _f32(umap), _f32(vmap),
+         _f32(np.asarray(viewmat, np.float32).reshape(-1)[:12]), _f32(np.asarray(c2w, np.float32).reshape(-1)[:12])]
+    npairs = ctypes.c_longlong(0)
+    lib().orc_texture_edit(
+        ctypes.c_int(tb[0]), ctypes.c_int(tb[1]), ctypes.c_int(block_width), ctypes.c_int(W), ctypes.c_int(H),
+        ctypes.c_int(C), *[_p(x) for x in a], _cf(glob_scale), *[_p(x) for x in b], _cf(fx), _cf(fy), _cf(cx), _cf(cy),
+        ctypes.c_int(int(settings)), _p(out), ctypes.byref(npairs))
+    res = out.astype(np.float32)
+    return (res, int(npairs.value)) if return_pairs else res

@@ -128,3 +128,44 @@ def compare_all(ours, ref, settings, fwd_rtol, grad_rtol, what, max_flip_frac=2e
         print("\n".join(rows))
     assert not fails, "\n" + "\n".join(fails)
     return rows
+
+
+def make_edit_inputs(d, seed=7, window="median", painted_frac=0.4):
+    """Edit canvas + per-pixel depth window for a scene dict of numpy arrays (`scene_to_numpy`).
+    window = "median": [out_depth - 1e-2, out_depth + 1e-2] around the oracle forward's median depth, as the model's
+    edit_texture does (NS/models/gstex.py:566-568); "all": every depth; "none": an empty window.  A rectangle covering
+    `painted_frac` of each image side is painted with random colours and alpha in (0, 1]; the rest has alpha 0."""
+    g = np.random.default_rng(seed)
+    H, W = d["H"], d["W"]
+    img = g.random((H, W, 3)).astype(np.float32)
+    alpha = np.zeros((H, W, 1), np.float32)
+    h0, w0 = int(H * 0.2), int(W * 0.3)
+    h1, w1 = min(H, h0 + max(1, int(H * painted_frac))), min(W, w0 + max(1, int(W * painted_frac)))
+    alpha[h0:h1, w0:w1, 0] = (0.05 + 0.95 * g.random((h1 - h0, w1 - w0))).astype(np.float32)
+    if window == "all":
+        lo = np.full((H, W), -1e30, np.float32)
+        hi = np.full((H, W), 1e30, np.float32)
+    elif window == "none":
+        lo = np.full((H, W), 1.0, np.float32)
+        hi = np.full((H, W), -1.0, np.float32)
+    else:
+        depth = run_oracle_pipeline(d)["out_depth"]
+        lo, hi = (depth - 1e-2).astype(np.float32), (depth + 1e-2).astype(np.float32)
+    return dict(updated_img=img, updated_alpha=alpha, depth_lower=lo, depth_upper=hi)
+
+
+def run_oracle_edit(d, e, settings, channels=5, return_pairs=False):
+    """oracle.raster.texture_edit on a scene dict + edit inputs (binning by the oracle as well)."""
+    import oracle
+    import oracle.raster as R
+
+    intr = (d["fx"], d["fy"], d["cx"], d["cy"])
+    H, W, bw = d["H"], d["W"], d.get("bw", 16)
+    _, depths = oracle.project_points(d["means"], d["viewmat"], intr)
+    centers, extents = oracle.get_aabb_2d(d["means"], d["scales"], 1.0, d["quats"], d["viewmat"], intr)
+    nth = oracle.get_num_tiles_hit_2d(centers, extents, H, W, bw)
+    n = d["means"].shape[0]
+    return R.texture_edit((n, 1, channels), d["texture_dims"], e["updated_img"], e["updated_alpha"], e["depth_lower"],
+                          e["depth_upper"], centers, extents, depths, nth, d["opacities"], d["means"], d["scales"], 1.0,
+                          d["quats"], d["uv0"], d["umap"], d["vmap"], d["viewmat"], d["c2w"], *intr, H, W, bw, settings,
+                          return_pairs=return_pairs)
