@@ -226,7 +226,7 @@ extern "C" long long gstex_launch_count(void) { return g_launches.load(std::memo
 extern "C" const char* gstex_error_string(int code) {
     if (code == GSTEX_OK) return "ok";
     if (code == GSTEX_E_BADARG) return "gstex_b200: bad argument (null pointer, negative size or block_width outside [2,16])";
-    if (code == GSTEX_E_UNSUPPORTED) return "gstex_b200: unsupported settings bits (viewer visualisation 15-29) or channel count";
+    if (code == GSTEX_E_UNSUPPORTED) return "gstex_b200: unsupported settings bits (viewer visualisation 16-29) or channel count";
     if (code == GSTEX_E_WORKSPACE) return "gstex_b200: workspace too small";
     if (code > 0) return cudaGetErrorString((cudaError_t)code);
     return "gstex_b200: unknown error";

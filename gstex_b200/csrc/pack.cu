@@ -145,9 +145,7 @@ __global__ void __launch_bounds__(kThreads1D) pack_records_kernel(const PackPara
     r.q[2] = make_float4(a1x, a1y, a1z, is1 * is1);
     r.q[3] = make_float4(a2x, a2y, a2z, is2 * is2);
     r.q[4] = make_float4(xy_x, xy_y, __int_as_float(h), __int_as_float(wd));
-    // colors == nullptr: texture_edit.cu, which composites no colour
-    r.q[5] = p.colors ? make_float4(p.colors[3 * i], p.colors[3 * i + 1], p.colors[3 * i + 2], __int_as_float(st))
-                      : make_float4(0.f, 0.f, 0.f, __int_as_float(st));
+    r.q[5] = make_float4(p.colors[3 * i], p.colors[3 * i + 1], p.colors[3 * i + 2], __int_as_float(st));
     r.q[6] = make_float4(p.umap[3 * i], p.umap[3 * i + 1], p.umap[3 * i + 2], p.uv0[2 * i]);
     r.q[7] = make_float4(p.vmap[3 * i], p.vmap[3 * i + 1], p.vmap[3 * i + 2], p.uv0[2 * i + 1]);
 #pragma unroll

@@ -77,7 +77,9 @@ struct FwdShared {
     float4 origin;  // camera position: re-read from here in every pair evaluation instead of living in registers
 };
 
-template <int CMAX, bool REC>
+// VIS: settings bit 15 (viewer): normals are accumulated flipped towards the camera (texture.cu:236-241); its own
+// instantiations, so the training kernels carry no trace of it.
+template <int CMAX, bool REC, bool VIS = false>
 __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward_kernel(const FwdParams p) {
     // <= 3 channels (training): the texture fetch of a contributing pair is deferred to a lane-dense phase
     constexpr bool kDefer = (CMAX == 3);
@@ -326,7 +328,12 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
                         const float vis = e.alpha * T;
                         const float4 r5 = r.q[5], r6 = r.q[6], r7 = r.q[7];
                         rgb.x += r5.x * vis; rgb.y += r5.y * vis; rgb.z += r5.z * vis;
-                        nrm.x += vis * r1.x; nrm.y += vis * r1.y; nrm.z += vis * r1.z;
+                        if constexpr (VIS) {
+                            const float sgn = (pe.ray.x * r1.x + pe.ray.y * r1.y + pe.ray.z * r1.z > 0.f) ? -1.f : 1.f;
+                            nrm.x += vis * (sgn * r1.x); nrm.y += vis * (sgn * r1.y); nrm.z += vis * (sgn * r1.z);
+                        } else {
+                            nrm.x += vis * r1.x; nrm.y += vis * r1.y; nrm.z += vis * r1.z;
+                        }
                         const float t_view = e.t * pix.view_depth;
                         const float u = clamp01(r6.w + (r6.x * e.delta.x + r6.y * e.delta.y + r6.z * e.delta.z));
                         const float v = clamp01(r7.w + (r7.x * e.delta.x + r7.y * e.delta.y + r7.z * e.delta.z));
@@ -453,7 +460,8 @@ extern "C" int gstex_debug_fwd_stats(unsigned long long* out, int reset) {
 #endif
 
 extern "C" int gstex_pair_stream_supported(int channels, int n, int settings) {
-    return channels >= 1 && channels <= 3 && n > 0 && n < (1 << 27) && !(settings & GSTEX_SET_UV_GRAD);
+    return channels >= 1 && channels <= 3 && n > 0 && n < (1 << 27) &&
+           !(settings & (GSTEX_SET_UV_GRAD | GSTEX_SET_VIS_NORMALS));
 }
 
 extern "C" size_t gstex_pair_stream_bytes(int img_height, int img_width, int block_width, long long max_pairs) {
@@ -533,16 +541,20 @@ extern "C" int gstex_texture_forward_act(int img_height, int img_width, int bloc
             GSTEX_CUDA_TRY(cudaMemsetAsync(reinterpret_cast<char*>(pair_stream) + offsetof(StreamHeader, overflow), 1, 1, st));
     }
     // > 48 KB of shared memory: opt in (per device, cheap: done at every launch)
-#define GSTEX_FWD_LAUNCH(CM, RC)                                                                                        \
-    do {                                                                                                                \
-        GSTEX_CUDA_TRY(cudaFuncSetAttribute(texture_forward_kernel<CM, RC>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                            (int)sizeof(FwdShared)));                                                   \
-        texture_forward_kernel<CM, RC><<<grid, threads, sizeof(FwdShared), st>>>(p);                                    \
+#define GSTEX_FWD_LAUNCH(CM, RC, VS)                                                                                \
+    do {                                                                                                            \
+        GSTEX_CUDA_TRY(cudaFuncSetAttribute(texture_forward_kernel<CM, RC, VS>,                                     \
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FwdShared)));  \
+        texture_forward_kernel<CM, RC, VS><<<grid, threads, sizeof(FwdShared), st>>>(p);                            \
     } while (0)
-    if (record) GSTEX_FWD_LAUNCH(3, true);
-    else if (channels <= 3) GSTEX_FWD_LAUNCH(3, false);
-    else if (channels <= 6) GSTEX_FWD_LAUNCH(6, false);
-    else GSTEX_FWD_LAUNCH(GSTEX_MAX_CHANNELS, false);
+    if (settings & GSTEX_SET_VIS_NORMALS) {  // never recorded (gstex_pair_stream_supported)
+        if (channels <= 3) GSTEX_FWD_LAUNCH(3, false, true);
+        else if (channels <= 6) GSTEX_FWD_LAUNCH(6, false, true);
+        else GSTEX_FWD_LAUNCH(GSTEX_MAX_CHANNELS, false, true);
+    } else if (record) GSTEX_FWD_LAUNCH(3, true, false);
+    else if (channels <= 3) GSTEX_FWD_LAUNCH(3, false, false);
+    else if (channels <= 6) GSTEX_FWD_LAUNCH(6, false, false);
+    else GSTEX_FWD_LAUNCH(GSTEX_MAX_CHANNELS, false, false);
 #undef GSTEX_FWD_LAUNCH
     GSTEX_LAUNCH_CHECK();
     return GSTEX_OK;

@@ -20,7 +20,7 @@ from .utils import TileBinning, bin_gaussians_to_tiles, finish_binning
 _SCRATCH_CLEAN = 4   # GSTEX_SCRATCH_CLEAN, include/gstex_b200.h
 _GRAD_SCRATCH = {}   # (device index, stream, bytes) -> all-zero gradient scratch left by the last backward
 
-SUPPORTED_SETTINGS = (1 << 2) | (1 << 8) | (1 << 9) | (1 << 10)
+SUPPORTED_SETTINGS = (1 << 2) | (1 << 8) | (1 << 9) | (1 << 10) | (1 << 15)
 
 
 class PairStreamPolicy:
@@ -165,7 +165,7 @@ def texture_gaussians(
         raise ValueError("colors must have 3 channels (the reference kernels read float3, texture.cu:18)")
     if int(settings) & ~SUPPORTED_SETTINGS:
         raise NotImplementedError(
-            f"settings {int(settings):#x}: only bits 2, 8, 9, 10 are implemented (15-29 are viewer visualisation)")
+            f"settings {int(settings):#x}: only bits 2, 8, 9, 10, 15 are implemented (16-29 are viewer visualisation)")
     return _TextureGaussians.apply(
         texture_info, texture_dims.contiguous(), centers.contiguous(), extents.contiguous(), depths.contiguous(),
         num_tiles_hit.contiguous(), colors.contiguous(), opacity.contiguous(), means.contiguous(),

@@ -30,7 +30,7 @@ extern "C" {
 
 #define GSTEX_OK 0
 #define GSTEX_E_BADARG (-1)      /* null pointer, negative size, block_width outside [2,16] ... */
-#define GSTEX_E_UNSUPPORTED (-2) /* settings bits 15-29 (viewer visualisation), channels > 16 */
+#define GSTEX_E_UNSUPPORTED (-2) /* settings bits 16-29 (viewer visualisation), channels > 16 */
 #define GSTEX_E_WORKSPACE (-3)   /* workspace too small */
 
 /* settings bit-field, ref: cuda/csrc/texture.cu:54-65,381-387 */
@@ -38,7 +38,11 @@ extern "C" {
 #define GSTEX_SET_UV_GRAD (1 << 8)
 #define GSTEX_SET_BLUR (1 << 9)
 #define GSTEX_SET_NDC_REG (1 << 10)
-#define GSTEX_SETTINGS_SUPPORTED (GSTEX_SET_NEAREST | GSTEX_SET_UV_GRAD | GSTEX_SET_BLUR | GSTEX_SET_NDC_REG)
+/* viewer "visualization_mode" (texture.cu:58,236-241): out_normal accumulates the splat normal flipped towards the camera.
+ * Forward only -- the reference's backward never reads the bit (texture.cu:381-387) and neither does ours. */
+#define GSTEX_SET_VIS_NORMALS (1 << 15)
+#define GSTEX_SETTINGS_SUPPORTED \
+    (GSTEX_SET_NEAREST | GSTEX_SET_UV_GRAD | GSTEX_SET_BLUR | GSTEX_SET_NDC_REG | GSTEX_SET_VIS_NORMALS)
 #define GSTEX_MAX_CHANNELS 16
 
 int gstex_abi_version(void);

@@ -185,6 +185,7 @@ void orc_texture_forward(int tiles_x, int tiles_y, int bw, int img_w, int img_h,
     const int use_blur = (settings & (1 << 9)) != 0;
     const int use_ndc = (settings & (1 << 10)) != 0;
     const int bilinear = !(settings & (1 << 2));
+    const int vis_mode = (settings & (1 << 15)) != 0; /* C/texture.cu:58 */
     const int ntiles = tiles_x * tiles_y;
 #pragma omp parallel for schedule(dynamic, 1)
     for (int tile = 0; tile < ntiles; ++tile) {
@@ -215,7 +216,11 @@ void orc_texture_forward(int tiles_x, int tiles_y, int bw, int img_w, int img_h,
                     if (e.skip) continue;
                     const float vis = e.alpha * T;
                     rgb.x += colors[3 * g] * vis; rgb.y += colors[3 * g + 1] * vis; rgb.z += colors[3 * g + 2] * vis;
-                    nrm.x += vis * e.ax3.x; nrm.y += vis * e.ax3.y; nrm.z += vis * e.ax3.z;
+                    {
+                        f3 h = e.ax3; /* C/texture.cu:236-244: flipped towards the camera in visualization mode */
+                        if (vis_mode && ray.x * h.x + ray.y * h.y + ray.z * h.z > 0) { h.x = -h.x; h.y = -h.y; h.z = -h.z; }
+                        nrm.x += vis * h.x; nrm.y += vis * h.y; nrm.z += vis * h.z;
+                    }
                     const float t_view = e.t * view_depth;
                     f3 um = *(const f3*)(umaps + 3 * g), vm = *(const f3*)(vmaps + 3 * g);
                     f2 uv = {uv0s[2 * g] + dot3(um, e.delta), uv0s[2 * g + 1] + dot3(vm, e.delta)};

@@ -13,12 +13,12 @@ import numpy as np
 
 from . import (_cf, _f32, _i32, _p, bin_and_sort_gaussians, compute_cumulative_intersects, lib, tile_bounds_of)
 
-SUPPORTED_SETTINGS_MASK = (1 << 2) | (1 << 8) | (1 << 9) | (1 << 10)
+SUPPORTED_SETTINGS_MASK = (1 << 2) | (1 << 8) | (1 << 9) | (1 << 10) | (1 << 15)
 
 
 def _check_settings(settings: int) -> None:
     if settings & ~SUPPORTED_SETTINGS_MASK:
-        raise NotImplementedError(f"oracle restates settings bits 2, 8, 9, 10 only (got {settings:#x})")
+        raise NotImplementedError(f"oracle restates settings bits 2, 8, 9, 10, 15 only (got {settings:#x})")
 
 
 def texture_forward(tile_bounds, block_width, img_size, channels, texture_dims, gaussian_ids_sorted, tile_bins,

@@ -89,3 +89,19 @@ def test_product_never_imports_oracle():
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f
                 assert not re.search(r"#include[^\n]*oracle", src), f
                 assert "libgstex_oracle" not in src and "CDLL(oracle" not in src, f
+
+
+def test_texture_edit_argument_errors_need_no_gpu():
+    """gstex_texture_edit validates its arguments before touching CUDA: the ctypes signature marshals all 33 arguments
+    and bad sizes / channel counts come back as status codes."""
+    from ctypes import c_void_p as P
+
+    from gstex_b200 import _lib
+
+    lib = _lib.load()
+    z = P(0)
+    ptrs10, ptrs6 = [z] * 10, [z] * 6
+    assert lib.gstex_texture_edit(0, 128, 16, 5, 10, 10, 100, *ptrs10, 1.0, *ptrs6, 1.0, 1.0, 1.0, 1.0, 0, z, z, 0, z) == -1
+    assert lib.gstex_texture_edit(128, 128, 17, 5, 10, 10, 100, *ptrs10, 1.0, *ptrs6, 1.0, 1.0, 1.0, 1.0, 0, z, z, 0, z) == -1
+    assert lib.gstex_texture_edit(128, 128, 16, 3, 10, 10, 100, *ptrs10, 1.0, *ptrs6, 1.0, 1.0, 1.0, 1.0, 0, z, z, 0, z) == -2
+    assert b"gstex" in lib.gstex_error_string(-2)

@@ -23,6 +23,9 @@ SCENES = [
     dict(name="cfg2", n=3000, width=96, height=128, texels=30000, settings=(1 << 8) | (1 << 9) | (1 << 10), C=6),
     dict(name="cfg2", n=3000, width=96, height=128, texels=30000, settings=(1 << 2) | (1 << 9), C=3),  # nearest
     dict(name="cfg4", n=20000, width=240, height=136, texels=200000, settings=(1 << 9) | (1 << 10), C=3),
+    # settings bit 15, the viewer's visualization_mode: normals flipped towards the camera (forward only)
+    dict(name="cfg2", n=6000, width=160, height=160, texels=60000, settings=(1 << 9) | (1 << 10) | (1 << 15), C=6),
+    dict(name="cfg1", n=400, width=72, height=56, texels=400 * 16, settings=(1 << 15), C=3),
     dict(name="cfg1", n=300, width=40, height=40, texels=300 * 9, settings=1 << 9, C=10),
 ]
 
@@ -99,7 +102,7 @@ def test_forward_backward_matches_oracle(cfg):
     compare(ours, ref, cfg["settings"], ORACLE_FWD_RTOL, ORACLE_GRAD_RTOL, what="oracle:")
 
 
-@pytest.mark.parametrize("cfg", SCENES[:7], ids=_id)
+@pytest.mark.parametrize("cfg", SCENES[:9], ids=_id)
 def test_forward_backward_matches_reference_extension(cfg):
     from oracle import ref_ext
 

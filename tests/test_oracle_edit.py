@@ -66,3 +66,21 @@ def test_edit_oracle_is_linear_in_the_canvas_and_reads_blur_from_bit_0():
     for s in (1 << 9, 1 << 13, (1 << 9) | (1 << 10)):
         np.testing.assert_array_equal(run_oracle_edit(d, e, s), a)
     assert np.abs(run_oracle_edit(d, e, 1) - a).max() > 0  # the blur floor widens small splats to a pixel
+
+
+def test_oracle_visualization_normals_bit_15_only_flips_normals():
+    """settings bit 15 (C/texture.cu:58,236-241): every output but out_normal is unchanged; the accumulated normal is a
+    sum of camera-facing normals, so its component along each pixel's ray is never positive."""
+    from gstex_b200.synthetic import make_scene
+
+    d = scene_to_numpy(make_scene("cfg1", n=400, width=72, height=56, texels=6400, settings=0))
+    a, b = run_oracle_pipeline(d, settings=0), run_oracle_pipeline(d, settings=1 << 15)
+    for k in ("out_img", "out_depth", "out_reg", "out_alpha", "out_texture"):
+        np.testing.assert_array_equal(a[k], b[k])
+    assert np.abs(a["out_normal"] - b["out_normal"]).max() > 0.1
+    H, W = d["H"], d["W"]
+    ys, xs = np.mgrid[0:H, 0:W]
+    cam = np.stack([(xs + 0.5 - d["cx"]) / d["fx"], (ys + 0.5 - d["cy"]) / d["fy"], np.ones((H, W))], -1)
+    rays = cam @ d["c2w"][:3, :3].T
+    assert ((rays * b["out_normal"]).sum(-1) <= 1e-6).all()
+    assert ((rays * a["out_normal"]).sum(-1) > 1e-3).any()
