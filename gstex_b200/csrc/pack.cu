@@ -119,31 +119,44 @@ __global__ void __launch_bounds__(kThreads1D) pack_records_kernel(const PackPara
     const float mx = p.means[3 * i], my = p.means[3 * i + 1], mz = p.means[3 * i + 2];
     const float4 qt = reinterpret_cast<const float4*>(p.quats)[i];
     const float w = qt.x, x = qt.y, y = qt.z, z = qt.w;
+    // Every fp32 expression below is written with explicit rounding intrinsics, in the fused form (read from the SASS
+    // of the build that matched) under which the compositing kernels reproduce the reference extension's results
+    // (full-size texture_edit: 5e-7 of scale; the parity tests' 1e-5) -- ptxas fuses plain mul/add pairs as it sees
+    // fit, explicit .rn operations it leaves alone: the records then carry the same bits whatever code surrounds them.  (Left to the compiler,
+    // an unrelated edit of this kernel changed the contraction of the rotation columns and moved out_texture by 1e-4 of
+    // its scale: u = uv0 + umap.delta amplifies one ulp of an axis by |mean| / |splat|.)
     // columns of R(quat), helpers.cuh:166-185
-    const float a1x = 1.f - 2.f * (y * y + z * z), a1y = 2.f * (x * y + w * z), a1z = 2.f * (x * z - w * y);
-    const float a2x = 2.f * (x * y - w * z), a2y = 1.f - 2.f * (x * x + z * z), a2z = 2.f * (y * z + w * x);
-    const float a3x = 2.f * (x * z + w * y), a3y = 2.f * (y * z - w * x), a3z = 1.f - 2.f * (x * x + y * y);
+    const float a1x = __fsub_rn(1.f, __fmul_rn(2.f, __fmaf_rn(y, y, __fmul_rn(z, z))));
+    const float a1y = __fmul_rn(2.f, __fmaf_rn(x, y, __fmul_rn(w, z)));
+    const float a1z = __fmul_rn(2.f, __fmaf_rn(x, z, -__fmul_rn(w, y)));
+    const float a2x = __fmul_rn(2.f, __fmaf_rn(x, y, -__fmul_rn(w, z)));
+    const float a2y = __fsub_rn(1.f, __fmul_rn(2.f, __fmaf_rn(x, x, __fmul_rn(z, z))));
+    const float a2z = __fmul_rn(2.f, __fmaf_rn(w, x, __fmul_rn(y, z)));
+    const float a3x = __fmul_rn(2.f, __fmaf_rn(x, z, __fmul_rn(w, y)));
+    const float a3y = __fmul_rn(2.f, __fmaf_rn(-w, x, __fmul_rn(y, z)));
+    const float a3z = __fsub_rn(1.f, __fmul_rn(2.f, __fmaf_rn(x, x, __fmul_rn(y, y))));
     const float ox = __ldg(p.c2w + 3), oy = __ldg(p.c2w + 7), oz = __ldg(p.c2w + 11);
-    const float dx = mx - ox, dy = my - oy, dz = mz - oz;
-    const float tnum = a3x * dx + a3y * dy + a3z * dz;  // compute_tt numerator, texture_helpers.cuh:303,312
+    const float dx = __fsub_rn(mx, ox), dy = __fsub_rn(my, oy), dz = __fsub_rn(mz, oz);
+    // compute_tt numerator, texture_helpers.cuh:303,312
+    const float tnum = __fmaf_rn(a3z, dz, __fmaf_rn(a3x, dx, __fmul_rn(a3y, dy)));
     const float sx = p.scales[3 * i], sy = p.scales[3 * i + 1];
-    const float is1 = 1.f / (sx * p.glob_scale), is2 = 1.f / (sy * p.glob_scale);
+    const float is1 = __frcp_rn(__fmul_rn(sx, p.glob_scale)), is2 = __frcp_rn(__fmul_rn(sy, p.glob_scale));
     // projected mean (texture.cu:184-185): transform_4x3 + project_pix
     float vm[12];
 #pragma unroll
     for (int k = 0; k < 12; ++k) vm[k] = __ldg(p.viewmat + k);
-    const float vx = vm[0] * mx + vm[1] * my + vm[2] * mz + vm[3];
-    const float vy = vm[4] * mx + vm[5] * my + vm[6] * mz + vm[7];
-    const float vz = vm[8] * mx + vm[9] * my + vm[10] * mz + vm[11];
-    const float rw = 1.f / (vz + 1e-6f);
-    const float xy_x = vx * rw * p.fx + p.cx, xy_y = vy * rw * p.fy + p.cy;
+    const float vx = __fadd_rn(vm[3], __fmaf_rn(mz, vm[2], __fmaf_rn(mx, vm[0], __fmul_rn(my, vm[1]))));
+    const float vy = __fadd_rn(vm[7], __fmaf_rn(mz, vm[6], __fmaf_rn(mx, vm[4], __fmul_rn(my, vm[5]))));
+    const float vz = __fadd_rn(vm[11], __fmaf_rn(mz, vm[10], __fmaf_rn(mx, vm[8], __fmul_rn(my, vm[9]))));
+    const float rw = __frcp_rn(__fadd_rn(vz, 1e-6f));
+    const float xy_x = __fmaf_rn(p.fx, __fmul_rn(vx, rw), p.cx), xy_y = __fmaf_rn(p.fy, __fmul_rn(vy, rw), p.cy);
     const int h = p.texture_dims[3 * i], wd = p.texture_dims[3 * i + 1], st = p.texture_dims[3 * i + 2];
     const float opac = p.opacities[i];
     SplatRec r;
     r.q[0] = make_float4(mx, my, mz, tnum);
     r.q[1] = make_float4(a3x, a3y, a3z, opac);
-    r.q[2] = make_float4(a1x, a1y, a1z, is1 * is1);
-    r.q[3] = make_float4(a2x, a2y, a2z, is2 * is2);
+    r.q[2] = make_float4(a1x, a1y, a1z, __fmul_rn(is1, is1));
+    r.q[3] = make_float4(a2x, a2y, a2z, __fmul_rn(is2, is2));
     r.q[4] = make_float4(xy_x, xy_y, __int_as_float(h), __int_as_float(wd));
     r.q[5] = make_float4(p.colors[3 * i], p.colors[3 * i + 1], p.colors[3 * i + 2], __int_as_float(st));
     r.q[6] = make_float4(p.umap[3 * i], p.umap[3 * i + 1], p.umap[3 * i + 2], p.uv0[2 * i]);
@@ -151,7 +164,7 @@ __global__ void __launch_bounds__(kThreads1D) pack_records_kernel(const PackPara
 #pragma unroll
     for (int k = 0; k < 8; ++k) p.recs[i].q[k] = r.q[k];
     p.recs_bwd[i].quat = qt;
-    p.recs_bwd[i].aux = make_float4(1.f / sx, 1.f / sy, rw, 0.f);
+    p.recs_bwd[i].aux = make_float4(__frcp_rn(sx), __frcp_rn(sy), rw, 0.f);
 
     // support box, in double
     const double gsx = (double)sx * (double)p.glob_scale, gsy = (double)sy * (double)p.glob_scale;

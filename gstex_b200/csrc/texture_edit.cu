@@ -202,9 +202,7 @@ extern "C" int gstex_texture_edit(int img_height, int img_width, int block_width
     const int use_blur = settings & 1;  // texture_edit.cu:48 (bit 0, not the forward's bit 9)
     const int num_tiles = ((img_width + block_width - 1) / block_width) * ((img_height + block_width - 1) / block_width);
     {
-        // colours are not composited here: any readable (n,3) array serves as the packer's colour input.  (pack.cu is
-        // left byte-identical on purpose: its fp32 expressions are contracted by nvcc exactly as the reference
-        // kernel's are, and an unrelated edit there was seen to change that -- out_texture moved by 1e-4.)
+        // colours are not composited here: any readable (n,3) array serves as the packer's colour input
         const int rc = launch_pack_records(n, texture_dims, /*colors=*/means, opacities, means, scales, glob_scale,
                                            quats, uv0, umap, vmap, viewmat, c2w, fx, fy, cx, cy,
                                            use_blur ? GSTEX_SET_BLUR : 0, workspace, st, tile_bins, num_tiles);
