@@ -173,10 +173,8 @@ def test_edit_argument_errors():
     e = make_edit_inputs(scene_to_numpy(s), window="all")
     with pytest.raises(ValueError):
         run_ours_edit(s, e, 0, channels=3)
-    with pytest.raises(NotImplementedError):
-        G.texture_edit((1, 1, 5), *([None] * 26), use_torch_impl=True, block_width=16) if False else \
-            G.texture_edit((1, 1, 5), None, None, None, None, None, None, None, None, None, None, None, None, 1, None,
-                           None, None, None, None, None, 1.0, 1.0, 0.0, 0.0, 8, 8, 16, 0, None, True)
+    with pytest.raises(NotImplementedError):  # use_torch_impl=True: there is no PyTorch/CPU path
+        G.texture_edit((1, 1, 5), *([None] * 12), 1, *([None] * 6), 1.0, 1.0, 0.0, 0.0, 8, 8, 16, 0, None, True)
     cpu = {k: (x.clone() if isinstance(x, torch.Tensor) else x) for k, x in s.items()}
     with pytest.raises(RuntimeError):  # CPU tensors: there is no CPU path
         z = torch.zeros
