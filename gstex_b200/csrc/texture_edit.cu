@@ -10,8 +10,9 @@
 // HOW (ours): the per-view packed records and conservative support boxes of pack.cu; warp-autonomous units
 // (32 pixels, an 8x4 block of a 16x16 tile) handed out longest tile list first by a persistent grid; per round of 32
 // list entries a warp tests the support boxes against its block, compacts the survivors and pulls their 128-byte
-// records into its own shared-memory stage with coalesced 16-byte loads (8 lanes per record), then evaluates them
-// in list order.  Culling is exact: a culled pair has alpha < 1/255 (skipped by the reference too); it could only
+// records into its own double-buffered shared-memory stage (cp.async, 8 lanes x 16 B per record) one round ahead
+// of the round it evaluates in list order; ids are requested three rounds ahead and boxes two, so a warp walking a
+// long list alone does not sit through the id -> box -> record chain of dependent loads every round.  Culling is exact: a culled pair has alpha < 1/255 (skipped by the reference too); it could only
 // END a pixel whose transmittance is within a factor 255/254 of the 1e-4 threshold, and from the moment a warp
 // holds such a pixel it evaluates every remaining entry of the list.  Products that are exactly zero (untouched
 // canvas: m = 0; zero bilinear weights at chart borders) are not sent to memory: x + 0 == x, so no result changes,
@@ -40,19 +41,44 @@ struct EditParams {
     int force_nocull;
 };
 
-constexpr int kEditWarps = 8;
+constexpr int kEditWarps = 4;  // double-buffered 4 KB record stages: 8.5 KB per warp, static shared memory < 48 KB
 // T * (1 - alpha) <= 1e-4 with alpha < 1/255 needs T <= 1e-4 * 255/254 = 1.0039e-4; a little above that
 constexpr float kEditDangerT = 1.01e-4f;
 
 struct EditWarpShared {
-    SplatRec rec[32];  // 4 KB
-    int pos[32];       // round-local list position of each staged record
-    int gid[32];       // and its splat
+    SplatRec rec[2][32];  // 2 x 4 KB: the round being evaluated and the round being fetched
+    int pos[2][32];       // round-local list position of each staged record
+    int gid[2][32];       // and its splat
 };
 struct EditShared {
     EditWarpShared w[kEditWarps];
     Camera cam;
 };
+
+__device__ __forceinline__ void edit_cp_async16(void* smem_dst, const void* gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)),
+                 "l"(gmem_src)
+                 : "memory");
+}
+__device__ __forceinline__ void edit_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void edit_cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void edit_cp_async_wait_all_but_one() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+
+// Compacts the entries of `mask` (bit = lane of the round) into stage `b` and starts the copy of their records
+// (8 lanes x 16 B per record, cp.async -> LDGSTS: nobody waits here).  Returns the number of staged records.
+__device__ __forceinline__ int edit_stage(EditWarpShared& ws, int b, unsigned mask, int gid, int lane,
+                                          const SplatRec* __restrict__ recs) {
+    const int ns = __popc(mask);
+    if ((mask >> lane) & 1u) {
+        const int rank = __popc(mask & ((1u << lane) - 1u));
+        ws.pos[b][rank] = lane;
+        ws.gid[b][rank] = gid;
+    }
+    __syncwarp();
+    for (int s = lane >> 3; s < ns; s += 4) edit_cp_async16(&ws.rec[b][s].q[lane & 7], &recs[ws.gid[b][s]].q[lane & 7]);
+    edit_cp_async_commit();
+    return ns;
+}
 
 __device__ __forceinline__ void edit_add(float* p, float v) {
     if (v != 0.f) atomicAdd(p, v);  // result unused: RED.E.ADD.F32
@@ -98,42 +124,45 @@ __global__ void __launch_bounds__(kEditWarps * 32) texture_edit_kernel(const Edi
         float T = 1.f;
         bool danger = p.force_nocull != 0;  // warp-uniform: culling is off from here on
 
-        for (int base = range.x; base < range.y; base += 32) {
-            if (__all_sync(0xffffffffu, done)) break;
-            const int idx = base + lane;
-            const bool valid = idx < range.y;
-            int gid = 0;
-            bool hit = false;
-            if (valid) {
-                gid = __ldg(p.ids + idx);
-                const float4 b = __ldg(p.boxes + gid);
-                hit = (b.x <= X1) && (b.z >= X0) && (b.y <= Y1) && (b.w >= Y0);
-            }
-            const unsigned valid_mask = __ballot_sync(0xffffffffu, valid);
-            unsigned pending = danger ? valid_mask : __ballot_sync(0xffffffffu, hit);
-            while (pending) {
-                // ---- stage the pending entries' records, in list order
-                const int ns = __popc(pending);
-                if ((pending >> lane) & 1u) {
-                    const int rank = __popc(pending & lt_mask);
-                    ws.pos[rank] = lane;
-                    ws.gid[rank] = gid;
-                }
-                __syncwarp();
-                for (int s = lane >> 3; s < ns; s += 4) ws.rec[s].q[lane & 7] = __ldg(&p.recs[ws.gid[s]].q[lane & 7]);
-                __syncwarp();
-                pending = 0u;
+        // ---- software pipeline over rounds of 32 list entries.  A warp walking a long list alone is bound by the
+        // chain of dependent loads per round (id -> support box -> record): ids are requested three rounds ahead,
+        // boxes two, and the culled survivors' records one round ahead (cp.async into the other stage), so that the
+        // evaluation of round r waits for none of them.
+        const int nrounds = (range.y - range.x + 31) >> 5;
+        auto load_gid = [&](int r) { const int i = range.x + 32 * r + lane; return (r < nrounds && i < range.y) ? __ldg(p.ids + i) : -1; };
+        auto load_box = [&](int g) { return g >= 0 ? __ldg(p.boxes + g) : make_float4(1.f, 1.f, 0.f, 0.f); };
+        auto hits = [&](const float4 b) { return (b.x <= X1) && (b.z >= X0) && (b.y <= Y1) && (b.w >= Y0); };
+        int gid_c = load_gid(0), gid_1 = load_gid(1), gid_2 = load_gid(2);
+        float4 box_1 = load_box(gid_1);
+        unsigned valid_c = __ballot_sync(0xffffffffu, gid_c >= 0);
+        int ns_c = edit_stage(ws, 0, danger ? valid_c : __ballot_sync(0xffffffffu, gid_c >= 0 && hits(load_box(gid_c))),
+                              gid_c, lane, p.recs);
+        for (int r = 0; r < nrounds; ++r) {
+            const int cur = r & 1;
+            if (__all_sync(0xffffffffu, done)) break;  // (outstanding copies are drained below)
+            // next round: cull with the boxes requested one iteration ago, start its record copies
+            const unsigned valid_n = __ballot_sync(0xffffffffu, gid_1 >= 0);
+            const bool culled_n = !danger;
+            int ns_n = edit_stage(ws, cur ^ 1, danger ? valid_n : __ballot_sync(0xffffffffu, gid_1 >= 0 && hits(box_1)),
+                                  gid_1, lane, p.recs);
+            const float4 box_2 = load_box(gid_2);
+            const int gid_3 = load_gid(r + 3);
+            edit_cp_async_wait_all_but_one();  // this round's records have landed
+            __syncwarp();
+            int ns = ns_c;
+            while (ns > 0) {
+                unsigned pending = 0u;
                 for (int s = 0; s < ns; ++s) {
                     if (!done) {
-                        const SplatRec& r = ws.rec[s];
-                        const float4 r0 = r.q[0], r1 = r.q[1], r2 = r.q[2], r3 = r.q[3], r4 = r.q[4];
+                        const SplatRec& rc = ws.rec[cur][s];
+                        const float4 r0 = rc.q[0], r1 = rc.q[1], r2 = rc.q[2], r3 = rc.q[3], r4 = rc.q[4];
                         const PairEval e = eval_pair(pix, r0, r1, r2, r3, r4, use_blur);
                         const float next_T = T * (1.f - e.alpha);
                         if (next_T <= 1e-4f) done = true;  // tested before `skip`, texture_edit.cu:171-176
                         if (!e.skip && !done) {
                             const float t_view = e.t * pix.view_depth;
                             if (t_view >= lo && t_view <= hi) {
-                                const float4 r5 = r.q[5], r6 = r.q[6], r7 = r.q[7];
+                                const float4 r5 = rc.q[5], r6 = rc.q[6], r7 = rc.q[7];
                                 const float u = clamp01(r6.w + (r6.x * e.delta.x + r6.y * e.delta.y + r6.z * e.delta.z));
                                 const float v = clamp01(r7.w + (r7.x * e.delta.x + r7.y * e.delta.y + r7.z * e.delta.z));
                                 const TexQuery tq = tex_query(__float_as_int(r4.z), __float_as_int(r4.w),
@@ -159,14 +188,30 @@ __global__ void __launch_bounds__(kEditWarps * 32) texture_edit_kernel(const Edi
                         // a pixel of this warp can now be ended by a pair the boxes would cull: evaluate every
                         // remaining entry of the list, starting with the rest of this round
                         danger = true;
-                        const int j = ws.pos[s];
-                        pending = valid_mask & ~((2u << j) - 1u);
+                        const int j = ws.pos[cur][s];
+                        pending = valid_c & ~((2u << j) - 1u);
                         break;
                     }
                 }
-                __syncwarp();
+                ns = 0;
+                if (pending) {  // restage the rest of this round unculled (the next round's copies finish with it)
+                    __syncwarp();
+                    ns = edit_stage(ws, cur, pending, gid_c, lane, p.recs);
+                    edit_cp_async_wait_all();
+                    __syncwarp();
+                }
             }
+            if (danger && culled_n) {  // the next round was staged culled before the flip: stage it again, in full
+                edit_cp_async_wait_all();
+                __syncwarp();
+                ns_n = edit_stage(ws, cur ^ 1, valid_n, gid_1, lane, p.recs);
+            }
+            __syncwarp();
+            gid_c = gid_1; valid_c = valid_n; ns_c = ns_n;
+            gid_1 = gid_2; box_1 = box_2; gid_2 = gid_3;
         }
+        edit_cp_async_wait_all();  // nothing of this unit may still be landing when the next unit stages
+        __syncwarp();
     }
 }
 
@@ -226,7 +271,7 @@ extern "C" int gstex_texture_edit(int img_height, int img_width, int block_width
         const char* env = getenv("GSTEX_DBG");
         p.force_nocull = (env && (atoi(env) & 16)) ? 1 : 0;
     }
-    int grid = 148 * 4;  // persistent: units come from the cursor, surplus CTAs leave at once
+    int grid = 148 * 6;  // persistent: units come from the cursor, surplus CTAs leave at once
     if (grid > (p.num_units + kEditWarps - 1) / kEditWarps) grid = (p.num_units + kEditWarps - 1) / kEditWarps;
     texture_edit_kernel<<<grid, kEditWarps * 32, 0, st>>>(p);
     GSTEX_LAUNCH_CHECK();
