@@ -31,6 +31,7 @@ from gstex_b200.multiview import GradientBucket, shard_views  # noqa: E402
 
 METRIC = "fwd+bwd Mpix/s, 1M textured splats @800x800 (project+bin+sort+forward+backward)"
 UNIT = "Mpix/s"
+OWN_BINNING_STREAM = True  # --binning-stream own|current
 PARAM_KEYS = ["colors", "opacities", "means", "scales", "quats", "uv0", "umap", "vmap", "texture"]
 VOUT_KEYS = ["v_out_img", "v_out_depth", "v_out_reg", "v_out_alpha", "v_out_texture", "v_out_normal"]
 
@@ -47,6 +48,8 @@ def parse_args():
     ap.add_argument("--size", type=int, default=None, help="override image size (debug)")
     ap.add_argument("--no-ref-cuda", action="store_true", help="skip timing the reference CUDA extension")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--binning-stream", default="own", choices=["own", "current"],
+                    help="next view's projection + binning on a stream of their own (default) or on the current stream")
     return ap.parse_args()
 
 
@@ -153,7 +156,7 @@ class Workload:
         if self.binning is None:
             from gstex_b200.multiview import BinningStream
 
-            self.binning = BinningStream(self.dev)
+            self.binning = BinningStream(self.dev, own_stream=OWN_BINNING_STREAM)
         p = self.params
         return self.binning.begin(p["means"], p["scales"], 1, p["quats"], viewmat, self.intr, self.H, self.W, self.bw,
                                   wait_for_current=first)
@@ -214,7 +217,7 @@ class Workload:
         if self.binning is None:
             from gstex_b200.multiview import BinningStream
 
-            self.binning = BinningStream(self.dev)
+            self.binning = BinningStream(self.dev, own_stream=OWN_BINNING_STREAM)
         side = (self.binning.stream,)  # reads each view's camera matrix
         fd.prefetch(view_in(0))
         d = fd.take(also=side)
@@ -354,7 +357,9 @@ def ncu_traffic(kernel_key):
 
 
 def main():
+    global OWN_BINNING_STREAM
     args = parse_args()
+    OWN_BINNING_STREAM = args.binning_stream == "own"
     # stdout carries ONE JSON line and nothing else: libraries that log to file descriptor 1 (NCCL's version banner and
     # NCCL_DEBUG output go to stdout) are sent to stderr for the whole run, the line is written to the saved descriptor
     sys.stdout.flush()
@@ -460,9 +465,9 @@ def main():
                                "frac": ab["total"] * args.views_per_gpu / (ms_per_step * 1e-3) / 1e9 / peak,
                                "frac_of_nominal_8tbs": ab["total"] * args.views_per_gpu / (ms_per_step * 1e-3) / 1e9 / 8000.0},
                 "per_entry_ms_per_view": {k: x[2] / args.steps / args.views_per_gpu for k, x in entry_ms.items()},
-                "streams": "2: the next view's projection + binning (gstex_b200.multiview.BinningStream) run beside this "
-                           "view's forward/backward, so the per-entry CUDA-event times overlap, include the wait for SMs "
-                           "and sum to more than the step"}
+                "streams": ("2: the next view's projection + binning (gstex_b200.multiview.BinningStream) run beside this "
+                            "view's forward/backward, so the per-entry CUDA-event times overlap, include the wait for SMs "
+                            "and sum to more than the step") if OWN_BINNING_STREAM else "1 (--binning-stream current)"}
 
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,

@@ -154,11 +154,13 @@ class BinningStream:
             """The four positional arguments of `texture_gaussians` this stage produces."""
             return self.centers, self.extents, self.depths, self.num_tiles_hit
 
-    def __init__(self, device):
+    def __init__(self, device, own_stream: bool = True):
+        """`own_stream=False` keeps the same call sequence on the CURRENT stream (no overlap, fewer host-side stream
+        and event operations per view): the A/B switch of `bench.py --binning-stream current`."""
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise RuntimeError("BinningStream needs a CUDA device (there is no CPU path)")
-        self.stream = torch.cuda.Stream(self.device)
+        self.stream = torch.cuda.Stream(self.device) if own_stream else torch.cuda.current_stream(self.device)
 
     def begin(self, means, scales, glob_scale, quats, viewmat, intrins, img_height: int, img_width: int,
               block_width: int, *, wait_for_current: bool = True) -> "BinningStream.Prepared":
