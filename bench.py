@@ -204,17 +204,15 @@ class Workload:
                 self.binning.finish(pre)
         self.reduce_grads(world)
 
-    def step_e2e(self, world, host):
-        """Same step, but every view's inputs (camera, upstream-gradient images) come from pinned HOST memory
-        and its result (rendered image + a scalar) goes back to the host inside the timed region.  The copies
-        are real and counted every step; `HostViewFeeder` runs them one view ahead / behind on copy streams."""
+    def _e2e_loop(self, world, host, view_in, backward, results):
+        """Common skeleton of the two end-to-end legs: every view's HOST inputs are prefetched one view ahead on a copy
+        stream (`HostViewFeeder`), its results go back behind the compute, the host waits once at the end of the step."""
         if self.feeder is None:
             from gstex_b200.multiview import HostViewFeeder
 
             self.feeder = HostViewFeeder(self.dev)
         fd, nv = self.feeder, len(self.viewmats)
         self.zero_grad(world)
-        view_in = lambda i: {"vm": host["viewmats"][i], "c2w": host["c2ws"][i], "v": host["v"]}
         if self.binning is None:
             from gstex_b200.multiview import BinningStream
 
@@ -230,30 +228,60 @@ class Workload:
             outs = self.forward_view(pre, d["vm"], d["c2w"])
             d_next = fd.take(also=side) if i + 1 < nv else None
             pre = self.prep_view(d_next["vm"]) if d_next is not None else None
-            self.backward_view(outs, d["v"])
+            res = backward(outs, d)
             if pre is not None:
                 self.binning.finish(pre)
             if i + 2 < nv:  # view i's staging slot is free once its backward is enqueued
                 fd.prefetch(view_in(i + 2))
-            fd.send_back(outs[0].detach(), host["out_img"][i])
-            fd.send_back(outs[3].detach().sum(), host["scalar"][i])
+            for dev_t, host_t in results(i, outs, res):
+                fd.send_back(dev_t, host_t)
             d = d_next
         self.reduce_grads(world)
         fd.finish()  # the host consumes the result every step
 
+    def step_e2e(self, world, host):
+        """The training step as the reference's trainer runs it (NS/pipelines/base_pipeline.py:291-304): per view the
+        camera and the uint8 ground-truth image come from pinned HOST memory (full_images_datamanager.py:316-333), the
+        image is rendered, composited and compared on the device (`gstex_b200.photometric_loss` = gstex.py:1204-1205,
+        1297-1319), its backward feeds `texture_gaussians`' backward, and the three loss values go back to the host."""
+        import gstex_b200 as G
+
+        def backward(outs, d):
+            gt = d["gt"].to(self.torch.float32) / 255.0  # get_gt_img, NS/models/gstex.py:1260-1275
+            _, main, l1, ssim = G.photometric_loss(outs[0], outs[4], outs[3], self.background, gt, 0.2)
+            main.backward()
+            return self.torch.stack([main.detach(), l1, ssim])
+
+        self._e2e_loop(world, host, lambda i: {"vm": host["viewmats"][i], "c2w": host["c2ws"][i], "gt": host["gt"][i]},
+                       backward, lambda i, outs, res: [(res, host["losses"][i])])
+
+    def step_e2e_upstream(self, world, host):
+        """Round-1 leg, kept for continuity: fixed upstream-gradient images (six fp32 images, 30.7 MB per view) from
+        pinned host memory instead of a ground-truth image; rendered image + a scalar back to the host."""
+        def backward(outs, d):
+            self.backward_view(outs, d["v"])
+
+        self._e2e_loop(world, host, lambda i: {"vm": host["viewmats"][i], "c2w": host["c2ws"][i], "v": host["v"]},
+                       backward, lambda i, outs, res: [(outs[0].detach(), host["out_img"][i]),
+                                                       (outs[3].detach().sum(), host["scalar"][i])])
+
     def make_host(self):
         torch = self.torch
         nv = len(self.viewmats)
+        g = torch.Generator().manual_seed(4242)
         host = {
             "viewmats": [m.cpu().pin_memory() for m in self.viewmats],
             "c2ws": [m.cpu().pin_memory() for m in self.c2ws],
             "v": {k: x.cpu().pin_memory() for k, x in self.v.items()},
+            "gt": [torch.randint(0, 256, (self.H, self.W, 3), dtype=torch.uint8, generator=g).pin_memory() for _ in range(nv)],
             "out_img": [torch.empty(self.H, self.W, 3).pin_memory() for _ in range(nv)],
             "scalar": [torch.empty(()).pin_memory() for _ in range(nv)],
+            "losses": [torch.empty(3).pin_memory() for _ in range(nv)],
         }
-        h2d = nv * (2 * 16 * 4 + sum(x.numel() * 4 for x in host["v"].values()))
-        d2h = nv * (self.H * self.W * 3 * 4 + 4)
-        return host, h2d, d2h
+        cam = 2 * 16 * 4
+        bytes_ = {"loss": (nv * (cam + self.H * self.W * 3), nv * 12),
+                  "upstream": (nv * (cam + sum(x.numel() * 4 for x in host["v"].values())), nv * (self.H * self.W * 3 * 4 + 4))}
+        return host, bytes_
 
     def stats(self):
         """Intersections and depth complexity of view 0 (data dependent; reported with every number)."""
@@ -266,6 +294,14 @@ class Workload:
         return int(nth.sum().item())
 
 
+def host_threads():
+    """Host threads this process may run on (cgroup/affinity aware)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def cpu_reference_view(s, v, threads=None):
     """One view (view 0) fwd+bwd of the same scene through the CPU restatement of the reference algorithm
     (oracle/, OpenMP over tiles).  Returns (seconds, num_intersects, threads)."""
@@ -273,8 +309,8 @@ def cpu_reference_view(s, v, threads=None):
     import oracle
     from common import run_oracle_pipeline, scene_to_numpy
 
-    if threads:
-        oracle.set_num_threads(threads)
+    # torchrun exports OMP_NUM_THREADS=1 to every rank: the CPU arm sets its own thread count, always
+    oracle.set_num_threads(threads or host_threads())
     d = scene_to_numpy(s)
     vn = {k: x.numpy() for k, x in v.items()}
     t0 = time.perf_counter()
@@ -340,6 +376,10 @@ def time_reference_cuda(wl, s):
     return statistics.median(times)
 
 
+def stats3(xs):
+    return {"min": min(xs), "median": statistics.median(xs), "max": max(xs)}
+
+
 def measured_peak_gbs():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -348,11 +388,28 @@ def measured_peak_gbs():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def ncu_traffic(kernel_key):
-    """DRAM bytes per launch of the dominant kernel from the committed ncu capture (profiles/traffic.json)."""
+def kernel_source_stamp():
+    """sha256 over the CUDA sources: ties profiles/traffic.json (written by scripts/ncu_traffic.py from an ncu capture)
+    to the build it was captured from -- the GPU box has no .git to ask."""
+    import glob
+    import hashlib
+
+    h = hashlib.sha256()
+    for f in sorted(glob.glob(os.path.join(ROOT, "gstex_b200", "csrc", "*.cu*"))):
+        h.update(os.path.basename(f).encode())
+        h.update(open(f, "rb").read())
+    return h.hexdigest()[:16]
+
+
+def ncu_capture(kernel_key):
+    """{"dram_bytes", "inst"} per launch of the entry point's dominant kernel from the committed ncu capture, or None
+    when profiles/traffic.json was captured from other kernel sources than the ones being timed."""
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            return json.load(f).get(kernel_key)
+            d = json.load(f)
+        if d.get("source_stamp") != kernel_source_stamp():
+            return None
+        return d.get(kernel_key)
     except Exception:
         return None
 
@@ -408,41 +465,46 @@ def main():
     P = H * W
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
 
-    for _ in range(max(args.warmup, 1)):
-        wl.step(world)
-    barrier()
+    def timed(step_fn, before=None):
+        """W warm-up steps, then EXACTLY K steps between barrier + synchronize on both sides; one CUDA event per step
+        boundary.  Returns (ms per step from the first to the last event, max over ranks; per-step ms of this rank)."""
+        for _ in range(max(args.warmup, 3 if args.steps > 1 else 1)):
+            step_fn()
+        barrier()
+        if before is not None:
+            before()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+        ev[0].record()
+        for k in range(args.steps):
+            step_fn()
+            ev[k + 1].record()
+        barrier()
+        per = [ev[k].elapsed_time(ev[k + 1]) for k in range(args.steps)]
+        return max_over_ranks(ev[0].elapsed_time(ev[-1])) / args.steps, per
+
     clocks = ClockSampler(local_rank)
-    if rank == 0:
-        clocks.start()
-    launches0 = lib.gstex_launch_count()
-    _lib.Timing.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(args.steps):
-        wl.step(world)
-    e1.record()
-    barrier()
+    launches0 = [0]
+
+    def begin_timed_region():
+        if rank == 0:
+            clocks.start()
+        launches0[0] = lib.gstex_launch_count()
+        _lib.Timing.start()
+
+    ms_per_step, per_step = timed(lambda: wl.step(world), before=begin_timed_region)
     per_call = _lib.Timing.stop()
-    launches = lib.gstex_launch_count() - launches0
-    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    launches = lib.gstex_launch_count() - launches0[0]
     clk = clocks.stop() if rank == 0 else None
-    ms_per_step = ms_total / args.steps
     value = total_views * P / (ms_per_step * 1e-3) / 1e6
 
     # ---- end to end through the public API with host buffers
-    host, h2d, d2h = wl.make_host()
-    for _ in range(max(args.warmup, 1)):
-        wl.step_e2e(world, host)
-    barrier()
+    host, hb = wl.make_host()
     t0 = time.perf_counter()
-    e0.record()
-    for _ in range(args.steps):
-        wl.step_e2e(world, host)
-    e1.record()
-    barrier()
+    e2e_ms, e2e_per = timed(lambda: wl.step_e2e(world, host))
     wall = time.perf_counter() - t0
-    e2e_ms = max_over_ranks(max(e0.elapsed_time(e1), 0.0)) / args.steps
     e2e_value = total_views * P / (e2e_ms * 1e-3) / 1e6
+    e2e_up_ms, _ = timed(lambda: wl.step_e2e_upstream(world, host))
+    h2d, d2h = hb["loss"]
 
     if rank != 0:
         if world > 1:
@@ -458,10 +520,16 @@ def main():
     key = {"gstex_texture_backward": "backward", "gstex_texture_forward": "forward", "gstex_sort_isects": "sort"}.get(base, "total")
     peak, peak_src = measured_peak_gbs()
     achieved = ab[key] / (entry_ms[dom][0] * 1e-3) / 1e9
+    cap = ncu_capture(base) or {}
     step_ms_kernels = sum(x[2] for x in entry_ms.values()) / args.steps
     roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "frac_of_nominal_8tbs": achieved / 8000.0,  # both denominators are reported
-                "traffic": ncu_traffic(base), "peak_source": peak_src, "alg_bytes_per_launch": ab[key],
+                "traffic": cap.get("dram_bytes"), "peak_source": peak_src, "alg_bytes_per_launch": ab[key],
+                # instruction-issue roofline of the same kernel: warp-instructions (ncu smsp__inst_executed.sum of the capture
+                # this build was profiled with) / (SMs x 4 schedulers x SM clock) / the kernel's own duration under ncu
+                "issue_frac": cap.get("issue_frac"), "inst_per_launch": cap.get("inst"),
+                "traffic_source": "profiles/traffic.json (ncu capture of this build)" if cap else
+                                  "none: profiles/traffic.json was captured from different kernel sources",
                 "avg_launch_ms": entry_ms[dom][0],
                 "share_of_step": entry_ms[dom][2] / args.steps / ms_per_step,
                 "whole_path": {"alg_bytes_per_view": ab["total"],
@@ -484,16 +552,21 @@ def main():
                    "parallelism": f"views sharded over {world} GPU(s), one NCCL all-reduce of the flat gradient bucket (9 tensors)" if world > 1
                    else "single GPU"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "ms_per_step": e2e_ms, "wall_ms_per_step": wall * 1e3 / args.steps,
-                "what": "per view: camera + upstream-gradient images from pinned host memory, rendered image + scalar "
-                        "back to the host (copy streams, one view ahead/behind the compute: gstex_b200.multiview."
-                        "HostViewFeeder); splat/texture parameters are model state resident in HBM"},
+                "ms_per_step": e2e_ms, "step_ms": stats3(e2e_per),
+                "what": "per view: camera + uint8 ground-truth image from pinned host memory, render, on-device compose + "
+                        "L1/SSIM loss (gstex_b200.photometric_loss) and its backward into texture_gaussians' backward, the "
+                        "three loss values back to the host (copy streams one view ahead/behind the compute: gstex_b200."
+                        "multiview.HostViewFeeder); splat/texture parameters are model state resident in HBM"},
+        "e2e_upstream_grads": {"value": total_views * P / (e2e_up_ms * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": e2e_up_ms,
+                               "h2d_bytes_per_step": hb["upstream"][0], "d2h_bytes_per_step": hb["upstream"][1],
+                               "what": "round-1 leg: six fp32 upstream-gradient images per view from the host, rendered image back"},
+        "step_ms": stats3(per_step),
         "gpu_launches": int(launches),
         "kernel_ms_per_step": step_ms_kernels,
         "roofline": roofline,
         "clocks": clk,
     }
-    if world == 1 and not args.no_cpu_baseline:
+    if not args.no_cpu_baseline:  # rank 0, every N (about 1 s on 16 host threads)
         dt, Icpu, threads = cpu_reference_view(s, v)
         out["cpu_baseline"] = {"value": P / dt / 1e6, "unit": UNIT, "cores": threads, "kind": "port",
                                "sample": f"1 view of the same scene, fwd+bwd incl. binning+sort, {dt:.1f} s, I={Icpu}"}
@@ -505,6 +578,22 @@ def main():
                                                   "what": "reference CUDA kernels + torch cumsum/sort, unmodified, sm_100 build"}
         except Exception as exc:  # the checker must never break the bench
             out["reference_cuda_same_gpu"] = {"error": str(exc)[:200]}
+        try:  # parity of view 0 against the reference's kernels at the benchmark's own size (outside the timed region)
+            from gstex_b200.texture import GradientTargets
+            from oracle import parity
+
+            GradientTargets.clear()
+            rep = parity.compare_view(s, v, dev, view=0)
+            if rep is not None:
+                out["parity"] = {"img_max_rel": rep["img_max_rel"], "grad_max_rel": rep["grad_max_rel"],
+                                 "idx_mismatch": rep["idx_mismatch"], "bin_mismatch": rep["bin_mismatch"],
+                                 "outliers": rep["outliers"], "exact": rep["exact"],
+                                 "what": "view 0 vs the reference's own CUDA kernels on the same tensors: max |err| / tensor "
+                                         "scale over the six images / nine gradients, share of elements outside 1e-5 / 1e-4, "
+                                         "mismatching elements of sorted ids + tile bins + final_idx + depth_idx (idx) and of "
+                                         "depths + centers + extents + tile counts (bin), all of which must be 0"}
+        except Exception as exc:
+            out["parity"] = {"error": str(exc)[:200]}
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()

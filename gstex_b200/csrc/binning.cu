@@ -14,6 +14,21 @@ namespace gstex {
 static std::atomic<long long> g_launches{0};
 void note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
+static std::atomic<int> g_sm_count[64];
+int sm_count() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+    int n = g_sm_count[dev].load(std::memory_order_relaxed);
+    if (n <= 0) {
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;  // B200
+        g_sm_count[dev].store(n, std::memory_order_relaxed);
+    }
+    return n;
+}
+
+static std::atomic<int> g_force_nocull{0};
+int force_nocull_flag() { return g_force_nocull.load(std::memory_order_relaxed); }
+
 // ---------------------------------------------------------------------------------------------
 // projection helpers
 // ---------------------------------------------------------------------------------------------
@@ -172,6 +187,10 @@ using namespace gstex;
 
 
 static int check_bw(int bw) { return (bw >= 2 && bw <= 16) ? GSTEX_OK : GSTEX_E_BADARG; }
+
+extern "C" int gstex_debug_force_nocull(int on) {
+    return gstex::g_force_nocull.exchange(on ? 1 : 0, std::memory_order_relaxed);
+}
 
 extern "C" int gstex_project_bounds(const float* means, const float* scales, float glob_scale, const float* quats,
                                     const float* viewmat, float fx, float fy, float cx, float cy, int n,

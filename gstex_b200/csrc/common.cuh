@@ -22,6 +22,10 @@
 namespace gstex {
 
 void note_launch();  // binning.cu
+// SMs of the current device (cudaDevAttrMultiProcessorCount, cached per device): persistent grids are sized from it.
+int sm_count();
+// Test hook (gstex_debug_force_nocull): the compositing kernels evaluate every list entry for every unit.
+int force_nocull_flag();
 
 constexpr int kThreads1D = 256;  // per-splat / per-intersection kernels
 constexpr float kNear = 0.01f;   // ref: t_near in get_aabb_2d.cu:25, texture.cu:213,294

@@ -166,10 +166,19 @@ __global__ void __launch_bounds__(kThreads1D) pack_records_kernel(const PackPara
     p.recs_bwd[i].quat = qt;
     p.recs_bwd[i].aux = make_float4(__frcp_rn(sx), __frcp_rn(sy), rw, 0.f);
 
-    // support box, in double
+    // support box, in double.  The kernels (like the reference) build R from the quaternion AS GIVEN: for a non-unit
+    // quaternion its columns are neither unit nor orthogonal.  The pair evaluation reads l1 = delta.a1, l2 = delta.a2
+    // on the plane delta.a3 = 0, so the points with l1 = u*sx, l2 = v*sy are delta = u*sx*c1 + v*sy*c2 with c1, c2 the
+    // first two columns of inverse([a1; a2; a3]) = (a2 x a3, a3 x a1) / det -- equal to a1, a2 for a unit quaternion.
     const double gsx = (double)sx * (double)p.glob_scale, gsy = (double)sy * (double)p.glob_scale;
-    const double A1[3] = {(double)a1x * gsx, (double)a1y * gsx, (double)a1z * gsx};
-    const double A2[3] = {(double)a2x * gsy, (double)a2y * gsy, (double)a2z * gsy};
+    const double b1[3] = {a1x, a1y, a1z}, b2[3] = {a2x, a2y, a2z}, b3[3] = {a3x, a3y, a3z};
+    const double c1r[3] = {b2[1] * b3[2] - b2[2] * b3[1], b2[2] * b3[0] - b2[0] * b3[2], b2[0] * b3[1] - b2[1] * b3[0]};
+    const double c2r[3] = {b3[1] * b1[2] - b3[2] * b1[1], b3[2] * b1[0] - b3[0] * b1[2], b3[0] * b1[1] - b3[1] * b1[0]};
+    const double det = b1[0] * c1r[0] + b1[1] * c1r[1] + b1[2] * c1r[2];
+    const bool frame_ok = fabs(det) > 1e-12 && det == det;
+    const double idet = frame_ok ? 1.0 / det : 0.0;
+    const double A1[3] = {c1r[0] * idet * gsx, c1r[1] * idet * gsx, c1r[2] * idet * gsx};
+    const double A2[3] = {c2r[0] * idet * gsy, c2r[1] * idet * gsy, c2r[2] * idet * gsy};
     double a[3], b[3], c[3];
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
@@ -177,7 +186,9 @@ __global__ void __launch_bounds__(kThreads1D) pack_records_kernel(const PackPara
         b[k] = (double)vm[4 * k] * A2[0] + (double)vm[4 * k + 1] * A2[1] + (double)vm[4 * k + 2] * A2[2];
         c[k] = (double)vm[4 * k] * mx + (double)vm[4 * k + 1] * my + (double)vm[4 * k + 2] * mz + (double)vm[4 * k + 3];
     }
-    p.boxes[i] = support_box(a, b, c, (double)opac, p.fx, p.fy, p.cx, p.cy, p.use_blur != 0, xy_x, xy_y);
+    const float inf = __int_as_float(0x7f800000);
+    p.boxes[i] = frame_ok ? support_box(a, b, c, (double)opac, p.fx, p.fy, p.cx, p.cy, p.use_blur != 0, xy_x, xy_y)
+                          : make_float4(-inf, -inf, inf, inf);  // degenerate frame: never culled
 }
 
 int launch_pack_records(int n, const int32_t* texture_dims, const float* colors, const float* opacities,

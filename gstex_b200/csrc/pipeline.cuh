@@ -1,8 +1,9 @@
-// pipeline.cuh -- mbarrier + TMA bulk-copy (cp.async.bulk, SASS UBLKCP) helpers and the shared-memory ring
-// both compositing kernels use: one producer warp stages 32-record batches (gathered by sorted id, one
-// 128-byte bulk copy per record, completion counted in bytes on the stage's "full" mbarrier), the pixel
-// warps consume them and release the stage on its "empty" mbarrier.  Warps therefore run decoupled (no
-// block-wide barrier per batch) up to kStages batches apart.  sm_100a.
+// pipeline.cuh -- mbarrier + TMA bulk-copy (cp.async.bulk, SASS UBLKCP) helpers of the compositing kernels.
+// The forward (raster_fwd.cu) gives every warp a private double-buffered record stage: each lane issues one
+// 128-byte bulk copy of a surviving splat's record, completion is counted in bytes on the stage's mbarrier, and the
+// warp waits on it alone -- no producer warp, no block-wide barrier.  The recompute backward (raster_bwd.cu) keeps
+// the CTA-wide ring: one producer warp stages 32-record batches into kStages slots ("full" mbarrier counted in
+// bytes), the pixel warps consume them and release a slot on its "empty" mbarrier.  sm_100a.
 #pragma once
 #include "raster_common.cuh"
 

@@ -14,8 +14,6 @@
 //   * per-splat gradients are summed with a segmented shuffle reduction over the lanes holding the same splat
 //     and leave the warp as one atomicAdd per (splat, value); texel gradients are the 4*C atomics of the
 //     reference, now issued by full warps.
-#include <cstdlib>
-
 #include "bwd_stream.cuh"
 
 namespace gstex {
@@ -52,7 +50,7 @@ __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src)
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all_but_one() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 
-__global__ void __launch_bounds__(kStreamWarps * 32, 2) texture_backward_stream_kernel(const StreamBwdParams p, const int dbg) {
+__global__ void __launch_bounds__(kStreamWarps * 32, 2) texture_backward_stream_kernel(const StreamBwdParams p) {
     extern __shared__ __align__(16) unsigned char stream_smem[];
     StreamShared& sm = *reinterpret_cast<StreamShared*>(stream_smem);
     if (*(volatile uint32_t*)&p.sv.hdr->overflow != 0u) return;  // the recompute kernel handles this view
@@ -214,12 +212,10 @@ __global__ void __launch_bounds__(kStreamWarps * 32, 2) texture_backward_stream_
                     if (q.b10 == q.b00) { c00 += c10; c10 = 0.f; }
                     if (q.b11 == q.b01) { c01 += c11; c11 = 0.f; }
                     const float g0 = vis * vt[0], g1 = vis * vt[1], g2 = vis * vt[2];
-                    if (!(dbg & 1)) {
-                        if (c00 != 0.f) red_add_v4(p.tex_acc + q.b00, c00 * g0, c00 * g1, c00 * g2, 0.f);
-                        if (c01 != 0.f) red_add_v4(p.tex_acc + q.b01, c01 * g0, c01 * g1, c01 * g2, 0.f);
-                        if (c10 != 0.f) red_add_v4(p.tex_acc + q.b10, c10 * g0, c10 * g1, c10 * g2, 0.f);
-                        if (c11 != 0.f) red_add_v4(p.tex_acc + q.b11, c11 * g0, c11 * g1, c11 * g2, 0.f);
-                    }
+                    if (c00 != 0.f) red_add_v4(p.tex_acc + q.b00, c00 * g0, c00 * g1, c00 * g2, 0.f);
+                    if (c01 != 0.f) red_add_v4(p.tex_acc + q.b01, c01 * g0, c01 * g1, c01 * g2, 0.f);
+                    if (c10 != 0.f) red_add_v4(p.tex_acc + q.b10, c10 * g0, c10 * g1, c10 * g2, 0.f);
+                    if (c11 != 0.f) red_add_v4(p.tex_acc + q.b11, c11 * g0, c11 * g1, c11 * g2, 0.f);
                 }
                 {   // distortion_vjp, helpers.cuh:266-269, with the FINAL sums
                     const float d = use_ndc ? div_normal(kFar * t_view - kFar * kNear, (kFar - kNear) * t_view) : e.t;
@@ -246,7 +242,7 @@ __global__ void __launch_bounds__(kStreamWarps * 32, 2) texture_backward_stream_
                 if (!valid) same = 1u << lane;
                 const int rank = __popc(lane == 31 ? 0u : (same >> (lane + 1)));
                 const int steps = __reduce_max_sync(0xffffffffu, rank) + 1;
-                for (int s = 0; s < ((dbg & 4) ? 1 : steps); ++s) {
+                for (int s = 0; s < steps; ++s) {
                     if (rank == s && valid) {
                         const float run = tab[F_VTRUN][pl];
                         v_alpha = T * v_vis - T * run;
@@ -320,7 +316,7 @@ __global__ void __launch_bounds__(kStreamWarps * 32, 2) texture_backward_stream_
                 }
                 run &= run >> off;
             }
-            if (head && valid && !(dbg & 2)) {  // four 16-byte vector reductions per (unit, splat)
+            if (head && valid) {  // four 16-byte vector reductions per (unit, splat)
                 float4* acc = p.splat_acc + (size_t)gid * 4;
                 red_add_v4(acc, v[0], v[1], v[2], v[3]);
                 red_add_v4(acc + 1, v[4], v[5], v[6], 0.f);
@@ -380,16 +376,15 @@ int launch_backward_stream(const StreamBwdParams& p, cudaStream_t st) {
     // the work counter is the only state the backward owns in the header
     GSTEX_CUDA_TRY(cudaMemsetAsync(&p.sv.hdr->next_unit, 0, sizeof(uint32_t), st));
     if (!p.scratch_clean) GSTEX_CUDA_TRY(cudaMemsetAsync(p.tex_acc, 0, grad_scratch_bytes(p.n, p.num_texels), st));
-    int blocks = 148 * 2;
+    int blocks = sm_count() * 2;
     const int need = (p.sv.num_units + kStreamWarps - 1) / kStreamWarps;
     if (blocks > need) blocks = need;
     if (blocks < 1) blocks = 1;
-    const char* env = getenv("GSTEX_DBG");
     GSTEX_CUDA_TRY(cudaFuncSetAttribute(texture_backward_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)sizeof(StreamShared)));
-    texture_backward_stream_kernel<<<blocks, kStreamWarps * 32, sizeof(StreamShared), st>>>(p, env ? atoi(env) : 0);
+    texture_backward_stream_kernel<<<blocks, kStreamWarps * 32, sizeof(StreamShared), st>>>(p);
     GSTEX_LAUNCH_CHECK();
-    unpack_grads_kernel<<<148 * 8, 256, 0, st>>>(p.tex_acc, p.num_texels, p.C, p.tex_scale, p.splat_acc, p.n, p.v_texture, p.v_colors,
+    unpack_grads_kernel<<<sm_count() * 8, 256, 0, st>>>(p.tex_acc, p.num_texels, p.C, p.tex_scale, p.splat_acc, p.n, p.v_texture, p.v_colors,
                                                   p.v_opacity, p.v_means, p.v_scales, p.v_quats);
     GSTEX_LAUNCH_CHECK();
     return GSTEX_OK;

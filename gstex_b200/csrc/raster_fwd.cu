@@ -52,7 +52,7 @@ struct FwdParams {
     const int32_t* order;   // tiles, longest list first (nullptr: natural order)
     float tex_scale, tex_bias;  // every fetched sample is tex_scale * sample + tex_bias (1, 0: the reference's call)
     int units_per_tile, num_units;
-    int force_nocull;  // debugging / tests (GSTEX_DBG bit 4): evaluate every list entry for every unit
+    int force_nocull;  // tests (gstex_debug_force_nocull): evaluate every list entry for every unit
     StreamView sv;  // pair stream (REC kernels only)
 };
 
@@ -523,12 +523,9 @@ extern "C" int gstex_texture_forward_act(int img_height, int img_width, int bloc
     p.order = (n > 0 && tile_bins != nullptr && num_tiles <= kOrderMaxTiles) ? ws_order(workspace, n) : nullptr;
     p.units_per_tile = p.g.threads / 32;
     p.num_units = p.g.tiles_x * p.g.tiles_y * p.units_per_tile;
-    {
-        const char* env = getenv("GSTEX_DBG");
-        p.force_nocull = (env && (atoi(env) & 16)) ? 1 : 0;
-    }
+    p.force_nocull = force_nocull_flag();
     // persistent grid: enough CTAs to fill every SM at the kernels' occupancy, never more than there are units
-    int grid = 148 * kFwdCtasPerSm;
+    int grid = sm_count() * kFwdCtasPerSm;
     if (grid > (p.num_units + kFwdWarps - 1) / kFwdWarps) grid = (p.num_units + kFwdWarps - 1) / kFwdWarps;
     const int threads = kFwdWarps * 32;
     // Record the pair stream for the stream backward when the caller gave a pool and the configuration is the

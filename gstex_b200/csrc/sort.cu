@@ -17,7 +17,9 @@ constexpr int kSortWarps = kSortThreads / 32;
 constexpr int kSortItems = 16;
 constexpr int kSortTile = kSortThreads * kSortItems;  // 4096 keys per tile
 constexpr int kRadix = 256;
-constexpr int kSortMaxBlocks = 148 * 4;
+// Upper bound of the grid AND a layout constant of the workspace (one histogram row per block), so it does not follow
+// the device: 4 CTAs per SM of a 148-SM B200; a part with another SM count runs the same grid.
+constexpr int kSortMaxBlocks = 592;
 
 struct SortGeom {
     int n;                // keys

@@ -267,11 +267,8 @@ extern "C" int gstex_texture_edit(int img_height, int img_width, int block_width
     p.order = num_tiles <= kOrderMaxTiles ? ws_order(workspace, n) : nullptr;
     p.units_per_tile = p.g.threads / 32;
     p.num_units = p.g.tiles_x * p.g.tiles_y * p.units_per_tile;
-    {
-        const char* env = getenv("GSTEX_DBG");
-        p.force_nocull = (env && (atoi(env) & 16)) ? 1 : 0;
-    }
-    int grid = 148 * 6;  // persistent: units come from the cursor, surplus CTAs leave at once
+    p.force_nocull = force_nocull_flag();
+    int grid = sm_count() * 6;  // persistent: units come from the cursor, surplus CTAs leave at once
     if (grid > (p.num_units + kEditWarps - 1) / kEditWarps) grid = (p.num_units + kEditWarps - 1) / kEditWarps;
     texture_edit_kernel<<<grid, kEditWarps * 32, 0, st>>>(p);
     GSTEX_LAUNCH_CHECK();

@@ -241,13 +241,14 @@ class GradientBucket:
         GradientTargets.set(self.params, self.views)
 
     def allreduce(self, world: int, group=None) -> None:
-        """Sum over the ranks (no-op for one rank).  Gradients produced outside autograd's in-place accumulation
-        (a `p.grad` that was replaced) are copied back into the bucket first."""
+        """Sum over the ranks (no-op for one rank).  A gradient produced outside the bucket (a `p.grad` that was
+        replaced by a fresh tensor) is ADDED to the bucket's slice -- which may already hold the sums the fused
+        accumulation (`GradientTargets`) wrote for other views -- before the slice becomes `p.grad` again."""
         for p, v in zip(self.params, self.views):
             if p.grad is None:
                 raise ValueError("GradientBucket.allreduce: a gradient is None on this rank")
             if p.grad is not v:
-                v.copy_(p.grad)
+                v.add_(p.grad)
                 p.grad = v
         if world <= 1:
             return

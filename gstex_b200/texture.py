@@ -8,6 +8,7 @@ Same positional signature (27 arguments), the same six outputs
 from __future__ import annotations
 
 import os
+import weakref
 from typing import Optional, Tuple
 
 import torch
@@ -76,7 +77,7 @@ class GradientTargets:
     at the headline size -- has nothing left to do.  The sums are bit-identical to autograd's.  `clear()` restores
     the plain behaviour."""
 
-    _map = {}
+    _map = {}  # (data_ptr, shape) -> (weak reference to the registered parameter, its gradient target)
 
     @classmethod
     def set(cls, params, grads) -> None:
@@ -84,7 +85,7 @@ class GradientTargets:
         for p, g in zip(params, grads):
             if g.shape != p.shape or g.dtype != torch.float32 or not g.is_contiguous() or g.device != p.device:
                 raise ValueError("GradientTargets: each target must be a contiguous fp32 tensor shaped like its parameter")
-            m[(p.data_ptr(), tuple(p.shape))] = g
+            m[(p.data_ptr(), tuple(p.shape))] = (weakref.ref(p), g)
         cls._map = m
 
     @classmethod
@@ -93,15 +94,24 @@ class GradientTargets:
 
     @classmethod
     def lookup(cls, tensors):
-        """The nine targets if every tensor is registered, else None."""
+        """The nine targets if every tensor is (an alias of) a registered parameter that is STILL ALIVE at the address
+        it was registered with, else None.  A registration whose parameter has been freed or re-allocated (the model
+        replaces its Parameters on densification / re-charting, NS/models/gstex.py:749,890-895, and the caching
+        allocator recycles their addresses) is dropped on sight, so an unrelated tensor that happens to land on a stale
+        address can never be mistaken for it."""
         if not cls._map:
             return None
         out = []
         for t in tensors:
-            g = cls._map.get((t.data_ptr(), tuple(t.shape)))
-            if g is None:
+            key = (t.data_ptr(), tuple(t.shape))
+            ent = cls._map.get(key)
+            if ent is None:
                 return None
-            out.append(g)
+            owner = ent[0]()
+            if owner is None or owner.data_ptr() != key[0] or tuple(owner.shape) != key[1] or owner.device != t.device:
+                del cls._map[key]
+                return None
+            out.append(ent[1])
         return out
 
 

@@ -130,16 +130,16 @@ class TileBinning:
                  "block_counts", "tile_start", "tile_bins", "stats_host", "event", "fast", "result")
 
 
-_PINNED_STATS = {"ring": [], "next": 0}
+_PINNED_FREE = []  # pinned 2-int read-back buffers not owned by any outstanding request
 
 
 def _pinned_stats() -> Tensor:
-    ring = _PINNED_STATS["ring"]
-    if len(ring) < 8:
-        ring.append(torch.empty(2, dtype=torch.int32).pin_memory())
-        return ring[-1]
-    _PINNED_STATS["next"] = (_PINNED_STATS["next"] + 1) % len(ring)
-    return ring[_PINNED_STATS["next"]]
+    """A pinned read-back buffer owned by ONE binning request until `finish_binning` has read it (then it returns to
+    the free list): any number of requests may be outstanding without one's async copy landing in another's buffer."""
+    try:
+        return _PINNED_FREE.pop()
+    except IndexError:
+        return torch.empty(2, dtype=torch.int32).pin_memory()
 
 
 def begin_binning(num_points: int, centers: Tensor, extents: Tensor, depths: Tensor, num_tiles_hit: Tensor,
@@ -150,6 +150,12 @@ def begin_binning(num_points: int, centers: Tensor, extents: Tensor, depths: Ten
     dev = _lib.require_cuda(centers, extents, depths, nth)
     for t, nm in ((centers, "centers"), (extents, "extents"), (depths, "depths")):
         _lib.require_dtype(t, torch.float32, nm)
+    if nth.dtype != torch.int32:  # the reference takes any integer dtype (torch.cumsum, utils.py:57)
+        if nth.dtype.is_floating_point or nth.dtype == torch.bool:
+            raise RuntimeError(f"gstex_b200: num_tiles_hit must be an integer tensor, got {nth.dtype}")
+        nth = nth.to(torch.int32)
+    if nth.numel() != int(num_points):
+        raise RuntimeError(f"gstex_b200: num_tiles_hit has {nth.numel()} entries for {int(num_points)} points")
     b = TileBinning()
     b.num_points, b.centers, b.extents, b.depths = int(num_points), centers, extents, depths
     b.tile_bounds, b.block_size = tile_bounds, int(block_size)
@@ -206,6 +212,9 @@ def finish_binning(b: TileBinning):
         return b.result
     b.event.synchronize()  # the one host wait of the binning stage
     num_intersects, max_list = b.stats_host.tolist()
+    if len(_PINNED_FREE) < 64:
+        _PINNED_FREE.append(b.stats_host)
+    b.stats_host = None
     if num_intersects < 1 or max_list > lib.gstex_tile_bucket_max_list():
         b.result = general(num_intersects)
         return b.result

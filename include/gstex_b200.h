@@ -51,6 +51,11 @@ const char* gstex_error_string(int code);
 /* Number of CUDA kernels this library has launched in this process so far (statistics only). */
 long long gstex_launch_count(void);
 
+/* TEST HOOK: non-zero makes the compositing kernels (forward, texture_edit) evaluate every list entry for every pixel
+ * block instead of culling by support box, so that tests can assert culling never changes a result.  Process-wide;
+ * returns the previous value.  Not for production use (no environment variable is ever read by this library). */
+int gstex_debug_force_nocull(int on);
+
 /* ---- stage (a): per-splat projection, bounds, tile count ------------------------------------- */
 
 /* ref: get_aabb_2d.py:22-32 project_points(points, viewmat, intrins, clip=False).

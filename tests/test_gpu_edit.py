@@ -110,21 +110,19 @@ def test_edit_matches_reference_extension(c):
 
 
 def test_edit_culling_changes_nothing():
-    """GSTEX_DBG bit 4 evaluates every list entry for every unit; the support-box culling must give the same sums
+    """The test hook `gstex_debug_force_nocull` evaluates every list entry for every unit; the support-box culling must give the same sums
     (up to the order of the float atomics)."""
     c = CASES[1]
     s = _scene(c)
     e = make_edit_inputs(scene_to_numpy(s), window="all")
     a, _ = run_ours_edit(s, e, c["settings"])
-    old = os.environ.get("GSTEX_DBG")
-    os.environ["GSTEX_DBG"] = "16"
+    from gstex_b200 import _lib
+
+    _lib.load().gstex_debug_force_nocull(1)
     try:
         b, _ = run_ours_edit(s, e, c["settings"])
     finally:
-        if old is None:
-            del os.environ["GSTEX_DBG"]
-        else:
-            os.environ["GSTEX_DBG"] = old
+        _lib.load().gstex_debug_force_nocull(0)
     a, b = a.cpu().numpy(), b.cpu().numpy()
     assert float(a[:, 4].sum()) > 0
     np.testing.assert_allclose(a, b, rtol=2e-6, atol=2e-6 * float(np.abs(b).max()))

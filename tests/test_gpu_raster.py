@@ -235,16 +235,27 @@ def test_prepared_binning_gives_identical_results():
     assert junk.numel() == 1 << 22
 
 
+def _scale_quats(s, lo=0.6, hi=1.5, seed=5):
+    """Non-unit quaternions: the kernels (like the reference, helpers.cuh:166-185) build R from the quaternion as given,
+    so its columns shrink and skew; the model normalises (gstex.py:1062) but the drop-in API does not promise it."""
+    g = torch.Generator().manual_seed(seed)
+    s["quats"] = (s["quats"] * (lo + (hi - lo) * torch.rand(s["quats"].shape[0], 1, generator=g))).contiguous()
+    return s
+
+
 @pytest.mark.parametrize("cfg", [dict(name="cfg2", n=30000, size=320), dict(name="cfg5", n=250000, size=400),
-                                 dict(name="cfg1", n=3000, size=200)], ids=lambda c: c["name"])
+                                 dict(name="cfg1", n=3000, size=200), dict(name="cfg2", n=30000, size=320, nonunit=True)],
+                         ids=lambda c: c["name"] + ("-nonunit" if c.get("nonunit") else ""))
 def test_culling_never_changes_a_result(cfg, monkeypatch):
     """The support-box / live-rectangle culling of the forward is claimed to be exact: with culling
-    forced off (GSTEX_DBG bit 4: every list entry evaluated for every pixel block) every output must be
+    forced off (test hook `gstex_debug_force_nocull`: every list entry evaluated for every pixel block) every output must be
     bit-identical, the index outputs included."""
     import gstex_b200 as G
     from gstex_b200.synthetic import make_scene
 
     s = make_scene(cfg["name"], n=cfg["n"], width=cfg["size"], height=cfg["size"])
+    if cfg.get("nonunit"):
+        _scale_quats(s)
     sd = {k: (x.cuda() if isinstance(x, torch.Tensor) else x) for k, x in s.items()}
     intr = (s["fx"], s["fy"], s["cx"], s["cy"])
     H, W, bw = s["H"], s["W"], 16
@@ -253,13 +264,37 @@ def test_culling_never_changes_a_result(cfg, monkeypatch):
     args = (s["texture_info"], sd["texture_dims"], centers, extents, depths, nth, sd["colors"], sd["opacities"],
             sd["means"], sd["scales"], 1, sd["quats"], sd["uv0"], sd["umap"], sd["vmap"], sd["texture"], sd["viewmat"],
             sd["c2w"], *intr, H, W, bw, s["settings"], sd["background"])
+    from gstex_b200 import _lib
+
     culled = G.texture_gaussians(*args)
-    monkeypatch.setenv("GSTEX_DBG", "16")
-    plain = G.texture_gaussians(*args)
-    monkeypatch.delenv("GSTEX_DBG")
+    _lib.load().gstex_debug_force_nocull(1)
+    try:
+        plain = G.texture_gaussians(*args)
+    finally:
+        _lib.load().gstex_debug_force_nocull(0)
     names = ["out_img", "out_depth", "out_reg", "out_alpha", "out_texture", "out_normal"]
     for nm, a, b in zip(names, culled, plain):
         assert torch.equal(a, b), f"{nm}: {int((a != b).sum())} elements differ between culled and unculled forward"
+
+
+def test_non_unit_quaternions_match_reference_extension():
+    """Quaternions scaled by 0.6..1.5: support boxes are derived from the actual (skewed) frame, so culling stays exact
+    and every output and gradient still matches the reference's kernels."""
+    from oracle import ref_ext
+
+    C = ref_ext.load()
+    if C is None:
+        pytest.skip("oracle/_ref/gstex_ref_C.so not built (python oracle/build_ref.py)")
+    from gstex_b200.synthetic import make_scene, make_upstream_grads
+
+    s = _scale_quats(make_scene("cfg2", n=6000, width=160, height=160, texels=60000, settings=(1 << 9) | (1 << 10)))
+    v = make_upstream_grads(s)
+    ours, sd = run_ours(s, v)
+    vd = {k: x.cuda() for k, x in v.items()}
+    t = lambda k: torch.from_numpy(ours[k]).cuda()  # noqa: E731
+    ref = ref_ext.ref_forward_backward(C, sd, t("centers"), t("extents"), t("depths"), t("num_tiles_hit"), vd)
+    ref = {k: (x.detach().cpu().numpy() if isinstance(x, torch.Tensor) else x) for k, x in ref.items()}
+    compare(ours, ref, s["settings"], what="refext-nonunit:")
 
 
 def test_graft_smoke_entry():
