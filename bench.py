@@ -587,11 +587,13 @@ def main():
             if rep is not None:
                 out["parity"] = {"img_max_rel": rep["img_max_rel"], "grad_max_rel": rep["grad_max_rel"],
                                  "idx_mismatch": rep["idx_mismatch"], "bin_mismatch": rep["bin_mismatch"],
+                                 "fwd_bit_mismatch": rep["fwd_bit_mismatch"],
                                  "outliers": rep["outliers"], "exact": rep["exact"],
                                  "what": "view 0 vs the reference's own CUDA kernels on the same tensors: max |err| / tensor "
                                          "scale over the six images / nine gradients, share of elements outside 1e-5 / 1e-4, "
                                          "mismatching elements of sorted ids + tile bins + final_idx + depth_idx (idx) and of "
-                                         "depths + centers + extents + tile counts (bin), all of which must be 0"}
+                                         "depths + centers + extents + tile counts (bin), elements of the six images that are not "
+                                         "bit-identical (fwd_bit); idx, bin and fwd_bit must be 0"}
         except Exception as exc:
             out["parity"] = {"error": str(exc)[:200]}
     print(json.dumps(out))

@@ -110,15 +110,18 @@ struct TexQuery {
 
 __device__ __forceinline__ TexQuery tex_query(int h, int w, int start, float u, float v, bool bilinear) {
     TexQuery q;
-    const float tcx = (float)h * u, tcy = (float)w * v;
+    // explicit roundings: the texel coordinate is rounded before its integer part is subtracted (no fma), as compiled
+    // in the reference's forward
+    const float tcx = __fmul_rn((float)h, u), tcy = __fmul_rn((float)w, v);
     int ix = (int)tcx, iy = (int)tcy;
     const int jx = min(ix + 1, h - 1), jy = min(iy + 1, w - 1);
-    q.fx = tcx - (float)ix;
-    q.fy = tcy - (float)iy;
+    q.fx = __fsub_rn(tcx, (float)ix);
+    q.fy = __fsub_rn(tcy, (float)iy);
     ix = min(ix, h - 1);
     iy = min(iy, w - 1);
-    const float wii = (1.f - q.fx) * (1.f - q.fy), wij = (1.f - q.fx) * q.fy;
-    const float wji = q.fx * (1.f - q.fy), wjj = q.fx * q.fy;
+    const float ox = __fsub_rn(1.f, q.fx), oy = __fsub_rn(1.f, q.fy);
+    const float wii = __fmul_rn(ox, oy), wij = __fmul_rn(ox, q.fy);
+    const float wji = __fmul_rn(q.fx, oy), wjj = __fmul_rn(q.fx, q.fy);
     q.b00 = start + ix * w + iy;
     q.b01 = start + ix * w + jy;
     q.b10 = start + jx * w + iy;

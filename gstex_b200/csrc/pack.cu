@@ -126,7 +126,9 @@ __global__ void __launch_bounds__(kThreads1D) pack_records_kernel(const PackPara
     // an unrelated edit of this kernel changed the contraction of the rotation columns and moved out_texture by 1e-4 of
     // its scale: u = uv0 + umap.delta amplifies one ulp of an axis by |mean| / |splat|.)
     // columns of R(quat), helpers.cuh:166-185
-    const float a1x = __fsub_rn(1.f, __fmul_rn(2.f, __fmaf_rn(y, y, __fmul_rn(z, z))));
+    // a1x: y*y and z*z are shared with a3z and a2y in the reference's forward, so ptxas keeps both products rounded:
+    // 1 - 2 * (y*y + z*z) with a plain add (texture_forward SASS); every other entry fuses one product
+    const float a1x = __fsub_rn(1.f, __fmul_rn(2.f, __fadd_rn(__fmul_rn(y, y), __fmul_rn(z, z))));
     const float a1y = __fmul_rn(2.f, __fmaf_rn(x, y, __fmul_rn(w, z)));
     const float a1z = __fmul_rn(2.f, __fmaf_rn(x, z, -__fmul_rn(w, y)));
     const float a2x = __fmul_rn(2.f, __fmaf_rn(x, y, -__fmul_rn(w, z)));

@@ -216,8 +216,8 @@ __global__ void __launch_bounds__(kMaxTileThreads + 32, 2) texture_backward_kern
                 float3 v_diff = make_float3(0.f, 0.f, 0.f);
                 {
                     const int th = __float_as_int(r4.z), tw = __float_as_int(r4.w);
-                    const float u = clamp01(r6.w + (r6.x * e.delta.x + r6.y * e.delta.y + r6.z * e.delta.z));
-                    const float vv = clamp01(r7.w + (r7.x * e.delta.x + r7.y * e.delta.y + r7.z * e.delta.z));
+                    const float u = chart_coord(r6, e.delta);
+                    const float vv = chart_coord(r7, e.delta);
                     const TexQuery q = tex_query(th, tw, __float_as_int(r5.w), u, vv, bilinear);
                     const size_t o00 = (size_t)q.b00 * C, o01 = (size_t)q.b01 * C, o10 = (size_t)q.b10 * C, o11 = (size_t)q.b11 * C;
                     float v_u = 0.f, v_v = 0.f;

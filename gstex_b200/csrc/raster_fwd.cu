@@ -211,13 +211,14 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
                 const float* t01 = p.texture + (size_t)tq.b01 * C;
                 const float* t10 = p.texture + (size_t)tq.b10 * C;
                 const float* t11 = p.texture + (size_t)tq.b11 * C;
-                val0 = tq.w00 * __ldg(t00) + tq.w01 * __ldg(t01) + tq.w10 * __ldg(t10) + tq.w11 * __ldg(t11);
-                if (C > 1) val1 = tq.w00 * __ldg(t00 + 1) + tq.w01 * __ldg(t01 + 1) + tq.w10 * __ldg(t10 + 1) + tq.w11 * __ldg(t11 + 1);
-                if (C > 2) val2 = tq.w00 * __ldg(t00 + 2) + tq.w01 * __ldg(t01 + 2) + tq.w10 * __ldg(t10 + 2) + tq.w11 * __ldg(t11 + 2);
-                // affine texel activation (SH2RGB of the caller folded into the fetch; the weights sum to one)
-                val0 = fmaf(p.tex_scale, val0, p.tex_bias);
-                if (C > 1) val1 = fmaf(p.tex_scale, val1, p.tex_bias);
-                if (C > 2) val2 = fmaf(p.tex_scale, val2, p.tex_bias);
+                val0 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00), __ldg(t01), __ldg(t10), __ldg(t11));
+                if (C > 1) val1 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00 + 1), __ldg(t01 + 1), __ldg(t10 + 1), __ldg(t11 + 1));
+                if (C > 2) val2 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00 + 2), __ldg(t01 + 2), __ldg(t10 + 2), __ldg(t11 + 2));
+                // affine texel activation (SH2RGB of the caller folded into the fetch; the weights sum to one);
+                // (1, 0) leaves the sample bit for bit
+                val0 = __fmaf_rn(p.tex_scale, val0, p.tex_bias);
+                if (C > 1) val1 = __fmaf_rn(p.tex_scale, val1, p.tex_bias);
+                if (C > 2) val2 = __fmaf_rn(p.tex_scale, val2, p.tex_bias);
             }
             if (REC && rec_ok) {  // the m pairs are consecutive items of the unit's stream, list order
                 int new_chunk = cur_chunk;
@@ -260,9 +261,9 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
                     const int j = __ffs(low) - 1;
                     low &= low - 1u;
                     const float4 e4 = ws.h_e[(h_head + j) & (kHits - 1)];
-                    tex[0] += e4.w * e4.x;
-                    if (CMAX > 1) tex[1] += e4.w * e4.y;
-                    if (CMAX > 2) tex[2] += e4.w * e4.z;
+                    tex[0] = __fmaf_rn(e4.w, e4.x, tex[0]);
+                    if (CMAX > 1) tex[1] = __fmaf_rn(e4.w, e4.y, tex[1]);
+                    if (CMAX > 2) tex[2] = __fmaf_rn(e4.w, e4.z, tex[2]);
                 }
                 const unsigned long long wmask = (unsigned long long)window;
                 mine &= ~(sh ? ((wmask << sh) | (wmask >> (64 - sh))) : wmask);
@@ -304,7 +305,7 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
                     pe.origin = make_float3(ox, oy, oz);
                 }
                 const PairEval e = eval_pair(pe, r0, r1, r2, r3, r4, use_blur);
-                const float next_T = T * (1.f - e.alpha);
+                const float next_T = __fmul_rn(T, __fsub_rn(1.f, e.alpha));
 #ifdef GSTEX_STATS
                 {
                     const unsigned live = __ballot_sync(0xffffffffu, !done);
@@ -325,18 +326,19 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
                         done = true;  // this splat is not composited
                     } else if (!e.skip) {
                         const int idx = ws.q_idx[q];
-                        const float vis = e.alpha * T;
+                        const float vis = __fmul_rn(e.alpha, T);
                         const float4 r5 = r.q[5], r6 = r.q[6], r7 = r.q[7];
-                        rgb.x += r5.x * vis; rgb.y += r5.y * vis; rgb.z += r5.z * vis;
-                        if constexpr (VIS) {
-                            const float sgn = (pe.ray.x * r1.x + pe.ray.y * r1.y + pe.ray.z * r1.z > 0.f) ? -1.f : 1.f;
-                            nrm.x += vis * (sgn * r1.x); nrm.y += vis * (sgn * r1.y); nrm.z += vis * (sgn * r1.z);
+                        rgb.x = __fmaf_rn(vis, r5.x, rgb.x); rgb.y = __fmaf_rn(vis, r5.y, rgb.y); rgb.z = __fmaf_rn(vis, r5.z, rgb.z);
+                        if constexpr (VIS) {  // the reference tests the UNCLAMPED denominator dot(ax3, ray) > 0 (texture.cu:236-241)
+                            const bool flip = dot3_ref(r1.x, r1.y, r1.z, pe.ray.x, pe.ray.y, pe.ray.z) > 0.f;
+                            nrm.x = __fmaf_rn(vis, flip ? -r1.x : r1.x, nrm.x); nrm.y = __fmaf_rn(vis, flip ? -r1.y : r1.y, nrm.y);
+                            nrm.z = __fmaf_rn(vis, flip ? -r1.z : r1.z, nrm.z);
                         } else {
-                            nrm.x += vis * r1.x; nrm.y += vis * r1.y; nrm.z += vis * r1.z;
+                            nrm.x = __fmaf_rn(vis, r1.x, nrm.x); nrm.y = __fmaf_rn(vis, r1.y, nrm.y); nrm.z = __fmaf_rn(vis, r1.z, nrm.z);
                         }
-                        const float t_view = e.t * pix.view_depth;
-                        const float u = clamp01(r6.w + (r6.x * e.delta.x + r6.y * e.delta.y + r6.z * e.delta.z));
-                        const float v = clamp01(r7.w + (r7.x * e.delta.x + r7.y * e.delta.y + r7.z * e.delta.z));
+                        const float t_view = __fmul_rn(e.t, pix.view_depth);
+                        const float u = chart_coord(r6, e.delta);
+                        const float v = chart_coord(r7, e.delta);
                         hit = true;
                         if constexpr (kDefer) {
                             h_T = T; h_u = u; h_v = v; h_vis = vis;
@@ -350,9 +352,9 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
 #pragma unroll
                             for (int k = 0; k < CMAX; ++k) {
                                 if (k < C) {
-                                    const float val = fmaf(p.tex_scale, tq.w00 * __ldg(t00 + k) + tq.w01 * __ldg(t01 + k) +
-                                                      tq.w10 * __ldg(t10 + k) + tq.w11 * __ldg(t11 + k), p.tex_bias);
-                                    tex[k] += vis * val;
+                                    const float val = __fmaf_rn(p.tex_scale, bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00 + k),
+                                                                                          __ldg(t01 + k), __ldg(t10 + k), __ldg(t11 + k)), p.tex_bias);
+                                    tex[k] = __fmaf_rn(vis, val, tex[k]);
                                 }
                             }
                         }
@@ -360,10 +362,8 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
                             pix_depth = t_view;
                             pix_depth_index = idx;
                         }
-                        float d = e.t;
-                        if (use_ndc) d = div_normal(kFar * t_view - kFar * kNear, (kFar - kNear) * t_view);
-                        pix_reg += vis * (d * d * ts.x + ts.z - 2.f * d * ts.y);  // distortion(), helpers.cuh:259-264
-                        ts.x += vis; ts.y += vis * d; ts.z += vis * d * d;
+                        const float d = use_ndc ? ndc_depth_ref(t_view) : e.t;
+                        distortion_ref(d, vis, ts, pix_reg);  // distortion(), helpers.cuh:259-264
                         T = next_T;
                         cur_idx = idx;
                     }
@@ -431,9 +431,9 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
             p.final_Ts[id] = T;
             p.final_idx[id] = cur_idx;
             p.depth_idx[id] = pix_depth_index;
-            p.out_img[3 * id + 0] = rgb.x + T * bg0;
-            p.out_img[3 * id + 1] = rgb.y + T * bg1;
-            p.out_img[3 * id + 2] = rgb.z + T * bg2;
+            p.out_img[3 * id + 0] = __fmaf_rn(bg0, T, rgb.x);
+            p.out_img[3 * id + 1] = __fmaf_rn(bg1, T, rgb.y);
+            p.out_img[3 * id + 2] = __fmaf_rn(bg2, T, rgb.z);
             p.out_normal[3 * id + 0] = nrm.x; p.out_normal[3 * id + 1] = nrm.y; p.out_normal[3 * id + 2] = nrm.z;
             p.out_depth[id] = pix_depth;
             p.out_reg[id] = pix_reg;

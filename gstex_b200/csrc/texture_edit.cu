@@ -163,8 +163,8 @@ __global__ void __launch_bounds__(kEditWarps * 32) texture_edit_kernel(const Edi
                             const float t_view = e.t * pix.view_depth;
                             if (t_view >= lo && t_view <= hi) {
                                 const float4 r5 = rc.q[5], r6 = rc.q[6], r7 = rc.q[7];
-                                const float u = clamp01(r6.w + (r6.x * e.delta.x + r6.y * e.delta.y + r6.z * e.delta.z));
-                                const float v = clamp01(r7.w + (r7.x * e.delta.x + r7.y * e.delta.y + r7.z * e.delta.z));
+                                const float u = chart_coord(r6, e.delta);
+                                const float v = chart_coord(r7, e.delta);
                                 const TexQuery tq = tex_query(__float_as_int(r4.z), __float_as_int(r4.w),
                                                               __float_as_int(r5.w), u, v, true);
                                 const float wq[4] = {tq.w00, tq.w01, tq.w10, tq.w11};

@@ -105,7 +105,8 @@ def report(ours, ref, settings, have_grads=True):
     d2 = 1.0 if settings & (1 << 10) else max(1.0, float(ref["out_depth"].abs().max()) ** 2)
     for k in IMG_KEYS:
         rel, frac, scale = _err(ours[k], ref[k], IMG_RTOL, 2e-6 * d2 if k == "out_reg" else 0.0)
-        rep["images"][k] = {"max_rel": rel, "outside": frac, "scale": scale}
+        a, b = ours[k].contiguous().view(torch.int32), ref[k].contiguous().view(torch.int32)
+        rep["images"][k] = {"max_rel": rel, "outside": frac, "scale": scale, "bit_mismatch": int((a != b).sum())}
     if have_grads:
         for k in GRAD_KEYS:
             rel, frac, scale = _err(ours[k], ref[k], GRAD_RTOL)
@@ -114,6 +115,7 @@ def report(ours, ref, settings, have_grads=True):
     rep["grad_max_rel"] = max([x["max_rel"] for x in rep["grads"].values()] or [0.0])
     rep["idx_mismatch"] = sum(rep["exact"][k] for k in ("gaussian_ids_sorted", "tile_bins", "final_idx", "depth_idx"))
     rep["bin_mismatch"] = sum(rep["exact"][k] for k in ("depths", "centers", "extents", "num_tiles_hit"))
+    rep["fwd_bit_mismatch"] = sum(x["bit_mismatch"] for x in rep["images"].values())
     rep["outliers"] = {"img": max(x["outside"] for x in rep["images"].values()),
                        "grad": max([x["outside"] for x in rep["grads"].values()] or [0.0])}
     return rep

@@ -6,9 +6,11 @@ Every configuration the metric is quoted on -- cfg2 (300k splats, 1e7 texels, 80
 reference's unmodified kernels on the same tensors (oracle/parity.py).  The bars are BASELINE.json's north star:
   * depths (the sort key), centers, extents, tile counts, the sorted intersection list, the tile ranges and the two
     index images final_idx / depth_idx (texture.cu:837-863): BIT-EXACT;
-  * six images within 1e-5, nine gradients within 1e-4, relative to each tensor's scale; the share of elements
-    outside (pixels where a discrete decision -- alpha < 1/255, T <= 1e-4, T > 0.5, blur floor -- flips between two
-    fp32 instruction orders) is bounded by 2e-4 for images AND gradients and printed.
+  * the six images: BIT-IDENTICAL too -- the forward's per-pair arithmetic is pinned to the fused forms of the
+    reference kernel's sm_100 build (csrc/raster_common.cuh), so the bar here is stricter than the north star's 1e-5;
+  * nine gradients within 1e-4 relative to each tensor's scale (float atomics in no fixed order on both sides, and
+    the reference's backward recomputes alpha with its own instruction order); the share of elements outside is
+    bounded by 2e-4 and printed.
 Mean tile lists are 300-1200 entries here: the 16-warp sort classes, the forward's hit ring, the chunk chains of
 the pair stream and the pool sizing policy all run at the sizes the benchmark runs them.
 """
@@ -27,7 +29,8 @@ def _table(rep):
     rows = [f"I = {rep['num_intersects']}   exact mismatches: {rep['exact']}"]
     for grp in ("images", "grads"):
         for k, x in rep[grp].items():
-            rows.append(f"  {k:12s} scale {x['scale']:9.3e}  max|err|/scale {x['max_rel']:9.2e}  outside {x['outside']:8.2e}")
+            rows.append(f"  {k:12s} scale {x['scale']:9.3e}  max|err|/scale {x['max_rel']:9.2e}  outside {x['outside']:8.2e}"
+                        + (f"  bit mismatches {x['bit_mismatch']}" if "bit_mismatch" in x else ""))
     return "\n".join(rows)
 
 
@@ -45,6 +48,8 @@ def test_full_size_matches_reference_extension(name):
     print(_table(rep))
     bad = {k: n for k, n in rep["exact"].items() if n}
     assert not bad, f"{name}: not bit-exact: {bad}\n{_table(rep)}"
+    bits = {k: x["bit_mismatch"] for k, x in rep["images"].items() if x["bit_mismatch"]}
+    assert not bits, f"{name}: forward images not bit-identical to the reference kernel: {bits}\n{_table(rep)}"
     fails = [f"{k}: {x}" for grp in ("images", "grads") for k, x in rep[grp].items() if x["outside"] > MAX_OUTSIDE]
     assert not fails, f"{name}:\n" + "\n".join(fails) + "\n" + _table(rep)
     torch.cuda.empty_cache()
