@@ -50,6 +50,7 @@ _SIGNATURES = {
     "gstex_texture_backward_act": (I, [I, I, I, I, I, I] + [P] * 7 + [F] + [P] * 5 + [F, F] + [P] * 2 + [F, F, F, F, I] +
                                    [P] * 11 + [P] * 9 + [P, SZ, I, P, SZ, P, SZ, ctypes.c_longlong, I, P]),
     "gstex_grad_scratch_bytes": (SZ, [I, ctypes.c_longlong]),
+    "gstex_unpack_grads": (I, [I, I, ctypes.c_longlong, F, P, SZ, P, P, P, P, P, P, P]),
     "gstex_compute_sh_forward": (I, [I, I, I, P, P, P, P]),
     "gstex_compute_sh_backward": (I, [I, I, I, P, P, P, P]),
     "gstex_texture_sample_forward": (I, [I, I, P, P, P, P, P]),

@@ -29,6 +29,7 @@ struct StreamBwdParams {
     const uint32_t* order_valid;  // (workspace counters[1]); units are taken in that order when set
     float tex_scale;    // slope of the forward's texel activation: the unpack sweep multiplies texel gradients by it
     int scratch_clean;  // the caller vouches the scratch is as a previous call left it: skip the clear
+    int defer_unpack;   // leave the sums in the scratch (GSTEX_DEFER_UNPACK): gstex_unpack_grads moves them later
 };
 
 static inline size_t grad_scratch_bytes(int n, long long num_texels) {
@@ -37,5 +38,9 @@ static inline size_t grad_scratch_bytes(int n, long long num_texels) {
 
 // Enqueues the stream backward; the kernel returns at once when the forward flagged a pool overflow.
 int launch_backward_stream(const StreamBwdParams& p, cudaStream_t st);
+// The unpack sweep alone: adds every non-zero accumulator word to the gradient tensors and clears it.
+int launch_unpack_grads(float4* tex_acc, long long num_texels, int C, float tex_scale, float4* splat_acc, int n,
+                        float* v_texture, float* v_colors, float* v_opacity, float* v_means, float* v_scales,
+                        float* v_quats, cudaStream_t st);
 
 }  // namespace gstex

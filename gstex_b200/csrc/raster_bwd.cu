@@ -351,9 +351,11 @@ extern "C" int gstex_texture_backward_act(
         return GSTEX_E_BADARG;
     if (settings & ~GSTEX_SETTINGS_SUPPORTED) return GSTEX_E_UNSUPPORTED;
     if (channels < 1 || channels > GSTEX_MAX_CHANNELS) return GSTEX_E_UNSUPPORTED;
-    if (zero_fill < 0 || zero_fill > 7 || (zero_fill & 3) == 3) return GSTEX_E_BADARG;
+    if (zero_fill < 0 || zero_fill > 15 || (zero_fill & 3) == 3) return GSTEX_E_BADARG;
     const int scratch_clean = (zero_fill & GSTEX_SCRATCH_CLEAN) != 0;
+    const int defer_unpack = (zero_fill & GSTEX_DEFER_UNPACK) != 0;
     zero_fill &= 3;
+    if (defer_unpack && zero_fill != 2) return GSTEX_E_BADARG;  // deferring only makes sense for running sums
     if (zero_fill && (num_texels < 0 || (n > 0 && (!v_colors || !v_opacity || !v_means || !v_scales || !v_quats ||
                                                     !v_uv0 || !v_umap || !v_vmap || !v_texture))))
         return GSTEX_E_BADARG;
@@ -413,6 +415,7 @@ extern "C" int gstex_texture_backward_act(
         sp.v_colors = v_colors; sp.v_opacity = v_opacity; sp.v_means = v_means; sp.v_scales = v_scales;
         sp.v_quats = v_quats; sp.v_texture = v_texture;
         sp.n = n; sp.num_texels = num_texels; sp.scratch_clean = scratch_clean; sp.tex_scale = tex_scale;
+        sp.defer_unpack = defer_unpack;
         sp.order = ws_order(workspace, n); sp.order_valid = ws_counters(workspace) + 1;
         sp.tex_acc = reinterpret_cast<float4*>(grad_scratch); sp.splat_acc = sp.tex_acc + num_texels;
         // the unpack kernel of the stream path adds to the gradients wherever this view contributed
@@ -431,6 +434,20 @@ extern "C" int gstex_texture_backward_act(
     else launch_bwd<GSTEX_MAX_CHANNELS>(p, uv, st);
     GSTEX_LAUNCH_CHECK();
     return GSTEX_OK;
+}
+
+extern "C" int gstex_unpack_grads(int channels, int n, long long num_texels, float tex_scale, void* grad_scratch,
+                                  size_t grad_scratch_size, float* v_colors, float* v_opacity, float* v_means,
+                                  float* v_scales, float* v_quats, float* v_texture, void* stream) {
+    if (channels < 1 || channels > 3 || n < 0 || num_texels < 0) return GSTEX_E_BADARG;
+    if (n == 0 && num_texels == 0) return GSTEX_OK;
+    if (!grad_scratch || ((uintptr_t)grad_scratch & 15) || ((uintptr_t)v_quats & 15) ||
+        grad_scratch_size < grad_scratch_bytes(n, num_texels))
+        return GSTEX_E_BADARG;
+    if (!v_colors || !v_opacity || !v_means || !v_scales || !v_quats || !v_texture) return GSTEX_E_BADARG;
+    float4* tex_acc = reinterpret_cast<float4*>(grad_scratch);
+    return launch_unpack_grads(tex_acc, num_texels, channels, tex_scale, tex_acc + num_texels, n, v_texture, v_colors,
+                               v_opacity, v_means, v_scales, v_quats, (cudaStream_t)stream);
 }
 
 extern "C" int gstex_texture_backward(

@@ -384,8 +384,16 @@ int launch_backward_stream(const StreamBwdParams& p, cudaStream_t st) {
                                         (int)sizeof(StreamShared)));
     texture_backward_stream_kernel<<<blocks, kStreamWarps * 32, sizeof(StreamShared), st>>>(p);
     GSTEX_LAUNCH_CHECK();
-    unpack_grads_kernel<<<sm_count() * 8, 256, 0, st>>>(p.tex_acc, p.num_texels, p.C, p.tex_scale, p.splat_acc, p.n, p.v_texture, p.v_colors,
-                                                  p.v_opacity, p.v_means, p.v_scales, p.v_quats);
+    if (p.defer_unpack) return GSTEX_OK;  // the sums stay in the scratch until gstex_unpack_grads
+    return launch_unpack_grads(p.tex_acc, p.num_texels, p.C, p.tex_scale, p.splat_acc, p.n, p.v_texture, p.v_colors, p.v_opacity,
+                               p.v_means, p.v_scales, p.v_quats, st);
+}
+
+int launch_unpack_grads(float4* tex_acc, long long num_texels, int C, float tex_scale, float4* splat_acc, int n,
+                        float* v_texture, float* v_colors, float* v_opacity, float* v_means, float* v_scales,
+                        float* v_quats, cudaStream_t st) {
+    unpack_grads_kernel<<<sm_count() * 8, 256, 0, st>>>(tex_acc, num_texels, C, tex_scale, splat_acc, n, v_texture, v_colors,
+                                                         v_opacity, v_means, v_scales, v_quats);
     GSTEX_LAUNCH_CHECK();
     return GSTEX_OK;
 }

@@ -228,22 +228,34 @@ class GradientBucket:
 
     def zero_(self) -> None:
         """Zero every gradient and (re)attach the views as `p.grad`."""
+        from .texture import GradientTargets
+
+        GradientTargets.flush()  # sums a previous step left deferred must not leak into this one
         self.flat.zero_()
         for p, v in zip(self.params, self.views):
             if p.grad is not v:
                 p.grad = v
 
-    def register(self) -> None:
+    def register(self, defer: bool = True) -> None:
         """Let `texture_gaussians`' backward add each view's gradients straight into the bucket
-        (`texture.GradientTargets`) instead of handing them to autograd's accumulation pass."""
+        (`texture.GradientTargets`) instead of handing them to autograd's accumulation pass.  `defer`: the per-view
+        sums stay in the backward's padded accumulators and reach the bucket once per step (`allreduce` / `flush`)
+        instead of after every view."""
         from .texture import GradientTargets
 
-        GradientTargets.set(self.params, self.views)
+        GradientTargets.set(self.params, self.views, defer=defer)
+
+    def flush(self) -> None:
+        """Make the bucket hold every gradient accumulated so far (no-op unless sums are deferred)."""
+        from .texture import GradientTargets
+
+        GradientTargets.flush()
 
     def allreduce(self, world: int, group=None) -> None:
         """Sum over the ranks (no-op for one rank).  A gradient produced outside the bucket (a `p.grad` that was
         replaced by a fresh tensor) is ADDED to the bucket's slice -- which may already hold the sums the fused
         accumulation (`GradientTargets`) wrote for other views -- before the slice becomes `p.grad` again."""
+        self.flush()
         for p, v in zip(self.params, self.views):
             if p.grad is None:
                 raise ValueError("GradientBucket.allreduce: a gradient is None on this rank")

@@ -19,6 +19,7 @@ from . import _lib
 from .utils import TileBinning, bin_gaussians_to_tiles, finish_binning
 
 _SCRATCH_CLEAN = 4   # GSTEX_SCRATCH_CLEAN, include/gstex_b200.h
+_DEFER_UNPACK = 8    # GSTEX_DEFER_UNPACK
 _GRAD_SCRATCH = {}   # (device index, stream, bytes) -> all-zero gradient scratch left by the last backward
 
 SUPPORTED_SETTINGS = (1 << 2) | (1 << 8) | (1 << 9) | (1 << 10) | (1 << 15)
@@ -78,9 +79,27 @@ class GradientTargets:
     the plain behaviour."""
 
     _map = {}  # (data_ptr, shape) -> (weak reference to the registered parameter, its gradient target)
+    # `defer`: the stream backward leaves each view's sums in the padded scratch (C ABI GSTEX_DEFER_UNPACK) and
+    # `flush()` -- called by `GradientBucket.allreduce` / `zero_` -- moves them into the targets once per step, instead
+    # of one sweep over all texel accumulators per view.
+    defer = False
+    _pending = {}  # scratch key -> (scratch, C, n, T, tex_scale, the six stream-path targets)
 
     @classmethod
-    def set(cls, params, grads) -> None:
+    def flush(cls) -> None:
+        """Move the sums deferred so far into their targets (on the current stream of each scratch's device)."""
+        pend, cls._pending = cls._pending, {}
+        for key, (scratch, C, n, T, tex_scale, tg) in pend.items():
+            dev = scratch.device
+            with torch.cuda.device(dev):
+                rc = _lib.load().gstex_unpack_grads(C, n, T, tex_scale, _lib.ptr(scratch), scratch.numel(),
+                                                    *[_lib.ptr(t) for t in tg], _lib.stream_ptr(dev))
+            _lib.check(rc, "gstex_unpack_grads")
+
+    @classmethod
+    def set(cls, params, grads, defer: bool = False) -> None:
+        cls.flush()
+        cls.defer = bool(defer)
         m = {}
         for p, g in zip(params, grads):
             if g.shape != p.shape or g.dtype != torch.float32 or not g.is_contiguous() or g.device != p.device:
@@ -90,7 +109,9 @@ class GradientTargets:
 
     @classmethod
     def clear(cls) -> None:
+        cls.flush()
         cls._map = {}
+        cls.defer = False
 
     @classmethod
     def lookup(cls, tensors):
@@ -318,15 +339,28 @@ class _TextureGaussians(Function):
         # The gradient scratch leaves every backward all-zero (the unpack kernel clears what the stream kernel
         # wrote), so one buffer per (device, stream, size) is kept and its 200 MB clear paid once.  It is taken out
         # of the cache for the duration of the call: a call that raises never puts a half-written buffer back.
-        scratch, scratch_key, clean = None, None, 0
+        scratch, scratch_key, clean, defer = None, None, 0, 0
         if pairs is not None:
             nbytes = lib.gstex_grad_scratch_bytes(means.shape[0], texture.shape[0])
             scratch_key = (dev.index, torch.cuda.current_stream(dev).cuda_stream, nbytes)
+            want_defer = targets is not None and GradientTargets.defer
+            pend = GradientTargets._pending.get(scratch_key)
+            if pend is not None:
+                # The scratch of this (device, stream, size) holds deferred sums.  They may only keep accumulating for
+                # the same targets and activation slope; any other use of the scratch moves them out first.
+                mine = (v_colors, v_opacity, v_means, v_scales, v_quats, v_texture)
+                if not (want_defer and pend[4] == float(ctx.texture_affine[0]) and all(a is b for a, b in zip(pend[5], mine))):
+                    GradientTargets.flush()
+                    pend = None
             scratch = _GRAD_SCRATCH.pop(scratch_key, None)
+            if scratch is None and pend is not None:
+                scratch = pend[0]
             if scratch is None:
                 scratch = torch.empty((nbytes,), dtype=torch.uint8, device=dev)
             else:
                 clean = _SCRATCH_CLEAN
+            if want_defer:
+                defer = _DEFER_UNPACK
         with torch.cuda.device(dev):
             rc = lib.gstex_texture_backward_act(
                 int(H), int(W), int(ctx.block_width), C, means.shape[0], max(int(ctx.num_intersects), 0),
@@ -339,8 +373,12 @@ class _TextureGaussians(Function):
                 p(v_scales), p(v_quats), p(v_uv0), p(v_umap), p(v_vmap), p(v_texture), p(ws), ws.numel(), 1,
                 p(pairs), pairs.numel() if pairs is not None else 0, p(scratch),
                 scratch.numel() if scratch is not None else 0, int(texture.shape[0]),
-                (2 if targets is not None else 1) | clean, _lib.stream_ptr(dev))
+                (2 if targets is not None else 1) | clean | defer, _lib.stream_ptr(dev))
         _lib.check(rc, "gstex_texture_backward")
+        if defer:
+            GradientTargets._pending[scratch_key] = (scratch, C, means.shape[0], int(texture.shape[0]),
+                                                     float(ctx.texture_affine[0]),
+                                                     (v_colors, v_opacity, v_means, v_scales, v_quats, v_texture))
         if scratch is not None:
             if len(_GRAD_SCRATCH) >= 4:  # a handful of model sizes at most; do not hoard memory
                 _GRAD_SCRATCH.clear()

@@ -177,9 +177,21 @@ int gstex_texture_forward(int img_height, int img_width, int block_width, int ch
  * first; 0: they are zero-filled by the caller; 2: they hold running sums (a multi-view step's accumulated
  * gradients) and this view's gradients are ADDED to them -- what autograd's AccumulateGrad would do in a separate
  * pass over all nine tensors.  OR-ing in GSTEX_SCRATCH_CLEAN vouches that `grad_scratch` is exactly as an earlier
- * call of this function left it (or was zero-filled by the caller) and skips the clear of the scratch. */
+ * call of this function left it (or was zero-filled by the caller) and skips the clear of the scratch.
+ * OR-ing in GSTEX_DEFER_UNPACK (only with zero_fill = 2, multi-view steps): the stream path leaves this view's sums in
+ * `grad_scratch` instead of sweeping all T texel accumulators after every view; the scratch keeps accumulating over
+ * the views of the step (pass it back with GSTEX_SCRATCH_CLEAN) and ONE gstex_unpack_grads call at the end of the
+ * step adds the sums to the gradient tensors and hands the scratch back all-zero.  Views that fall back to the
+ * recompute kernel (pool overflow) add to the gradient tensors directly, as without the flag. */
 #define GSTEX_SCRATCH_CLEAN 4
+#define GSTEX_DEFER_UNPACK 8
 size_t gstex_grad_scratch_bytes(int n, long long num_texels);
+/* The unpack sweep on its own (see GSTEX_DEFER_UNPACK): for every non-zero accumulator word of `grad_scratch`,
+ * v_texture += tex_scale * word (channels <= 3 of each texel) / v_colors, v_opacity, v_means, v_scales.xy, v_quats +=
+ * word, and the word is cleared.  v_quats must be 16-byte aligned. */
+int gstex_unpack_grads(int channels, int n, long long num_texels, float tex_scale, void* grad_scratch,
+                       size_t grad_scratch_size, float* v_colors, float* v_opacity, float* v_means, float* v_scales,
+                       float* v_quats, float* v_texture, void* stream);
 int gstex_texture_backward(int img_height, int img_width, int block_width, int channels, int n, int num_intersects,
                            const int32_t* texture_dims, const int32_t* gaussian_ids_sorted, const int32_t* tile_bins,
                            const float* colors, const float* opacities, const float* means, const float* scales,

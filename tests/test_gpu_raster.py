@@ -303,7 +303,8 @@ def test_graft_smoke_entry():
     g.smoke()
 
 
-def test_fused_gradient_accumulation_matches_autograd():
+@pytest.mark.parametrize("defer", [False, True], ids=["unpack-per-view", "deferred-unpack"])
+def test_fused_gradient_accumulation_matches_autograd(defer, backward_path):
     """GradientTargets / GradientBucket: two views accumulated by the backward's own unpack kernel (zero_fill = 2)
     give the sums autograd's AccumulateGrad gives over the same two views (the additions are the same; the backward
     itself reduces with floating-point atomics, so two runs agree to rounding, not bit for bit)."""
@@ -312,7 +313,9 @@ def test_fused_gradient_accumulation_matches_autograd():
     from gstex_b200.synthetic import make_scene, make_upstream_grads
     from gstex_b200.texture import GradientTargets
 
-    s = make_scene("cfg2", n=20000, width=256, height=256, views=2)
+    from gstex_b200 import texture as T
+
+    s = make_scene("cfg2", n=20000, width=256, height=256, views=3)
     v = {k: x.cuda() for k, x in make_upstream_grads(s).items()}
     sd = {k: (x.cuda() if isinstance(x, torch.Tensor) else x) for k, x in s.items()}
     intr = (s["fx"], s["fy"], s["cx"], s["cy"])
@@ -326,8 +329,8 @@ def test_fused_gradient_accumulation_matches_autograd():
         if fused:
             bucket = GradientBucket(params)
             bucket.zero_()
-            bucket.register()
-        for i in range(2):
+            bucket.register(defer=defer)
+        for i in range(3):
             vm, c2w = s["viewmats"][i].cuda().contiguous(), s["c2ws"][i].cuda().contiguous()
             _, depths, centers, extents, nth = G.project_bounds(pd["means"].detach(), pd["scales"].detach(), 1,
                                                                 pd["quats"].detach(), vm, intr, H, W, bw)
@@ -338,7 +341,12 @@ def test_fused_gradient_accumulation_matches_autograd():
                                                  v["v_out_texture"], v["v_out_normal"]])
         if fused:
             assert all(p.grad is g for p, g in zip(params, bucket.views))
+            if defer and backward_path == "stream":  # the sums are still in the padded scratch, not in the bucket
+                assert len(GradientTargets._pending) == 1 and float(bucket.views[8].abs().max()) == 0.0
             bucket.allreduce(1)
+            assert not GradientTargets._pending
+            for buf in T._GRAD_SCRATCH.values():  # handed back all-zero by the one unpack sweep
+                assert int(torch.count_nonzero(buf)) == 0
         GradientTargets.clear()
         return [p.grad.clone() for p in params]
 
