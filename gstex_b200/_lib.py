@@ -23,6 +23,7 @@ _SIGNATURES = {
     "gstex_error_string": (ctypes.c_char_p, [I]),
     "gstex_launch_count": (ctypes.c_longlong, []),
     "gstex_debug_force_nocull": (I, [I]),
+    "gstex_debug_forward_variant": (I, [I]),
     "gstex_project_points": (I, [P, P, F, F, F, F, I, P, P, P]),
     "gstex_get_aabb_2d": (I, [P, P, F, P, P, F, F, F, F, I, P, P, P]),
     "gstex_get_num_tiles_hit_2d": (I, [P, P, I, I, I, I, P, P]),
@@ -97,7 +98,7 @@ class _TimedLib:
     def __getattr__(self, name):
         fn = getattr(self._cdll, name)
         if not name.startswith("gstex_") or name.endswith("_bytes") or name in ("gstex_abi_version", "gstex_error_string",
-                                                                               "gstex_launch_count", "gstex_debug_force_nocull",
+                                                                               "gstex_launch_count", "gstex_debug_force_nocull", "gstex_debug_forward_variant",
                                                                                "gstex_pair_stream_supported",
                                                                                "gstex_tile_bucket_max_list", "gstex_tile_bucket_max_tiles"):
             return fn

@@ -23,8 +23,7 @@
 #include <cstddef>
 #include <cstdlib>
 
-#include "pair_stream.cuh"
-#include "pipeline.cuh"
+#include "raster_fwd.cuh"
 
 namespace gstex {
 
@@ -34,27 +33,6 @@ __device__ unsigned long long g_fwd_stats[16];
 #else
 #define STAT_ADD(k, v)
 #endif
-
-struct FwdParams {
-    RasterGeom g;
-    int C;
-    const SplatRec* recs;
-    const float4* boxes;
-    const int32_t* ids;
-    const int2* tile_bins;
-    const float* texture;
-    const float *viewmat, *c2w, *background;
-    float fx, fy, cx, cy;
-    int settings;
-    float *out_img, *out_depth, *out_reg, *out_texture, *out_normal, *final_Ts, *out_reg_s;
-    int32_t *final_idx, *depth_idx;
-    uint32_t* unit_cursor;  // zeroed before the launch
-    const int32_t* order;   // tiles, longest list first (nullptr: natural order)
-    float tex_scale, tex_bias;  // every fetched sample is tex_scale * sample + tex_bias (1, 0: the reference's call)
-    int units_per_tile, num_units;
-    int force_nocull;  // tests (gstex_debug_force_nocull): evaluate every list entry for every unit
-    StreamView sv;  // pair stream (REC kernels only)
-};
 
 constexpr int kFwdWarps = 5;    // warps per CTA; they share nothing but the camera (4 CTAs/SM = 20 warps)
 constexpr int kFwdCtasPerSm = 4;
@@ -459,6 +437,13 @@ extern "C" int gstex_debug_fwd_stats(unsigned long long* out, int reset) {
 }
 #endif
 
+static int g_forward_variant = 0;
+extern "C" int gstex_debug_forward_variant(int v) {
+    const int old = g_forward_variant;
+    g_forward_variant = v;
+    return old;
+}
+
 extern "C" int gstex_pair_stream_supported(int channels, int n, int settings) {
     return channels >= 1 && channels <= 3 && n > 0 && n < (1 << 27) &&
            !(settings & (GSTEX_SET_UV_GRAD | GSTEX_SET_VIS_NORMALS));
@@ -537,6 +522,8 @@ extern "C" int gstex_texture_forward_act(int img_height, int img_width, int bloc
         if (!record)  // tell the backward there is nothing to read
             GSTEX_CUDA_TRY(cudaMemsetAsync(reinterpret_cast<char*>(pair_stream) + offsetof(StreamHeader, overflow), 1, 1, st));
     }
+    // training configuration (16x16 tiles, <= 3 channels, no viewer bit): the lane-dense kernel
+    if (g_forward_variant != 1 && forward_dense_supported(p)) return launch_forward_dense(p, record, st);
     // > 48 KB of shared memory: opt in (per device, cheap: done at every launch)
 #define GSTEX_FWD_LAUNCH(CM, RC, VS)                                                                                \
     do {                                                                                                            \

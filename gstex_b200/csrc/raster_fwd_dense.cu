@@ -1,0 +1,450 @@
+// raster_fwd_dense.cu -- stage (c), training configuration: LANE-DENSE textured forward compositing.
+// Replaces texture_forward (gstex_cuda/cuda/csrc/texture.cu:11-329) for 16x16 tiles, <= 3 texture channels and no
+// viewer bits; raster_fwd.cu keeps the general kernel (other block widths, more channels, settings bit 15).  sm_100a.
+//
+// The general kernel evaluates every surviving splat of a warp's 8x4 pixel block on all 32 lanes, although on
+// average only ~10 of the 32 pixels lie inside the splat's support box and ~6 contribute: it was issue-bound on
+// instructions spent on lanes that could not contribute.  alpha does not depend on the transmittance -- only the
+// blend does -- so here the evaluation is PAIR-parallel, like the texture fetch already was:
+//   phase A  the (survivor, pixel-inside-its-support-box) pairs of a staged batch are enumerated densely over the
+//            lanes (prefix sum of the box-rectangle areas; a lane finds its survivor with one ballot, one
+//            REDUX.OR and one shuffle) and evaluated with eval_pair; pairs with alpha >= 1/255 are compacted into
+//            a per-warp ring, in (list position, pixel) order, with everything the blend needs (alpha, depth
+//            terms, chart coordinates);
+//   group    32 ring entries at a time: (i) lane-dense bilinear fetch, (ii) every pixel lane learns which entries
+//            are its own (five ballots), (iii) walks only those, front to back -- transmittance, termination,
+//            colour / normal / texture / median depth / distortion sums, in list order, so the sums are the
+//            reference's bit for bit -- and (iv) the composited entries are appended lane-densely to the pair
+//            stream the backward reads.
+// Exactness of the culling: a dropped pair has alpha < 1/255 and is skipped by the reference too (texture.cu:213);
+// it could only END a pixel whose transmittance lies in (1e-4, 1e-4 / (1 - 1/255)] (next_T <= 1e-4 is tested before
+// `skip`, texture.cu:216-221).  A pixel entering that window is SUSPENDED at that list position; once the warp's
+// other pixels are finished the suspended ones are resumed one list entry at a time with nothing dropped.
+#include "raster_fwd.cuh"
+
+namespace gstex {
+
+constexpr int kDWarps = 5;       // warps per CTA (they share only the camera)
+constexpr int kDCtasPerSm = 4;
+constexpr int kDBatch = 16;      // survivors per record stage (one 128-byte TMA bulk copy each)
+constexpr int kDQueue = 64;      // survivor ring: batch being evaluated + batch in flight + one culling round
+constexpr int kDRing = 64;       // pair ring: < 32 pending + <= 32 new per phase-A step
+
+struct DenseWarpShared {
+    SplatRec rec[2][kDBatch];    // 4 KB
+    int q_gid[kDQueue];          // splat id
+    int q_idx[kDQueue];          // position in the global sorted list
+    int q_rect[kDQueue];         // support box clipped to the unit: first pixel lane | width << 5 | pixel count << 9
+    float pix[6][32];            // per pixel lane: ray xyz, pixel centre xy, view depth of the ray
+    float4 e_a[kDRing];          // (alpha, negative = skipped pair that may still end the pixel; d; t_view; slot | lane << 5)
+    float4 e_b[kDRing];          // (u, v, T in front of the pair or -1 = not composited, vis)
+    float4 e_c[kDRing];          // (sample 0..2, -)
+    uint64_t bar[2];
+};
+
+struct DenseShared {
+    DenseWarpShared w[kDWarps];
+    Camera cam;
+};
+
+// floor(i / w) for 0 <= i < 32, 1 <= w <= 8 as (i * m) >> 8
+__device__ __forceinline__ int div_magic(int w) {
+    return w == 1 ? 257 : (int)((0x21252B34415681ull >> (8 * (w - 2))) & 0xffull);
+}
+
+template <bool REC>
+__global__ void __launch_bounds__(kDWarps * 32, kDCtasPerSm) texture_forward_dense_kernel(const FwdParams p) {
+    extern __shared__ __align__(128) unsigned char dense_smem[];
+    DenseShared& sm = *reinterpret_cast<DenseShared*>(dense_smem);
+    const RasterGeom g = p.g;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    DenseWarpShared& ws = sm.w[warp];
+    load_camera(sm.cam, p.viewmat, p.c2w, p.fx, p.fy, p.cx, p.cy);
+    if (lane == 0) {
+        mbar_init(&ws.bar[0], 1);
+        mbar_init(&ws.bar[1], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    const bool use_blur = p.settings & GSTEX_SET_BLUR;
+    const bool use_ndc = p.settings & GSTEX_SET_NDC_REG;
+    const bool bilinear = !(p.settings & GSTEX_SET_NEAREST);
+    const int C = p.C;
+    const unsigned full = 0xffffffffu;
+    const unsigned lt_mask = (1u << lane) - 1u, le_mask = lt_mask | (1u << lane);
+    const float3 origin = make_float3(sm.cam.c2w[3], sm.cam.c2w[7], sm.cam.c2w[11]);
+    const float4 no_box = make_float4(1.f, 1.f, 0.f, 0.f);
+    unsigned phase = 0;  // bit b: parity to wait for on bar[b]
+    bool rec_ok = REC && (*(volatile uint32_t*)&p.sv.hdr->overflow == 0u);
+
+    while (true) {
+        int unit = 0;
+        if (lane == 0) unit = (int)atomicAdd(p.unit_cursor, 1u);
+        unit = __shfl_sync(full, unit, 0);
+        if (unit >= p.num_units) break;
+        const int tslot = unit >> 3, w = unit & 7;  // 16x16 tiles: 8 units of 8x4 pixels
+        const int tile_id = p.order ? __ldg(p.order + tslot) : tslot;
+        const int tile_x = tile_id % g.tiles_x, tile_y = tile_id / g.tiles_x;
+        const int2 range = p.tile_bins[tile_id];
+        // lane == pixel lane: x = lane & 7, y = lane >> 3 within the unit
+        const Pixel pix = make_pixel_xy(sm.cam, g, tile_x, tile_y, ((w & 1) << 3) | (lane & 7), ((w >> 1) << 2) | (lane >> 3));
+        const float UX = (float)(tile_x * 16 + ((w & 1) << 3)) + 0.5f, UY = (float)(tile_y * 16 + ((w >> 1) << 2)) + 0.5f;
+        __syncwarp();
+        ws.pix[0][lane] = pix.ray.x; ws.pix[1][lane] = pix.ray.y; ws.pix[2][lane] = pix.ray.z;
+        ws.pix[3][lane] = pix.px; ws.pix[4][lane] = pix.py; ws.pix[5][lane] = pix.view_depth;
+        __syncwarp();
+
+        // ---- per-pixel state (this lane's own pixel)
+        bool done = !pix.inside, susp = false;
+        int susp_pos = 0;
+        float T = 1.f;
+        int cur_idx = 0, pix_depth_index = -1;
+        float3 rgb = make_float3(0.f, 0.f, 0.f), nrm = make_float3(0.f, 0.f, 0.f), ts = make_float3(0.f, 0.f, 0.f);
+        float pix_depth = 0.f, pix_reg = 0.f, tex0 = 0.f, tex1 = 0.f, tex2 = 0.f;
+        unsigned done_mask = __ballot_sync(full, done);  // pixels that take no more pairs (finished or suspended)
+        // live rectangle (unit-local pixel indices, inclusive) the support boxes are clipped to
+        int lx0 = 0, lx1 = 7, ly0 = 0, ly1 = 3;
+        auto shrink_live_rect = [&]() {
+            const unsigned live = ~done_mask;
+            const unsigned cols = (live | (live >> 8) | (live >> 16) | (live >> 24)) & 0xffu;
+            if (cols == 0u) return;
+            lx0 = __ffs(cols) - 1; lx1 = 31 - __clz(cols);
+            ly0 = (__ffs(live) - 1) >> 3; ly1 = (31 - __clz(live)) >> 3;
+        };
+        shrink_live_rect();
+        // pair-stream cursor of this unit (REC only): current chunk, items in it, items in total
+        int cur_chunk = -1, fill = kChunkItems, cnt = 0;
+
+        // ---- list walk: cursor = next list position to test; ring indices are monotonic
+        int cursor = range.x;
+        int q_head = 0, q_issue = 0, q_tail = 0;
+        int r_head = 0, r_tail = 0;
+        int cur = 0;
+        int gid_pf, gid_pf2;
+        float4 box_pf;
+        auto prime = [&]() {  // ids two rounds ahead, support boxes one round ahead of the round being tested
+            gid_pf = (cursor + lane < range.y) ? __ldg(p.ids + cursor + lane) : -1;
+            gid_pf2 = (cursor + 32 + lane < range.y) ? __ldg(p.ids + cursor + 32 + lane) : -1;
+            box_pf = (gid_pf >= 0) ? __ldg(p.boxes + gid_pf) : no_box;
+        };
+        // Test list entries until a batch of survivors is queued (or the list ends), then start the TMA copies of the
+        // next kDBatch queued records into stage `buf`.  A survivor's support box is clipped to the rectangle of the
+        // pixels still alive: that rectangle (first pixel lane, width, pixel count) is all phase A needs to enumerate
+        // its pairs.  Returns the number of records in flight.
+        auto fill_and_issue = [&](int buf) -> int {
+            while (q_tail - q_issue < kDBatch && cursor < range.y) {
+                const int gid = gid_pf;
+                const float4 box = box_pf;
+                const int pos = cursor + lane;
+                cursor += 32;
+                gid_pf = gid_pf2;
+                gid_pf2 = (cursor + 32 + lane < range.y) ? __ldg(p.ids + cursor + 32 + lane) : -1;
+                box_pf = (gid_pf >= 0) ? __ldg(p.boxes + gid_pf) : no_box;
+                int xa = lx0, xb = lx1, ya = ly0, yb = ly1;
+                if (!p.force_nocull) {  // pixel (x, y) of the unit has its centre at (UX + x, UY + y)
+                    xa = max(xa, (int)ceilf(fmaxf(box.x - UX, -1.f)));
+                    xb = min(xb, (int)floorf(fminf(box.z - UX, 8.f)));
+                    ya = max(ya, (int)ceilf(fmaxf(box.y - UY, -1.f)));
+                    yb = min(yb, (int)floorf(fminf(box.w - UY, 4.f)));
+                }
+                const bool hit = gid >= 0 && xa <= xb && ya <= yb;
+                const unsigned m = __ballot_sync(full, hit);
+                if (hit) {
+                    const int slot = (q_tail + __popc(m & lt_mask)) & (kDQueue - 1);
+                    const int wd = xb - xa + 1;
+                    ws.q_gid[slot] = gid;
+                    ws.q_idx[slot] = pos;
+                    ws.q_rect[slot] = (ya * 8 + xa) | (wd << 5) | ((wd * (yb - ya + 1)) << 9);
+                }
+                q_tail += __popc(m);
+            }
+            __syncwarp();
+            const int n_rec = min(q_tail - q_issue, kDBatch);
+            if (n_rec > 0) {
+                if (lane == 0) mbar_arrive_expect_tx(&ws.bar[buf], (uint32_t)n_rec * (uint32_t)sizeof(SplatRec));
+                if (lane < n_rec)
+                    bulk_copy_g2s(&ws.rec[buf][lane], p.recs + ws.q_gid[(q_issue + lane) & (kDQueue - 1)], sizeof(SplatRec),
+                                  &ws.bar[buf]);
+                q_issue += n_rec;
+            }
+            return n_rec;
+        };
+
+        // ---- one group of m <= 32 ring entries (oldest first).  `slow`: entries of suspended pixels (resume path).
+        auto process_group = [&](const int m, const bool slow) {
+            __syncwarp();
+            const int hs = (r_head + lane) & (kDRing - 1);
+            const bool valid = lane < m;
+            float4 ea = make_float4(0.f, 0.f, 0.f, 0.f), eb = ea;
+            if (valid) { ea = ws.e_a[hs]; eb = ws.e_b[hs]; }
+            const int code = __float_as_int(ea.w);
+            const int es = code & 31, epl = (code >> 5) & 31;
+            // (i) lane-dense bilinear fetch of the pairs that can still be composited
+            float val0 = 0.f, val1 = 0.f, val2 = 0.f;
+            if (valid && ea.x > 0.f && (slow || !((done_mask >> epl) & 1u))) {
+                const SplatRec& rr = ws.rec[cur][es];
+                const float4 r4 = rr.q[4];
+                const int start = __float_as_int(rr.q[5].w);
+                const TexQuery tq = tex_query(__float_as_int(r4.z), __float_as_int(r4.w), start, eb.x, eb.y, bilinear);
+                const float* t00 = p.texture + (size_t)tq.b00 * C;
+                const float* t01 = p.texture + (size_t)tq.b01 * C;
+                const float* t10 = p.texture + (size_t)tq.b10 * C;
+                const float* t11 = p.texture + (size_t)tq.b11 * C;
+                val0 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00), __ldg(t01), __ldg(t10), __ldg(t11));
+                if (C > 1) val1 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00 + 1), __ldg(t01 + 1), __ldg(t10 + 1), __ldg(t11 + 1));
+                if (C > 2) val2 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00 + 2), __ldg(t01 + 2), __ldg(t10 + 2), __ldg(t11 + 2));
+                // affine texel activation (SH2RGB of the caller folded into the fetch); (1, 0) leaves the sample bit for bit
+                val0 = __fmaf_rn(p.tex_scale, val0, p.tex_bias);
+                if (C > 1) val1 = __fmaf_rn(p.tex_scale, val1, p.tex_bias);
+                if (C > 2) val2 = __fmaf_rn(p.tex_scale, val2, p.tex_bias);
+            }
+            if (valid) ws.e_c[hs] = make_float4(val0, val1, val2, 0.f);
+            // (ii) which entries belong to this lane's pixel
+            unsigned own = __ballot_sync(full, valid);
+#pragma unroll
+            for (int bit = 0; bit < 5; ++bit) {
+                const unsigned bal = __ballot_sync(full, valid && ((epl >> bit) & 1));
+                own &= ((lane >> bit) & 1) ? bal : ~bal;
+            }
+            __syncwarp();
+            // (iii) owner walk, list order
+            while (own) {
+                const int j = __ffs(own) - 1;
+                own &= own - 1u;
+                if (done || (susp && !slow)) break;  // nothing further can change this pixel in this group
+                const int slot = (r_head + j) & (kDRing - 1);
+                const float4 a4 = ws.e_a[slot];
+                const float a = a4.x;
+                const float next_T = __fmul_rn(T, __fsub_rn(1.f, fabsf(a)));
+                if (next_T <= 1e-4f) { done = true; break; }  // this splat is not composited (texture.cu:216-221)
+                if (a > 0.f) {
+                    const int s = __float_as_int(a4.w) & 31;
+                    const SplatRec& r = ws.rec[cur][s];
+                    const float4 r1 = r.q[1], r5 = r.q[5], c4 = ws.e_c[slot];
+                    const int idx = ws.q_idx[(q_head + s) & (kDQueue - 1)];
+                    const float vis = __fmul_rn(a, T);
+                    rgb.x = __fmaf_rn(vis, r5.x, rgb.x); rgb.y = __fmaf_rn(vis, r5.y, rgb.y); rgb.z = __fmaf_rn(vis, r5.z, rgb.z);
+                    nrm.x = __fmaf_rn(vis, r1.x, nrm.x); nrm.y = __fmaf_rn(vis, r1.y, nrm.y); nrm.z = __fmaf_rn(vis, r1.z, nrm.z);
+                    tex0 = __fmaf_rn(vis, c4.x, tex0); tex1 = __fmaf_rn(vis, c4.y, tex1); tex2 = __fmaf_rn(vis, c4.z, tex2);
+                    if (T > 0.5f) {  // median depth, texture.cu:286-291
+                        pix_depth = a4.z;
+                        pix_depth_index = idx;
+                    }
+                    distortion_ref(a4.y, vis, ts, pix_reg);  // distortion(), helpers.cuh:259-264
+                    ws.e_b[slot].z = T;  // composited: a pair-stream item with this transmittance in front of it
+                    T = next_T;
+                    cur_idx = idx;
+                    // From here a pair with alpha < 1/255 -- which phase A drops -- could end this pixel: suspend it
+                    // at this list position; it is resumed with nothing dropped once the others are finished.
+                    if (!slow && T <= 1.0041e-4f) { susp = true; susp_pos = idx; break; }
+                }
+            }
+            __syncwarp();
+            // (iv) the composited entries, in ring order, become consecutive items of the unit's pair stream
+            if (REC && rec_ok) {
+                const float Tb = valid ? ws.e_b[hs].z : -1.f;
+                const bool alive = Tb >= 0.f;
+                const unsigned am = __ballot_sync(full, alive);
+                const int na = __popc(am);
+                if (na > 0) {
+                    int new_chunk = cur_chunk;
+                    if (fill + na > kChunkItems) {
+                        int c = 0;
+                        if (lane == 0) c = (int)atomicAdd(&p.sv.hdr->next_chunk, 1u);
+                        c = __shfl_sync(full, c, 0);
+                        if (c >= p.sv.num_chunks) {
+                            if (lane == 0) p.sv.hdr->overflow = 1u;
+                            rec_ok = false;
+                        } else {
+                            if (lane == 0) p.sv.chunk_prev[c] = cur_chunk;
+                            new_chunk = c;
+                        }
+                    }
+                    if (rec_ok) {
+                        if (alive) {
+                            int pos = fill + __popc(am & lt_mask);
+                            int ch = cur_chunk;
+                            if (pos >= kChunkItems) { pos -= kChunkItems; ch = new_chunk; }
+                            float4* dst = reinterpret_cast<float4*>(p.sv.items + (size_t)ch * kChunkItems + pos);
+                            const int q = (q_head + es) & (kDQueue - 1);
+                            const uint32_t gl = ((uint32_t)ws.q_gid[q] << 5) | (uint32_t)epl;
+                            dst[0] = make_float4(__uint_as_float(gl), __int_as_float(ws.q_idx[q]), Tb, eb.x);
+                            dst[1] = make_float4(eb.y, val0, val1, val2);
+                        }
+                        fill += na;
+                        if (fill > kChunkItems) { fill -= kChunkItems; cur_chunk = new_chunk; }
+                        cnt += na;
+                    }
+                }
+            }
+            done_mask = __ballot_sync(full, done || susp);
+            r_head += m;
+            __syncwarp();
+        };
+
+        // ---- evaluate one pair per lane and append the ones that matter to the ring.
+        // s: record slot of the survivor in the current stage, pl: pixel lane, active: this lane holds a pair.
+        // keep_all (resume path): nothing is dropped -- a pair with alpha < 1/255 is kept as a skipped pair.
+        auto eval_and_push = [&](const int s, const int pl, const bool active, const bool keep_all) {
+            const SplatRec& r = ws.rec[cur][s];
+            const float4 r0 = r.q[0], r1 = r.q[1], r2 = r.q[2], r3 = r.q[3], r4 = r.q[4];
+            Pixel pe;
+            pe.origin = origin;
+            pe.ray = make_float3(ws.pix[0][pl], ws.pix[1][pl], ws.pix[2][pl]);
+            pe.px = ws.pix[3][pl]; pe.py = ws.pix[4][pl];
+            const PairEval e = eval_pair(pe, r0, r1, r2, r3, r4, use_blur);
+            const bool small = e.alpha < 1.f / 255.f;
+            const bool keep = active && (keep_all || !small);
+            const unsigned km = __ballot_sync(full, keep);
+            if (keep) {
+                const bool skip = small || (e.t < kNear) || (e.t > kFar);
+                float u = 0.f, v = 0.f, t_view = 0.f, d = 0.f;
+                if (!skip) {
+                    t_view = __fmul_rn(e.t, ws.pix[5][pl]);
+                    u = chart_coord(r.q[6], e.delta);
+                    v = chart_coord(r.q[7], e.delta);
+                    d = use_ndc ? ndc_depth_ref(t_view) : e.t;
+                }
+                const int slot = (r_tail + __popc(km & lt_mask)) & (kDRing - 1);
+                ws.e_a[slot] = make_float4(skip ? -e.alpha : e.alpha, d, t_view, __int_as_float(s | (pl << 5)));
+                ws.e_b[slot] = make_float4(u, v, -1.f, 0.f);
+            }
+            r_tail += __popc(km);
+        };
+
+        // ---- phase A over the n survivors staged in rec[cur]
+        auto phase_a = [&](const int n) {
+            int rect = 0, cnt_s = 0;
+            if (lane < n) {
+                rect = ws.q_rect[(q_head + lane) & (kDQueue - 1)];
+                cnt_s = rect >> 9;
+            }
+            int end_s = cnt_s;
+#pragma unroll
+            for (int o = 1; o < kDBatch; o <<= 1) {
+                const int up = __shfl_up_sync(full, end_s, o);
+                if (lane >= o) end_s += up;
+            }
+            const int total = __shfl_sync(full, end_s, kDBatch - 1);
+            const int off_s = end_s - cnt_s;
+            const int wd = (rect >> 5) & 15;
+            // offset | first pixel lane << 10 | width << 15 | division magic << 19
+            const int word = off_s | ((rect & 31) << 10) | (wd << 15) | (div_magic(max(wd, 1)) << 19);
+            for (int base = 0; base < total; base += 32) {
+                const int j = base + lane;
+                const bool in_range = j < total;
+                const bool starts_here = lane < n && off_s >= base && off_s < base + 32;
+                const unsigned startmask = __reduce_or_sync(full, starts_here ? (1u << (off_s - base)) : 0u);
+                const int nbefore = __popc(__ballot_sync(full, lane < n && off_s < base));
+                const int s = min(max(nbefore + __popc(startmask & le_mask) - 1, 0), n - 1);
+                const int wv = __shfl_sync(full, word, s);
+                const int i = j - (wv & 1023);
+                const int yy = (i * ((wv >> 19) & 511)) >> 8;
+                int pl = ((wv >> 10) & 31) + yy * 8 + (i - yy * ((wv >> 15) & 15));
+                const bool active = in_range && pl >= 0 && pl < 32 && !((done_mask >> (pl & 31)) & 1u);
+                pl = active ? pl : 0;
+                eval_and_push(s, pl, active, false);
+                if (r_tail - r_head >= 32) {
+                    process_group(32, false);
+                    if (done_mask == full) return;
+                }
+            }
+        };
+
+        // ---- main walk: cull -> stage (TMA) -> phase A -> groups, one batch in flight behind the one evaluated
+        int n_cur = 0;
+        if (done_mask != full) {
+            prime();
+            n_cur = fill_and_issue(cur);
+        }
+        while (n_cur > 0) {
+            const int n_next = fill_and_issue(cur ^ 1);  // next batch in flight while this one is evaluated
+            mbar_wait(&ws.bar[cur], (phase >> cur) & 1u);
+            phase ^= 1u << cur;
+            phase_a(n_cur);
+            // the ring's entries point into this batch's record stage: finish them before it is refilled
+            while (r_tail != r_head && done_mask != full) process_group(min(32, r_tail - r_head), false);
+            r_head = r_tail;
+            if (done_mask == full) {
+                if (n_next > 0) {  // drain the copies in flight before their stage and barrier are reused
+                    mbar_wait(&ws.bar[cur ^ 1], (phase >> (cur ^ 1)) & 1u);
+                    phase ^= 1u << (cur ^ 1);
+                }
+                break;
+            }
+            q_head += n_cur;
+            n_cur = n_next;
+            cur ^= 1;
+            shrink_live_rect();
+        }
+
+        // ---- resume path: suspended pixels (transmittance within 255/254 of the termination threshold) re-walk the
+        // list from the entry after the one that suspended them, one entry at a time, every lane its own pixel and
+        // NOTHING dropped -- the reference's own loop, restricted to those pixels.  Rare: ~1 pixel in 500.
+        if (__any_sync(full, susp && !done)) {
+            __syncwarp();
+            q_head = 0;
+            int pos = __reduce_min_sync(full, (susp && !done) ? susp_pos + 1 : 0x7fffffff);
+            for (; pos < range.y; ++pos) {
+                const bool active = susp && !done && pos > susp_pos;
+                if (!__any_sync(full, susp && !done)) break;
+                if (!__any_sync(full, active)) continue;
+                const int gid = __ldg(p.ids + pos);
+                if (lane < 8) ws.rec[cur][0].q[lane] = __ldg(&p.recs[gid].q[lane]);
+                if (lane == 0) { ws.q_gid[0] = gid; ws.q_idx[0] = pos; }
+                __syncwarp();
+                eval_and_push(0, lane, active, true);
+                process_group(r_tail - r_head, true);
+            }
+            // the record stage was written with ordinary stores here; the next unit refills it through the async proxy
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        }
+
+        if (REC) {
+            const int unit0 = tile_id * kUnitsPerTile;
+            if (lane == 0) p.sv.units[unit0 + w] = make_int2(cur_chunk, rec_ok ? cnt : 0);
+        }
+        if (pix.inside) {
+            const float bg0 = __ldg(p.background), bg1 = __ldg(p.background + 1), bg2 = __ldg(p.background + 2);
+            const int id = pix.pix_id;
+            p.final_Ts[id] = T;
+            p.final_idx[id] = cur_idx;
+            p.depth_idx[id] = pix_depth_index;
+            p.out_img[3 * id + 0] = __fmaf_rn(bg0, T, rgb.x);
+            p.out_img[3 * id + 1] = __fmaf_rn(bg1, T, rgb.y);
+            p.out_img[3 * id + 2] = __fmaf_rn(bg2, T, rgb.z);
+            p.out_normal[3 * id + 0] = nrm.x; p.out_normal[3 * id + 1] = nrm.y; p.out_normal[3 * id + 2] = nrm.z;
+            p.out_depth[id] = pix_depth;
+            p.out_reg[id] = pix_reg;
+            p.out_reg_s[3 * id + 0] = ts.x; p.out_reg_s[3 * id + 1] = ts.y; p.out_reg_s[3 * id + 2] = ts.z;
+            p.out_texture[(size_t)C * id] = tex0;
+            if (C > 1) p.out_texture[(size_t)C * id + 1] = tex1;
+            if (C > 2) p.out_texture[(size_t)C * id + 2] = tex2;
+        }
+        __syncwarp();
+    }
+}
+
+bool forward_dense_supported(const FwdParams& p) {
+    return p.g.bw == 16 && p.C >= 1 && p.C <= 3 && !(p.settings & GSTEX_SET_VIS_NORMALS);
+}
+
+int launch_forward_dense(const FwdParams& p, bool record, cudaStream_t st) {
+    int grid = sm_count() * kDCtasPerSm;
+    if (grid > (p.num_units + kDWarps - 1) / kDWarps) grid = (p.num_units + kDWarps - 1) / kDWarps;
+    if (grid < 1) grid = 1;
+    const int threads = kDWarps * 32;
+    if (record) {
+        GSTEX_CUDA_TRY(cudaFuncSetAttribute(texture_forward_dense_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)sizeof(DenseShared)));
+        texture_forward_dense_kernel<true><<<grid, threads, sizeof(DenseShared), st>>>(p);
+    } else {
+        GSTEX_CUDA_TRY(cudaFuncSetAttribute(texture_forward_dense_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)sizeof(DenseShared)));
+        texture_forward_dense_kernel<false><<<grid, threads, sizeof(DenseShared), st>>>(p);
+    }
+    GSTEX_LAUNCH_CHECK();
+    return GSTEX_OK;
+}
+
+}  // namespace gstex

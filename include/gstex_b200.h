@@ -55,6 +55,10 @@ long long gstex_launch_count(void);
  * block instead of culling by support box, so that tests can assert culling never changes a result.  Process-wide;
  * returns the previous value.  Not for production use (no environment variable is ever read by this library). */
 int gstex_debug_force_nocull(int on);
+/* TEST HOOK: 1 forces the general forward kernel (raster_fwd.cu) where the lane-dense training kernel
+ * (raster_fwd_dense.cu) would run, 0 restores the automatic choice; the two must agree bit for bit.  Returns the
+ * previous value. */
+int gstex_debug_forward_variant(int v);
 
 /* ---- stage (a): per-splat projection, bounds, tile count ------------------------------------- */
 
