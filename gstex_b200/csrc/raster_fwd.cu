@@ -509,6 +509,7 @@ extern "C" int gstex_texture_forward_act(int img_height, int img_width, int bloc
     p.units_per_tile = p.g.threads / 32;
     p.num_units = p.g.tiles_x * p.g.tiles_y * p.units_per_tile;
     p.force_nocull = force_nocull_flag();
+    p.dbg = g_forward_variant;
     // persistent grid: enough CTAs to fill every SM at the kernels' occupancy, never more than there are units
     int grid = sm_count() * kFwdCtasPerSm;
     if (grid > (p.num_units + kFwdWarps - 1) / kFwdWarps) grid = (p.num_units + kFwdWarps - 1) / kFwdWarps;

@@ -24,6 +24,7 @@ struct FwdParams {
     float tex_scale, tex_bias;  // every fetched sample is tex_scale * sample + tex_bias (1, 0: the reference's call)
     int units_per_tile, num_units;
     int force_nocull;  // tests (gstex_debug_force_nocull): evaluate every list entry for every unit
+    int dbg;           // tests (gstex_debug_forward_variant)
     StreamView sv;  // pair stream (REC kernels only)
 };
 

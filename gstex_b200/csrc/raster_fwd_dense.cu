@@ -20,6 +20,8 @@
 // it could only END a pixel whose transmittance lies in (1e-4, 1e-4 / (1 - 1/255)] (next_T <= 1e-4 is tested before
 // `skip`, texture.cu:216-221).  A pixel entering that window is SUSPENDED at that list position; once the warp's
 // other pixels are finished the suspended ones are resumed one list entry at a time with nothing dropped.
+#include <cstdio>
+
 #include "raster_fwd.cuh"
 
 namespace gstex {
@@ -36,9 +38,9 @@ struct DenseWarpShared {
     int q_idx[kDQueue];          // position in the global sorted list
     int q_rect[kDQueue];         // support box clipped to the unit: first pixel lane | width << 5 | pixel count << 9
     float pix[6][32];            // per pixel lane: ray xyz, pixel centre xy, view depth of the ray
-    float4 e_a[kDRing];          // (alpha, negative = skipped pair that may still end the pixel; d; t_view; slot | lane << 5)
-    float4 e_b[kDRing];          // (u, v, T in front of the pair or -1 = not composited, vis)
-    float4 e_c[kDRing];          // (sample 0..2, -)
+    float4 e_a[kDRing];          // (alpha, negative = skipped pair that may still end the pixel; t; delta.x; delta.y)
+    float4 e_b[kDRing];          // (delta.z; record slot | pixel lane << 5; T in front of the pair or -1 = not composited; t_view)
+    float4 e_c[kDRing];          // (sample 0..2, depth term d of the distortion sum)
     uint64_t bar[2];
 };
 
@@ -131,7 +133,9 @@ __global__ void __launch_bounds__(kDWarps * 32, kDCtasPerSm) texture_forward_den
         // next kDBatch queued records into stage `buf`.  A survivor's support box is clipped to the rectangle of the
         // pixels still alive: that rectangle (first pixel lane, width, pixel count) is all phase A needs to enumerate
         // its pairs.  Returns the number of records in flight.
+        bool slow = false;  // resume path (see ADVANCE)
         auto fill_and_issue = [&](int buf) -> int {
+            const bool nocull = p.force_nocull != 0 || slow;
             while (q_tail - q_issue < kDBatch && cursor < range.y) {
                 const int gid = gid_pf;
                 const float4 box = box_pf;
@@ -141,7 +145,7 @@ __global__ void __launch_bounds__(kDWarps * 32, kDCtasPerSm) texture_forward_den
                 gid_pf2 = (cursor + 32 + lane < range.y) ? __ldg(p.ids + cursor + 32 + lane) : -1;
                 box_pf = (gid_pf >= 0) ? __ldg(p.boxes + gid_pf) : no_box;
                 int xa = lx0, xb = lx1, ya = ly0, yb = ly1;
-                if (!p.force_nocull) {  // pixel (x, y) of the unit has its centre at (UX + x, UY + y)
+                if (!nocull) {  // pixel (x, y) of the unit has its centre at (UX + x, UY + y)
                     xa = max(xa, (int)ceilf(fmaxf(box.x - UX, -1.f)));
                     xb = min(xb, (int)floorf(fminf(box.z - UX, 8.f)));
                     ya = max(ya, (int)ceilf(fmaxf(box.y - UY, -1.f)));
@@ -170,234 +174,256 @@ __global__ void __launch_bounds__(kDWarps * 32, kDCtasPerSm) texture_forward_den
             return n_rec;
         };
 
-        // ---- one group of m <= 32 ring entries (oldest first).  `slow`: entries of suspended pixels (resume path).
-        auto process_group = [&](const int m, const bool slow) {
-            __syncwarp();
-            const int hs = (r_head + lane) & (kDRing - 1);
-            const bool valid = lane < m;
-            float4 ea = make_float4(0.f, 0.f, 0.f, 0.f), eb = ea;
-            if (valid) { ea = ws.e_a[hs]; eb = ws.e_b[hs]; }
-            const int code = __float_as_int(ea.w);
-            const int es = code & 31, epl = (code >> 5) & 31;
-            // (i) lane-dense bilinear fetch of the pairs that can still be composited
-            float val0 = 0.f, val1 = 0.f, val2 = 0.f;
-            if (valid && ea.x > 0.f && (slow || !((done_mask >> epl) & 1u))) {
-                const SplatRec& rr = ws.rec[cur][es];
-                const float4 r4 = rr.q[4];
-                const int start = __float_as_int(rr.q[5].w);
-                const TexQuery tq = tex_query(__float_as_int(r4.z), __float_as_int(r4.w), start, eb.x, eb.y, bilinear);
-                const float* t00 = p.texture + (size_t)tq.b00 * C;
-                const float* t01 = p.texture + (size_t)tq.b01 * C;
-                const float* t10 = p.texture + (size_t)tq.b10 * C;
-                const float* t11 = p.texture + (size_t)tq.b11 * C;
-                val0 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00), __ldg(t01), __ldg(t10), __ldg(t11));
-                if (C > 1) val1 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00 + 1), __ldg(t01 + 1), __ldg(t10 + 1), __ldg(t11 + 1));
-                if (C > 2) val2 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00 + 2), __ldg(t01 + 2), __ldg(t10 + 2), __ldg(t11 + 2));
-                // affine texel activation (SH2RGB of the caller folded into the fetch); (1, 0) leaves the sample bit for bit
-                val0 = __fmaf_rn(p.tex_scale, val0, p.tex_bias);
-                if (C > 1) val1 = __fmaf_rn(p.tex_scale, val1, p.tex_bias);
-                if (C > 2) val2 = __fmaf_rn(p.tex_scale, val2, p.tex_bias);
-            }
-            if (valid) ws.e_c[hs] = make_float4(val0, val1, val2, 0.f);
-            // (ii) which entries belong to this lane's pixel
-            unsigned own = __ballot_sync(full, valid);
-#pragma unroll
-            for (int bit = 0; bit < 5; ++bit) {
-                const unsigned bal = __ballot_sync(full, valid && ((epl >> bit) & 1));
-                own &= ((lane >> bit) & 1) ? bal : ~bal;
-            }
-            __syncwarp();
-            // (iii) owner walk, list order
-            while (own) {
-                const int j = __ffs(own) - 1;
-                own &= own - 1u;
-                if (done || (susp && !slow)) break;  // nothing further can change this pixel in this group
-                const int slot = (r_head + j) & (kDRing - 1);
-                const float4 a4 = ws.e_a[slot];
-                const float a = a4.x;
-                const float next_T = __fmul_rn(T, __fsub_rn(1.f, fabsf(a)));
-                if (next_T <= 1e-4f) { done = true; break; }  // this splat is not composited (texture.cu:216-221)
-                if (a > 0.f) {
-                    const int s = __float_as_int(a4.w) & 31;
-                    const SplatRec& r = ws.rec[cur][s];
-                    const float4 r1 = r.q[1], r5 = r.q[5], c4 = ws.e_c[slot];
-                    const int idx = ws.q_idx[(q_head + s) & (kDQueue - 1)];
-                    const float vis = __fmul_rn(a, T);
-                    rgb.x = __fmaf_rn(vis, r5.x, rgb.x); rgb.y = __fmaf_rn(vis, r5.y, rgb.y); rgb.z = __fmaf_rn(vis, r5.z, rgb.z);
-                    nrm.x = __fmaf_rn(vis, r1.x, nrm.x); nrm.y = __fmaf_rn(vis, r1.y, nrm.y); nrm.z = __fmaf_rn(vis, r1.z, nrm.z);
-                    tex0 = __fmaf_rn(vis, c4.x, tex0); tex1 = __fmaf_rn(vis, c4.y, tex1); tex2 = __fmaf_rn(vis, c4.z, tex2);
-                    if (T > 0.5f) {  // median depth, texture.cu:286-291
-                        pix_depth = a4.z;
-                        pix_depth_index = idx;
-                    }
-                    distortion_ref(a4.y, vis, ts, pix_reg);  // distortion(), helpers.cuh:259-264
-                    ws.e_b[slot].z = T;  // composited: a pair-stream item with this transmittance in front of it
-                    T = next_T;
-                    cur_idx = idx;
-                    // From here a pair with alpha < 1/255 -- which phase A drops -- could end this pixel: suspend it
-                    // at this list position; it is resumed with nothing dropped once the others are finished.
-                    if (!slow && T <= 1.0041e-4f) { susp = true; susp_pos = idx; break; }
-                }
-            }
-            __syncwarp();
-            // (iv) the composited entries, in ring order, become consecutive items of the unit's pair stream
-            if (REC && rec_ok) {
-                const float Tb = valid ? ws.e_b[hs].z : -1.f;
-                const bool alive = Tb >= 0.f;
-                const unsigned am = __ballot_sync(full, alive);
-                const int na = __popc(am);
-                if (na > 0) {
-                    int new_chunk = cur_chunk;
-                    if (fill + na > kChunkItems) {
-                        int c = 0;
-                        if (lane == 0) c = (int)atomicAdd(&p.sv.hdr->next_chunk, 1u);
-                        c = __shfl_sync(full, c, 0);
-                        if (c >= p.sv.num_chunks) {
-                            if (lane == 0) p.sv.hdr->overflow = 1u;
-                            rec_ok = false;
-                        } else {
-                            if (lane == 0) p.sv.chunk_prev[c] = cur_chunk;
-                            new_chunk = c;
-                        }
-                    }
-                    if (rec_ok) {
-                        if (alive) {
-                            int pos = fill + __popc(am & lt_mask);
-                            int ch = cur_chunk;
-                            if (pos >= kChunkItems) { pos -= kChunkItems; ch = new_chunk; }
-                            float4* dst = reinterpret_cast<float4*>(p.sv.items + (size_t)ch * kChunkItems + pos);
-                            const int q = (q_head + es) & (kDQueue - 1);
-                            const uint32_t gl = ((uint32_t)ws.q_gid[q] << 5) | (uint32_t)epl;
-                            dst[0] = make_float4(__uint_as_float(gl), __int_as_float(ws.q_idx[q]), Tb, eb.x);
-                            dst[1] = make_float4(eb.y, val0, val1, val2);
-                        }
-                        fill += na;
-                        if (fill > kChunkItems) { fill -= kChunkItems; cur_chunk = new_chunk; }
-                        cnt += na;
-                    }
-                }
-            }
-            done_mask = __ballot_sync(full, done || susp);
-            r_head += m;
-            __syncwarp();
-        };
-
-        // ---- evaluate one pair per lane and append the ones that matter to the ring.
-        // s: record slot of the survivor in the current stage, pl: pixel lane, active: this lane holds a pair.
-        // keep_all (resume path): nothing is dropped -- a pair with alpha < 1/255 is kept as a skipped pair.
-        auto eval_and_push = [&](const int s, const int pl, const bool active, const bool keep_all) {
-            const SplatRec& r = ws.rec[cur][s];
-            const float4 r0 = r.q[0], r1 = r.q[1], r2 = r.q[2], r3 = r.q[3], r4 = r.q[4];
-            Pixel pe;
-            pe.origin = origin;
-            pe.ray = make_float3(ws.pix[0][pl], ws.pix[1][pl], ws.pix[2][pl]);
-            pe.px = ws.pix[3][pl]; pe.py = ws.pix[4][pl];
-            const PairEval e = eval_pair(pe, r0, r1, r2, r3, r4, use_blur);
-            const bool small = e.alpha < 1.f / 255.f;
-            const bool keep = active && (keep_all || !small);
-            const unsigned km = __ballot_sync(full, keep);
-            if (keep) {
-                const bool skip = small || (e.t < kNear) || (e.t > kFar);
-                float u = 0.f, v = 0.f, t_view = 0.f, d = 0.f;
-                if (!skip) {
-                    t_view = __fmul_rn(e.t, ws.pix[5][pl]);
-                    u = chart_coord(r.q[6], e.delta);
-                    v = chart_coord(r.q[7], e.delta);
-                    d = use_ndc ? ndc_depth_ref(t_view) : e.t;
-                }
-                const int slot = (r_tail + __popc(km & lt_mask)) & (kDRing - 1);
-                ws.e_a[slot] = make_float4(skip ? -e.alpha : e.alpha, d, t_view, __int_as_float(s | (pl << 5)));
-                ws.e_b[slot] = make_float4(u, v, -1.f, 0.f);
-            }
-            r_tail += __popc(km);
-        };
-
-        // ---- phase A over the n survivors staged in rec[cur]
-        auto phase_a = [&](const int n) {
-            int rect = 0, cnt_s = 0;
-            if (lane < n) {
-                rect = ws.q_rect[(q_head + lane) & (kDQueue - 1)];
-                cnt_s = rect >> 9;
-            }
-            int end_s = cnt_s;
-#pragma unroll
-            for (int o = 1; o < kDBatch; o <<= 1) {
-                const int up = __shfl_up_sync(full, end_s, o);
-                if (lane >= o) end_s += up;
-            }
-            const int total = __shfl_sync(full, end_s, kDBatch - 1);
-            const int off_s = end_s - cnt_s;
-            const int wd = (rect >> 5) & 15;
-            // offset | first pixel lane << 10 | width << 15 | division magic << 19
-            const int word = off_s | ((rect & 31) << 10) | (wd << 15) | (div_magic(max(wd, 1)) << 19);
-            for (int base = 0; base < total; base += 32) {
-                const int j = base + lane;
-                const bool in_range = j < total;
-                const bool starts_here = lane < n && off_s >= base && off_s < base + 32;
-                const unsigned startmask = __reduce_or_sync(full, starts_here ? (1u << (off_s - base)) : 0u);
-                const int nbefore = __popc(__ballot_sync(full, lane < n && off_s < base));
-                const int s = min(max(nbefore + __popc(startmask & le_mask) - 1, 0), n - 1);
-                const int wv = __shfl_sync(full, word, s);
-                const int i = j - (wv & 1023);
-                const int yy = (i * ((wv >> 19) & 511)) >> 8;
-                int pl = ((wv >> 10) & 31) + yy * 8 + (i - yy * ((wv >> 15) & 15));
-                const bool active = in_range && pl >= 0 && pl < 32 && !((done_mask >> (pl & 31)) & 1u);
-                pl = active ? pl : 0;
-                eval_and_push(s, pl, active, false);
-                if (r_tail - r_head >= 32) {
-                    process_group(32, false);
-                    if (done_mask == full) return;
-                }
-            }
-        };
-
-        // ---- main walk: cull -> stage (TMA) -> phase A -> groups, one batch in flight behind the one evaluated
-        int n_cur = 0;
+        // ---- the walk: ONE loop whose body is one of three steps (every step exists once in the code, so the
+        // per-pixel state is loop-carried through a single back edge):
+        //   GROUP    blend the oldest <= 32 ring entries            (>= 32 pending, or draining a finished batch)
+        //   PRODUCE  evaluate 32 pairs and push the ones that matter (dense enumeration; or, resuming suspended
+        //            pixels, one list entry with every lane its own pixel and nothing dropped)
+        //   ADVANCE  next batch / switch to the resume path / finish
+        int n_cur = 0, n_next = 0;
+        int pa_base = 0, pa_total = 0, pa_word = 0, pa_off = 0;  // phase A progress over the batch's pairs
+        bool setup = true, drain = false;
         if (done_mask != full) {
             prime();
             n_cur = fill_and_issue(cur);
         }
-        while (n_cur > 0) {
-            const int n_next = fill_and_issue(cur ^ 1);  // next batch in flight while this one is evaluated
-            mbar_wait(&ws.bar[cur], (phase >> cur) & 1u);
-            phase ^= 1u << cur;
-            phase_a(n_cur);
-            // the ring's entries point into this batch's record stage: finish them before it is refilled
-            while (r_tail != r_head && done_mask != full) process_group(min(32, r_tail - r_head), false);
-            r_head = r_tail;
-            if (done_mask == full) {
-                if (n_next > 0) {  // drain the copies in flight before their stage and barrier are reused
+        bool running = n_cur > 0;
+        int guard = 0;
+        while (running) {
+            if (p.dbg == 3 && ++guard > 200000) {
+                if (lane == 0)
+                    printf("STUCK unit %d slow %d setup %d drain %d n_cur %d n_next %d pa %d/%d ring %d..%d cursor %d range %d %d q %d %d %d mask %08x\n",
+                           unit, (int)slow, (int)setup, (int)drain, n_cur, n_next, pa_base, pa_total, r_head, r_tail, cursor,
+                           range.x, range.y, q_head, q_issue, q_tail, done_mask);
+                if (setup) { mbar_wait(&ws.bar[cur], (phase >> cur) & 1u); phase ^= 1u << cur; }
+                else if (n_next > 0) { mbar_wait(&ws.bar[cur ^ 1], (phase >> (cur ^ 1)) & 1u); phase ^= 1u << (cur ^ 1); }
+                break;
+            }
+            if (setup) {  // begin the batch staged in rec[cur]: next batch in flight, pair offsets of this one
+                setup = false;
+                drain = false;
+                n_next = fill_and_issue(cur ^ 1);
+                mbar_wait(&ws.bar[cur], (phase >> cur) & 1u);
+                phase ^= 1u << cur;
+                int rect = 0, cnt_s = 0;
+                if (lane < n_cur) {
+                    rect = ws.q_rect[(q_head + lane) & (kDQueue - 1)];
+                    cnt_s = rect >> 9;
+                }
+                int end_s = cnt_s;
+#pragma unroll
+                for (int o = 1; o < kDBatch; o <<= 1) {
+                    const int up = __shfl_up_sync(full, end_s, o);
+                    if (lane >= o) end_s += up;
+                }
+                pa_total = __shfl_sync(full, end_s, kDBatch - 1);
+                if (p.dbg == 3 && (pa_total > 512 || pa_total < 0) && lane < 16)
+                    printf("BAD unit %d lane %d slow %d n_cur %d rect %08x cnt %d end %d q_head %d live %d %d %d %d\n", unit, lane, (int)slow,
+                           n_cur, rect, cnt_s, end_s, q_head, lx0, lx1, ly0, ly1);
+                pa_base = 0;
+                pa_off = (lane < n_cur) ? end_s - cnt_s : 0x7fffffff;
+                const int wd = (rect >> 5) & 15;
+                // offset | first pixel lane << 10 | width << 15 | division magic << 19
+                pa_word = (end_s - cnt_s) | ((rect & 31) << 10) | (wd << 15) | (div_magic(max(wd, 1)) << 19);
+            }
+            const int pending = r_tail - r_head;
+            if (pending >= 32 || (drain && pending > 0)) {
+                // ================= GROUP: m <= 32 ring entries, oldest first =================
+                const int m = min(pending, 32);
+                __syncwarp();
+                const int hs = (r_head + lane) & (kDRing - 1);
+                const bool valid = lane < m;
+                float4 ea = make_float4(0.f, 0.f, 0.f, 0.f), eb = ea;
+                if (valid) { ea = ws.e_a[hs]; eb = ws.e_b[hs]; }
+                const int code = __float_as_int(eb.y);
+                const int es = code & 31, epl = (code >> 5) & 31;
+                // (i) lane-dense: chart coordinates, depth terms and the bilinear fetch of the pairs that can still
+                // be composited
+                float u = 0.f, v = 0.f, val0 = 0.f, val1 = 0.f, val2 = 0.f, dterm = 0.f, t_view = 0.f;
+                if (valid && ea.x > 0.f && (slow || !((done_mask >> epl) & 1u))) {
+                    const SplatRec& rr = ws.rec[cur][es];
+                    const float3 delta = make_float3(ea.z, ea.w, eb.x);
+                    u = chart_coord(rr.q[6], delta);
+                    v = chart_coord(rr.q[7], delta);
+                    t_view = __fmul_rn(ea.y, ws.pix[5][epl]);
+                    dterm = use_ndc ? ndc_depth_ref(t_view) : ea.y;
+                    const float4 r4 = rr.q[4];
+                    const int start = __float_as_int(rr.q[5].w);
+                    const TexQuery tq = tex_query(__float_as_int(r4.z), __float_as_int(r4.w), start, u, v, bilinear);
+                    const float* t00 = p.texture + (size_t)tq.b00 * C;
+                    const float* t01 = p.texture + (size_t)tq.b01 * C;
+                    const float* t10 = p.texture + (size_t)tq.b10 * C;
+                    const float* t11 = p.texture + (size_t)tq.b11 * C;
+                    val0 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00), __ldg(t01), __ldg(t10), __ldg(t11));
+                    if (C > 1) val1 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00 + 1), __ldg(t01 + 1), __ldg(t10 + 1), __ldg(t11 + 1));
+                    if (C > 2) val2 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00 + 2), __ldg(t01 + 2), __ldg(t10 + 2), __ldg(t11 + 2));
+                    // affine texel activation (SH2RGB of the caller folded into the fetch); (1, 0) leaves the sample as it is
+                    val0 = __fmaf_rn(p.tex_scale, val0, p.tex_bias);
+                    if (C > 1) val1 = __fmaf_rn(p.tex_scale, val1, p.tex_bias);
+                    if (C > 2) val2 = __fmaf_rn(p.tex_scale, val2, p.tex_bias);
+                }
+                if (valid) {
+                    ws.e_c[hs] = make_float4(val0, val1, val2, dterm);
+                    ws.e_b[hs].w = t_view;
+                }
+                // (ii) which entries belong to this lane's pixel
+                unsigned own = __ballot_sync(full, valid);
+#pragma unroll
+                for (int bit = 0; bit < 5; ++bit) {
+                    const unsigned bal = __ballot_sync(full, valid && ((epl >> bit) & 1));
+                    own &= ((lane >> bit) & 1) ? bal : ~bal;
+                }
+                __syncwarp();
+                // (iii) owner walk, list order; straight-line body (no early exits: one loop-carried copy of the state)
+                bool stop = done || (susp && !slow);
+                while (own) {
+                    const int j = __ffs(own) - 1;
+                    own &= own - 1u;
+                    const int slot = (r_head + j) & (kDRing - 1);
+                    const float4 a4 = ws.e_a[slot], b4 = ws.e_b[slot];
+                    const float a = a4.x;
+                    const float next_T = __fmul_rn(T, __fsub_rn(1.f, fabsf(a)));
+                    const bool term = !stop && next_T <= 1e-4f;  // this splat is not composited (texture.cu:216-221)
+                    const bool take = !stop && !term && a > 0.f;
+                    done = done || term;
+                    if (take) {
+                        const int s = __float_as_int(b4.y) & 31;
+                        const SplatRec& r = ws.rec[cur][s];
+                        const float4 r1 = r.q[1], r5 = r.q[5], c4 = ws.e_c[slot];
+                        const int idx = ws.q_idx[(q_head + s) & (kDQueue - 1)];
+                        const float vis = __fmul_rn(a, T);
+                        rgb.x = __fmaf_rn(vis, r5.x, rgb.x); rgb.y = __fmaf_rn(vis, r5.y, rgb.y); rgb.z = __fmaf_rn(vis, r5.z, rgb.z);
+                        nrm.x = __fmaf_rn(vis, r1.x, nrm.x); nrm.y = __fmaf_rn(vis, r1.y, nrm.y); nrm.z = __fmaf_rn(vis, r1.z, nrm.z);
+                        tex0 = __fmaf_rn(vis, c4.x, tex0); tex1 = __fmaf_rn(vis, c4.y, tex1); tex2 = __fmaf_rn(vis, c4.z, tex2);
+                        if (T > 0.5f) {  // median depth, texture.cu:286-291
+                            pix_depth = b4.w;
+                            pix_depth_index = idx;
+                        }
+                        distortion_ref(c4.w, vis, ts, pix_reg);  // distortion(), helpers.cuh:259-264
+                        ws.e_b[slot].z = T;  // composited: a pair-stream item with this transmittance in front of it
+                        T = next_T;
+                        cur_idx = idx;
+                        // From here a pair with alpha < 1/255 -- which PRODUCE drops -- could end this pixel: suspend it
+                        // at this list position; it is resumed with nothing dropped once the others are finished.
+                        if (!slow && next_T <= 1.0041e-4f) { susp = true; susp_pos = idx; }
+                    }
+                    stop = stop || term || (susp && !slow);
+                }
+                __syncwarp();
+                // (iv) the composited entries, in ring order, become consecutive items of the unit's pair stream
+                if (REC && rec_ok) {
+                    const float Tb = valid ? ws.e_b[hs].z : -1.f;
+                    const bool alive = Tb >= 0.f;
+                    const unsigned am = __ballot_sync(full, alive);
+                    const int na = __popc(am);
+                    if (na > 0) {
+                        int new_chunk = cur_chunk;
+                        if (fill + na > kChunkItems) {
+                            int c = 0;
+                            if (lane == 0) c = (int)atomicAdd(&p.sv.hdr->next_chunk, 1u);
+                            c = __shfl_sync(full, c, 0);
+                            if (c >= p.sv.num_chunks) {
+                                if (lane == 0) p.sv.hdr->overflow = 1u;
+                                rec_ok = false;
+                            } else {
+                                if (lane == 0) p.sv.chunk_prev[c] = cur_chunk;
+                                new_chunk = c;
+                            }
+                        }
+                        if (rec_ok) {
+                            if (alive) {
+                                int pos = fill + __popc(am & lt_mask);
+                                int ch = cur_chunk;
+                                if (pos >= kChunkItems) { pos -= kChunkItems; ch = new_chunk; }
+                                float4* dst = reinterpret_cast<float4*>(p.sv.items + (size_t)ch * kChunkItems + pos);
+                                const int q = (q_head + es) & (kDQueue - 1);
+                                const uint32_t gl = ((uint32_t)ws.q_gid[q] << 5) | (uint32_t)epl;
+                                dst[0] = make_float4(__uint_as_float(gl), __int_as_float(ws.q_idx[q]), Tb, u);
+                                dst[1] = make_float4(v, val0, val1, val2);
+                            }
+                            fill += na;
+                            if (fill > kChunkItems) { fill -= kChunkItems; cur_chunk = new_chunk; }
+                            cnt += na;
+                        }
+                    }
+                }
+                done_mask = __ballot_sync(full, done || (susp != slow));
+                r_head += m;
+                if (done_mask == full) {  // nobody takes pairs any more: drop what is queued, end the batch
+                    r_head = r_tail;
+                    pa_base = pa_total;
+                    drain = true;
+                }
+                __syncwarp();
+            } else if (!drain) {
+                // ================= PRODUCE: one pair per lane =================
+                // dense enumeration of the batch's (survivor, pixel inside its clipped support box) pairs
+                const int j = pa_base + lane;
+                const bool starts_here = pa_off >= pa_base && pa_off < pa_base + 32;
+                const unsigned startmask = __reduce_or_sync(full, starts_here ? (1u << (pa_off - pa_base)) : 0u);
+                const int nbefore = __popc(__ballot_sync(full, pa_off < pa_base));
+                const int s = min(max(nbefore + __popc(startmask & le_mask) - 1, 0), n_cur - 1);
+                const int wv = __shfl_sync(full, pa_word, s);
+                const int i = j - (wv & 1023);
+                const int yy = (i * ((wv >> 19) & 511)) >> 8;
+                int pl = ((wv >> 10) & 31) + yy * 8 + (i - yy * ((wv >> 15) & 15));
+                bool active = j < pa_total && (unsigned)pl < 32u && !((done_mask >> (pl & 31)) & 1u);
+                pl = active ? pl : 0;
+                if (slow) {  // resume path: a pixel only takes entries behind the one that suspended it
+                    const int behind = __shfl_sync(full, susp_pos, pl);  // every lane takes part (no short circuit)
+                    active = active && ws.q_idx[(q_head + s) & (kDQueue - 1)] > behind;
+                }
+                pa_base += 32;
+                drain = pa_base >= pa_total;
+                const SplatRec& r = ws.rec[cur][s];
+                const float4 r0 = r.q[0], r1 = r.q[1], r2 = r.q[2], r3 = r.q[3], r4 = r.q[4];
+                Pixel pe;
+                pe.origin = origin;
+                pe.ray = make_float3(ws.pix[0][pl], ws.pix[1][pl], ws.pix[2][pl]);
+                pe.px = ws.pix[3][pl]; pe.py = ws.pix[4][pl];
+                const PairEval e = eval_pair(pe, r0, r1, r2, r3, r4, use_blur);
+                // A dropped pair has alpha < 1/255.  The resume path keeps it as a skipped pair (it may end the pixel) unless
+                // 1 - alpha rounds to 1: then next_T == T and it cannot change or end anything.
+                const bool small = e.alpha < 1.f / 255.f;
+                const bool keep = active && (!small || (slow && __fsub_rn(1.f, e.alpha) < 1.f));
+                const unsigned km = __ballot_sync(full, keep);
+                if (keep) {
+                    const bool skip = small || (e.t < kNear) || (e.t > kFar);
+                    const int slot = (r_tail + __popc(km & lt_mask)) & (kDRing - 1);
+                    ws.e_a[slot] = make_float4(skip ? -e.alpha : e.alpha, e.t, e.delta.x, e.delta.y);
+                    ws.e_b[slot] = make_float4(e.delta.z, __int_as_float(s | (pl << 5)), -1.f, 0.f);
+                }
+                r_tail += __popc(km);
+            } else {
+                // ================= ADVANCE: the batch is evaluated and blended =================
+                const bool all_done = done_mask == full;
+                if (all_done && n_next > 0) {  // drain the copies in flight before their stage and barrier are reused
                     mbar_wait(&ws.bar[cur ^ 1], (phase >> (cur ^ 1)) & 1u);
                     phase ^= 1u << (cur ^ 1);
                 }
-                break;
+                q_head += n_cur;
+                n_cur = all_done ? 0 : n_next;
+                cur ^= 1;
+                if (n_cur == 0 && !slow && p.dbg != 2 && __any_sync(full, susp && !done)) {
+                    // Resume path: suspended pixels (transmittance within 255/254 of the termination threshold, where
+                    // even a pair with alpha < 1/255 could end them) re-walk the list from the entry after the one that
+                    // suspended them with the same machinery, but NOTHING is culled or dropped: every list entry is a
+                    // survivor, clipped to the rectangle of the suspended pixels.  Rare: ~1 pixel in 500.
+                    slow = true;
+                    cursor = __reduce_min_sync(full, (susp && !done) ? susp_pos + 1 : 0x7fffffff);
+                    q_head = q_issue = q_tail = 0;
+                    done_mask = __ballot_sync(full, done || !susp);
+                    shrink_live_rect();
+                    prime();
+                    n_cur = fill_and_issue(cur);
+                }
+                if (n_cur > 0) {
+                    shrink_live_rect();
+                    setup = true;
+                } else {
+                    running = false;
+                }
             }
-            q_head += n_cur;
-            n_cur = n_next;
-            cur ^= 1;
-            shrink_live_rect();
-        }
-
-        // ---- resume path: suspended pixels (transmittance within 255/254 of the termination threshold) re-walk the
-        // list from the entry after the one that suspended them, one entry at a time, every lane its own pixel and
-        // NOTHING dropped -- the reference's own loop, restricted to those pixels.  Rare: ~1 pixel in 500.
-        if (__any_sync(full, susp && !done)) {
-            __syncwarp();
-            q_head = 0;
-            int pos = __reduce_min_sync(full, (susp && !done) ? susp_pos + 1 : 0x7fffffff);
-            for (; pos < range.y; ++pos) {
-                const bool active = susp && !done && pos > susp_pos;
-                if (!__any_sync(full, susp && !done)) break;
-                if (!__any_sync(full, active)) continue;
-                const int gid = __ldg(p.ids + pos);
-                if (lane < 8) ws.rec[cur][0].q[lane] = __ldg(&p.recs[gid].q[lane]);
-                if (lane == 0) { ws.q_gid[0] = gid; ws.q_idx[0] = pos; }
-                __syncwarp();
-                eval_and_push(0, lane, active, true);
-                process_group(r_tail - r_head, true);
-            }
-            // the record stage was written with ordinary stores here; the next unit refills it through the async proxy
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         }
 
         if (REC) {
