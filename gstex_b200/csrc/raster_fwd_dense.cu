@@ -20,8 +20,6 @@
 // it could only END a pixel whose transmittance lies in (1e-4, 1e-4 / (1 - 1/255)] (next_T <= 1e-4 is tested before
 // `skip`, texture.cu:216-221).  A pixel entering that window is SUSPENDED at that list position; once the warp's
 // other pixels are finished the suspended ones are resumed one list entry at a time with nothing dropped.
-#include <cstdio>
-
 #include "raster_fwd.cuh"
 
 namespace gstex {
@@ -33,7 +31,7 @@ constexpr int kDQueue = 64;      // survivor ring: batch being evaluated + batch
 constexpr int kDRing = 64;       // pair ring: < 32 pending + <= 32 new per phase-A step
 
 struct DenseWarpShared {
-    SplatRec rec[2][kDBatch];    // 4 KB
+    SplatRec rec[2 * kDBatch];   // 4 KB: two stages of kDBatch records (the resume path uses all 32 slots at once)
     int q_gid[kDQueue];          // splat id
     int q_idx[kDQueue];          // position in the global sorted list
     int q_rect[kDQueue];         // support box clipped to the unit: first pixel lane | width << 5 | pixel count << 9
@@ -48,6 +46,8 @@ struct DenseShared {
     DenseWarpShared w[kDWarps];
     Camera cam;
 };
+
+__device__ unsigned long long g_dense_stats[8];  // dbg == 4: resume-path statistics (tests / tuning only)
 
 // floor(i / w) for 0 <= i < 32, 1 <= w <= 8 as (i * m) >> 8
 __device__ __forceinline__ int div_magic(int w) {
@@ -133,9 +133,8 @@ __global__ void __launch_bounds__(kDWarps * 32, kDCtasPerSm) texture_forward_den
         // next kDBatch queued records into stage `buf`.  A survivor's support box is clipped to the rectangle of the
         // pixels still alive: that rectangle (first pixel lane, width, pixel count) is all phase A needs to enumerate
         // its pairs.  Returns the number of records in flight.
-        bool slow = false;  // resume path (see ADVANCE)
         auto fill_and_issue = [&](int buf) -> int {
-            const bool nocull = p.force_nocull != 0 || slow;
+            const bool nocull = p.force_nocull != 0;
             while (q_tail - q_issue < kDBatch && cursor < range.y) {
                 const int gid = gid_pf;
                 const float4 box = box_pf;
@@ -167,7 +166,7 @@ __global__ void __launch_bounds__(kDWarps * 32, kDCtasPerSm) texture_forward_den
             if (n_rec > 0) {
                 if (lane == 0) mbar_arrive_expect_tx(&ws.bar[buf], (uint32_t)n_rec * (uint32_t)sizeof(SplatRec));
                 if (lane < n_rec)
-                    bulk_copy_g2s(&ws.rec[buf][lane], p.recs + ws.q_gid[(q_issue + lane) & (kDQueue - 1)], sizeof(SplatRec),
+                    bulk_copy_g2s(&ws.rec[buf * kDBatch + lane], p.recs + ws.q_gid[(q_issue + lane) & (kDQueue - 1)], sizeof(SplatRec),
                                   &ws.bar[buf]);
                 q_issue += n_rec;
             }
@@ -183,22 +182,15 @@ __global__ void __launch_bounds__(kDWarps * 32, kDCtasPerSm) texture_forward_den
         int n_cur = 0, n_next = 0;
         int pa_base = 0, pa_total = 0, pa_word = 0, pa_off = 0;  // phase A progress over the batch's pairs
         bool setup = true, drain = false;
+        bool slow = false;                    // resume path (see RESUME)
+        int slow_base = 0, slow_start = 0;    // base of the round of 32 list entries being resumed
+        unsigned slow_todo = 0u;              // suspended pixels still to evaluate against this round
         if (done_mask != full) {
             prime();
             n_cur = fill_and_issue(cur);
         }
         bool running = n_cur > 0;
-        int guard = 0;
         while (running) {
-            if (p.dbg == 3 && ++guard > 200000) {
-                if (lane == 0)
-                    printf("STUCK unit %d slow %d setup %d drain %d n_cur %d n_next %d pa %d/%d ring %d..%d cursor %d range %d %d q %d %d %d mask %08x\n",
-                           unit, (int)slow, (int)setup, (int)drain, n_cur, n_next, pa_base, pa_total, r_head, r_tail, cursor,
-                           range.x, range.y, q_head, q_issue, q_tail, done_mask);
-                if (setup) { mbar_wait(&ws.bar[cur], (phase >> cur) & 1u); phase ^= 1u << cur; }
-                else if (n_next > 0) { mbar_wait(&ws.bar[cur ^ 1], (phase >> (cur ^ 1)) & 1u); phase ^= 1u << (cur ^ 1); }
-                break;
-            }
             if (setup) {  // begin the batch staged in rec[cur]: next batch in flight, pair offsets of this one
                 setup = false;
                 drain = false;
@@ -217,9 +209,6 @@ __global__ void __launch_bounds__(kDWarps * 32, kDCtasPerSm) texture_forward_den
                     if (lane >= o) end_s += up;
                 }
                 pa_total = __shfl_sync(full, end_s, kDBatch - 1);
-                if (p.dbg == 3 && (pa_total > 512 || pa_total < 0) && lane < 16)
-                    printf("BAD unit %d lane %d slow %d n_cur %d rect %08x cnt %d end %d q_head %d live %d %d %d %d\n", unit, lane, (int)slow,
-                           n_cur, rect, cnt_s, end_s, q_head, lx0, lx1, ly0, ly1);
                 pa_base = 0;
                 pa_off = (lane < n_cur) ? end_s - cnt_s : 0x7fffffff;
                 const int wd = (rect >> 5) & 15;
@@ -241,7 +230,7 @@ __global__ void __launch_bounds__(kDWarps * 32, kDCtasPerSm) texture_forward_den
                 // be composited
                 float u = 0.f, v = 0.f, val0 = 0.f, val1 = 0.f, val2 = 0.f, dterm = 0.f, t_view = 0.f;
                 if (valid && ea.x > 0.f && (slow || !((done_mask >> epl) & 1u))) {
-                    const SplatRec& rr = ws.rec[cur][es];
+                    const SplatRec& rr = ws.rec[cur * kDBatch + es];
                     const float3 delta = make_float3(ea.z, ea.w, eb.x);
                     u = chart_coord(rr.q[6], delta);
                     v = chart_coord(rr.q[7], delta);
@@ -288,7 +277,7 @@ __global__ void __launch_bounds__(kDWarps * 32, kDCtasPerSm) texture_forward_den
                     done = done || term;
                     if (take) {
                         const int s = __float_as_int(b4.y) & 31;
-                        const SplatRec& r = ws.rec[cur][s];
+                        const SplatRec& r = ws.rec[cur * kDBatch + s];
                         const float4 r1 = r.q[1], r5 = r.q[5], c4 = ws.e_c[slot];
                         const int idx = ws.q_idx[(q_head + s) & (kDQueue - 1)];
                         const float vis = __fmul_rn(a, T);
@@ -355,6 +344,54 @@ __global__ void __launch_bounds__(kDWarps * 32, kDCtasPerSm) texture_forward_den
                     drain = true;
                 }
                 __syncwarp();
+            } else if (slow) {
+                // ================= RESUME: 32 list entries (one per lane) against ONE suspended pixel =================
+                // A suspended pixel (transmittance within 255/254 of the termination threshold, where even a pair with
+                // alpha < 1/255 could end it) re-walks the list from the entry after the one that suspended it, and
+                // nothing may be culled or dropped for it.  alpha of different entries is independent, so the walk is
+                // entry-parallel: every lane evaluates its own list entry for the pixel, straight from the packed
+                // records in global memory; entries that cannot change anything (1 - alpha rounds to 1: next_T == T) are
+                // left out, the rest go through the ring and GROUP like any other pair.  ~1 pixel in 200.
+                drain = false;
+                if (slow_todo == 0u) {
+                    slow_base += 32;
+                    slow_todo = __ballot_sync(full, susp && !done);
+                    if (slow_base >= range.y || slow_todo == 0u) {
+                        running = false;
+                        continue;
+                    }
+                }
+                const int px = __ffs(slow_todo) - 1;
+                slow_todo &= slow_todo - 1u;
+                const int pos = slow_base + lane;
+                const bool in_list = pos < range.y;
+                const int gid = in_list ? __ldg(p.ids + pos) : __ldg(p.ids + range.y - 1);
+                const float4* src = p.recs[gid].q;
+                const float4 r0 = __ldg(src), r1 = __ldg(src + 1), r2 = __ldg(src + 2), r3 = __ldg(src + 3), r4 = __ldg(src + 4);
+                const int behind = __shfl_sync(full, susp_pos, px);
+                Pixel pe;
+                pe.origin = origin;
+                pe.ray = make_float3(ws.pix[0][px], ws.pix[1][px], ws.pix[2][px]);
+                pe.px = ws.pix[3][px]; pe.py = ws.pix[4][px];
+                const PairEval e = eval_pair(pe, r0, r1, r2, r3, r4, use_blur);
+                const bool small = e.alpha < 1.f / 255.f;
+                const bool keep = in_list && pos > behind && (!small || __fsub_rn(1.f, e.alpha) < 1.f);
+                const unsigned km = __ballot_sync(full, keep);
+                if (km != 0u) {
+                    if (keep) {  // GROUP reads the record, the splat id and the list position of slot `lane`
+                        SplatRec& dst = ws.rec[lane];
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) dst.q[k] = __ldg(src + k);  // (reloaded: L1 hits; keeps the step's registers few)
+                        ws.q_gid[lane] = gid;
+                        ws.q_idx[lane] = pos;
+                        const bool skip = small || (e.t < kNear) || (e.t > kFar);
+                        const int slot = (r_tail + __popc(km & lt_mask)) & (kDRing - 1);
+                        ws.e_a[slot] = make_float4(skip ? -e.alpha : e.alpha, e.t, e.delta.x, e.delta.y);
+                        ws.e_b[slot] = make_float4(e.delta.z, __int_as_float(lane | (px << 5)), -1.f, 0.f);
+                    }
+                    r_tail += __popc(km);
+                    drain = true;  // blend them before the slots are reused
+                }
             } else if (!drain) {
                 // ================= PRODUCE: one pair per lane =================
                 // dense enumeration of the batch's (survivor, pixel inside its clipped support box) pairs
@@ -367,28 +404,22 @@ __global__ void __launch_bounds__(kDWarps * 32, kDCtasPerSm) texture_forward_den
                 const int i = j - (wv & 1023);
                 const int yy = (i * ((wv >> 19) & 511)) >> 8;
                 int pl = ((wv >> 10) & 31) + yy * 8 + (i - yy * ((wv >> 15) & 15));
-                bool active = j < pa_total && (unsigned)pl < 32u && !((done_mask >> (pl & 31)) & 1u);
+                const bool active = j < pa_total && (unsigned)pl < 32u && !((done_mask >> (pl & 31)) & 1u);
                 pl = active ? pl : 0;
-                if (slow) {  // resume path: a pixel only takes entries behind the one that suspended it
-                    const int behind = __shfl_sync(full, susp_pos, pl);  // every lane takes part (no short circuit)
-                    active = active && ws.q_idx[(q_head + s) & (kDQueue - 1)] > behind;
-                }
                 pa_base += 32;
                 drain = pa_base >= pa_total;
-                const SplatRec& r = ws.rec[cur][s];
+                const SplatRec& r = ws.rec[cur * kDBatch + s];
                 const float4 r0 = r.q[0], r1 = r.q[1], r2 = r.q[2], r3 = r.q[3], r4 = r.q[4];
                 Pixel pe;
                 pe.origin = origin;
                 pe.ray = make_float3(ws.pix[0][pl], ws.pix[1][pl], ws.pix[2][pl]);
                 pe.px = ws.pix[3][pl]; pe.py = ws.pix[4][pl];
                 const PairEval e = eval_pair(pe, r0, r1, r2, r3, r4, use_blur);
-                // A dropped pair has alpha < 1/255.  The resume path keeps it as a skipped pair (it may end the pixel) unless
-                // 1 - alpha rounds to 1: then next_T == T and it cannot change or end anything.
-                const bool small = e.alpha < 1.f / 255.f;
-                const bool keep = active && (!small || (slow && __fsub_rn(1.f, e.alpha) < 1.f));
+                // a dropped pair has alpha < 1/255 (skipped by the reference too); see RESUME for the one case it matters
+                const bool keep = active && e.alpha >= 1.f / 255.f;
                 const unsigned km = __ballot_sync(full, keep);
                 if (keep) {
-                    const bool skip = small || (e.t < kNear) || (e.t > kFar);
+                    const bool skip = (e.t < kNear) || (e.t > kFar);
                     const int slot = (r_tail + __popc(km & lt_mask)) & (kDRing - 1);
                     ws.e_a[slot] = make_float4(skip ? -e.alpha : e.alpha, e.t, e.delta.x, e.delta.y);
                     ws.e_b[slot] = make_float4(e.delta.z, __int_as_float(s | (pl << 5)), -1.f, 0.f);
@@ -404,18 +435,21 @@ __global__ void __launch_bounds__(kDWarps * 32, kDCtasPerSm) texture_forward_den
                 q_head += n_cur;
                 n_cur = all_done ? 0 : n_next;
                 cur ^= 1;
-                if (n_cur == 0 && !slow && p.dbg != 2 && __any_sync(full, susp && !done)) {
-                    // Resume path: suspended pixels (transmittance within 255/254 of the termination threshold, where
-                    // even a pair with alpha < 1/255 could end them) re-walk the list from the entry after the one that
-                    // suspended them with the same machinery, but NOTHING is culled or dropped: every list entry is a
-                    // survivor, clipped to the rectangle of the suspended pixels.  Rare: ~1 pixel in 500.
+                if (n_cur == 0 && p.dbg != 2 && __any_sync(full, susp && !done)) {
+                    // the main walk is over: resume the suspended pixels (RESUME above)
                     slow = true;
-                    cursor = __reduce_min_sync(full, (susp && !done) ? susp_pos + 1 : 0x7fffffff);
-                    q_head = q_issue = q_tail = 0;
-                    done_mask = __ballot_sync(full, done || !susp);
-                    shrink_live_rect();
-                    prime();
-                    n_cur = fill_and_issue(cur);
+                    cur = 0;
+                    q_head = 0;
+                    slow_start = __reduce_min_sync(full, (susp && !done) ? susp_pos + 1 : 0x7fffffff);
+                    slow_base = slow_start - 32;
+                    slow_todo = 0u;
+                    drain = false;
+                    if (p.dbg == 4 && lane == 0) {
+                        atomicAdd(&g_dense_stats[0], 1ull);
+                        atomicAdd(&g_dense_stats[2], (unsigned long long)(range.y - slow_start));
+                        atomicMax(&g_dense_stats[3], (unsigned long long)(range.y - slow_start));
+                    }
+                    continue;
                 }
                 if (n_cur > 0) {
                     shrink_live_rect();
@@ -426,6 +460,10 @@ __global__ void __launch_bounds__(kDWarps * 32, kDCtasPerSm) texture_forward_den
             }
         }
 
+        if (p.dbg == 4 && slow && lane == 0) {
+            atomicAdd(&g_dense_stats[4], (unsigned long long)(min(slow_base + 32, range.y) - slow_start));  // entries walked
+            atomicMax(&g_dense_stats[5], (unsigned long long)(min(slow_base + 32, range.y) - slow_start));
+        }
         if (REC) {
             const int unit0 = tile_id * kUnitsPerTile;
             if (lane == 0) p.sv.units[unit0 + w] = make_int2(cur_chunk, rec_ok ? cnt : 0);
@@ -449,6 +487,16 @@ __global__ void __launch_bounds__(kDWarps * 32, kDCtasPerSm) texture_forward_den
         }
         __syncwarp();
     }
+}
+
+extern "C" int gstex_debug_dense_stats(unsigned long long* out, int reset) {
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out, g_dense_stats, sizeof(unsigned long long) * 8);
+    if (reset) {
+        unsigned long long z[8] = {0};
+        cudaMemcpyToSymbol(g_dense_stats, z, sizeof(z));
+    }
+    return 0;
 }
 
 bool forward_dense_supported(const FwdParams& p) {
