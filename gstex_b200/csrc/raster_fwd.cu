@@ -523,8 +523,9 @@ extern "C" int gstex_texture_forward_act(int img_height, int img_width, int bloc
         if (!record)  // tell the backward there is nothing to read
             GSTEX_CUDA_TRY(cudaMemsetAsync(reinterpret_cast<char*>(pair_stream) + offsetof(StreamHeader, overflow), 1, 1, st));
     }
-    // training configuration (16x16 tiles, <= 3 channels, no viewer bit): the lane-dense kernel
-    if (g_forward_variant != 1 && forward_dense_supported(p)) return launch_forward_dense(p, record, st);
+    // The lane-dense kernel (raster_fwd_dense.cu; 16x16 tiles, <= 3 channels, no viewer bit) is bit-identical but measured
+    // 2-15 % slower than this file's kernel on every BASELINE configuration: opt-in only.
+    if (g_forward_variant >= 2 && forward_dense_supported(p)) return launch_forward_dense(p, record, st);
     // > 48 KB of shared memory: opt in (per device, cheap: done at every launch)
 #define GSTEX_FWD_LAUNCH(CM, RC, VS)                                                                                \
     do {                                                                                                            \

@@ -435,7 +435,7 @@ __global__ void __launch_bounds__(kDWarps * 32, kDCtasPerSm) texture_forward_den
                 q_head += n_cur;
                 n_cur = all_done ? 0 : n_next;
                 cur ^= 1;
-                if (n_cur == 0 && p.dbg != 2 && __any_sync(full, susp && !done)) {
+                if (n_cur == 0 && p.dbg != 3 && __any_sync(full, susp && !done)) {
                     // the main walk is over: resume the suspended pixels (RESUME above)
                     slow = true;
                     cur = 0;

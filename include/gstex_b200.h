@@ -55,9 +55,9 @@ long long gstex_launch_count(void);
  * block instead of culling by support box, so that tests can assert culling never changes a result.  Process-wide;
  * returns the previous value.  Not for production use (no environment variable is ever read by this library). */
 int gstex_debug_force_nocull(int on);
-/* TEST HOOK: 1 forces the general forward kernel (raster_fwd.cu) where the lane-dense training kernel
- * (raster_fwd_dense.cu) would run, 0 restores the automatic choice; the two must agree bit for bit.  Returns the
- * previous value. */
+/* TEST / TUNING HOOK: 2 selects the lane-dense forward kernel (raster_fwd_dense.cu: pair-parallel alpha evaluation;
+ * 16x16 tiles, <= 3 channels, no viewer bit) where it applies, 0 the default kernel (raster_fwd.cu); the two agree bit
+ * for bit (tests/test_gpu_raster.py).  4 = dense + resume-path statistics.  Returns the previous value. */
 int gstex_debug_forward_variant(int v);
 
 /* ---- stage (a): per-splat projection, bounds, tile count ------------------------------------- */

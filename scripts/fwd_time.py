@@ -10,7 +10,7 @@ from gstex_b200 import _lib, texture as T
 from gstex_b200.synthetic import make_scene
 
 name = sys.argv[1] if len(sys.argv) > 1 else "cfg5"
-variants = [int(x) for x in sys.argv[2:]] or [0, 1]
+variants = [int(x) for x in sys.argv[2:]] or [0, 2]   # 0 = default kernel, 2 = lane-dense kernel
 s = make_scene(name, views=8 if name == "cfg4" else 1)
 sd = {k: (x.cuda() if isinstance(x, torch.Tensor) else x) for k, x in s.items()}
 intr = (s["fx"], s["fy"], s["cx"], s["cy"]); H, W, bw = s["H"], s["W"], 16

@@ -296,10 +296,10 @@ def test_dense_forward_equals_general_forward(cfg):
 
     lib = _lib.load()
     vd = {k: x.cuda() for k, x in v.items()}
-    dense = parity.run_ours_view(sd, vd)
-    lib.gstex_debug_forward_variant(1)
+    general = parity.run_ours_view(sd, vd)
+    lib.gstex_debug_forward_variant(2)
     try:
-        general = parity.run_ours_view(sd, vd)
+        dense = parity.run_ours_view(sd, vd)
     finally:
         lib.gstex_debug_forward_variant(0)
     for k in parity.IMG_KEYS + ["final_idx", "depth_idx"]:
