@@ -30,6 +30,8 @@ _SIGNATURES = {
     "gstex_project_bounds": (I, [P, P, F, P, P, F, F, F, F, I, I, I, I, P, P, P, P, P, P]),
     "gstex_cumsum_workspace_bytes": (SZ, [I]),
     "gstex_cumsum_i32": (I, [P, I, P, P, P, SZ, P]),
+    "gstex_cumsum_noalloc_max_n": (I, []),
+    "gstex_cumsum_i32_noalloc": (I, [P, I, P, P, P]),
     "gstex_map_gaussian_to_intersects": (I, [I, I, P, P, P, P, I, I, I, P, P, P]),
     "gstex_sort_workspace_bytes": (SZ, [I]),
     "gstex_sort_isects": (I, [I, P, P, P, P, I, P, SZ, P]),
@@ -100,7 +102,8 @@ class _TimedLib:
         if not name.startswith("gstex_") or name.endswith("_bytes") or name in ("gstex_abi_version", "gstex_error_string",
                                                                                "gstex_launch_count", "gstex_debug_force_nocull", "gstex_debug_forward_variant",
                                                                                "gstex_pair_stream_supported",
-                                                                               "gstex_tile_bucket_max_list", "gstex_tile_bucket_max_tiles"):
+                                                                               "gstex_tile_bucket_max_list", "gstex_tile_bucket_max_tiles",
+                                                                               "gstex_cumsum_noalloc_max_n"):
             return fn
 
         def call(*args):

@@ -247,6 +247,8 @@ extern "C" const char* gstex_error_string(int code) {
     if (code == GSTEX_E_BADARG) return "gstex_b200: bad argument (null pointer, negative size or block_width outside [2,16])";
     if (code == GSTEX_E_UNSUPPORTED) return "gstex_b200: unsupported settings bits (viewer visualisation 16-29) or channel count";
     if (code == GSTEX_E_WORKSPACE) return "gstex_b200: workspace too small";
+    if (code == GSTEX_E_TOO_LARGE)
+        return "gstex_b200: size exceeds the fixed capacity of a no-allocation entry point (gstex_cumsum_noalloc_max_n)";
     if (code > 0) return cudaGetErrorString((cudaError_t)code);
     return "gstex_b200: unknown error";
 }

@@ -1,6 +1,8 @@
 // scan_emit.cu -- stage (b) integer kernels: inclusive prefix sum of the per-splat tile counts, emission
 // of the (tile<<32 | depth bits) keys, and extraction of the per-tile ranges from the sorted keys.
 // All results are integers and bit-exact with the reference by construction.  sm_100a.
+#include <atomic>
+
 #include "common.cuh"
 
 namespace gstex {
@@ -158,6 +160,61 @@ extern "C" int gstex_cumsum_i32(const int32_t* in, int n, int32_t* out, int32_t*
     if (workspace_bytes < gstex_cumsum_workspace_bytes(n)) return GSTEX_E_WORKSPACE;
     const int blocks = div_up(n, kScanTile);
     int32_t* block_sums = reinterpret_cast<int32_t*>(workspace);
+    scan_local_kernel<<<blocks, kScanThreads, 0, st>>>(in, n, out, block_sums);
+    GSTEX_LAUNCH_CHECK();
+    scan_add_kernel<<<blocks, kScanThreads, 0, st>>>(n, out, block_sums, total);
+    GSTEX_LAUNCH_CHECK();
+    return GSTEX_OK;
+}
+
+// ---- gstex_cumsum_i32_noalloc: the same scan with its scratch in a static device array ---------------------------
+// For callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc): no workspace
+// argument, no cudaMalloc / cudaFree / allocating library call.  No counterpart in the reference.
+// The per-tile totals live in a file-scope __device__ array that every GPU loading this
+// library holds until exit (64 KB).  In HOST code the array's name is only a stand-in, not a device address: the
+// address a kernel may use is fetched once per device, with that device current, by cudaGetSymbolAddress.
+constexpr int kNoAllocMaxTiles = 16384;                         // 64 KB of scratch
+constexpr int kNoAllocMaxN = kNoAllocMaxTiles * kScanTile;      // 67 108 864 elements
+static __device__ __align__(256) int32_t g_noalloc_block_sums[kNoAllocMaxTiles];
+
+constexpr int kNoAllocMaxDevices = 64;
+static std::atomic<int32_t*> g_noalloc_ptr[kNoAllocMaxDevices];
+
+// Device address of the scratch array on the CURRENT device (looked up once per device, then cached).
+static int noalloc_scratch(int32_t** out) {
+    int dev = -1;
+    GSTEX_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kNoAllocMaxDevices) return GSTEX_E_BADARG;
+    int32_t* p = g_noalloc_ptr[dev].load(std::memory_order_acquire);
+    if (p == nullptr) {
+        void* sym = nullptr;
+        GSTEX_CUDA_TRY(cudaGetSymbolAddress(&sym, g_noalloc_block_sums));
+        if (sym == nullptr) return (int)cudaErrorInvalidSymbol;
+        p = reinterpret_cast<int32_t*>(sym);
+        g_noalloc_ptr[dev].store(p, std::memory_order_release);  // racing threads store the same address
+    }
+    *out = p;
+    return GSTEX_OK;
+}
+
+extern "C" int gstex_cumsum_noalloc_max_n(void) { return kNoAllocMaxN; }
+
+extern "C" int gstex_cumsum_i32_noalloc(const int32_t* in, int n, int32_t* out, int32_t* total, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n < 0) return GSTEX_E_BADARG;
+    if (n > kNoAllocMaxN) return GSTEX_E_TOO_LARGE;
+    if (n == 0) {
+        if (total) GSTEX_CUDA_TRY(cudaMemsetAsync(total, 0, sizeof(int32_t), st));
+        return GSTEX_OK;
+    }
+    if (in == nullptr || out == nullptr) return GSTEX_E_BADARG;
+    int32_t* block_sums = nullptr;
+    const int rc = noalloc_scratch(&block_sums);
+    if (rc != GSTEX_OK) return rc;
+    // Nothing has to start at zero: scan_local_kernel writes the slot of every tile this call uses before
+    // scan_add_kernel (next on the stream) reads it; slots beyond `blocks` keep an earlier call's values and are
+    // never read.
+    const int blocks = div_up(n, kScanTile);
     scan_local_kernel<<<blocks, kScanThreads, 0, st>>>(in, n, out, block_sums);
     GSTEX_LAUNCH_CHECK();
     scan_add_kernel<<<blocks, kScanThreads, 0, st>>>(n, out, block_sums, total);

@@ -32,6 +32,7 @@ extern "C" {
 #define GSTEX_E_BADARG (-1)      /* null pointer, negative size, block_width outside [2,16] ... */
 #define GSTEX_E_UNSUPPORTED (-2) /* settings bits 16-29 (viewer visualisation), channels > 16 */
 #define GSTEX_E_WORKSPACE (-3)   /* workspace too small */
+#define GSTEX_E_TOO_LARGE (-4)   /* size beyond the fixed capacity of a no-allocation entry point */
 
 /* settings bit-field, ref: cuda/csrc/texture.cu:54-65,381-387 */
 #define GSTEX_SET_NEAREST (1 << 2)
@@ -90,6 +91,18 @@ int gstex_project_bounds(const float* means, const float* scales, float glob_sca
 size_t gstex_cumsum_workspace_bytes(int n);
 int gstex_cumsum_i32(const int32_t* in, int n, int32_t* out, int32_t* total, void* workspace, size_t workspace_bytes,
                      void* stream);
+
+/* No counterpart in the reference.  gstex_cumsum_i32 for callers that
+ * cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): the same
+ * kernels and the same results, but the scratch (per-tile totals) lives in a static 64 KB device array inside the
+ * library instead of a caller-provided workspace, and the call makes no cudaMalloc, cudaFree or allocating library call.
+ * Limits and caveats: n <= gstex_cumsum_noalloc_max_n() = 67 108 864, larger n returns GSTEX_E_TOO_LARGE and launches
+ * nothing; every GPU that loads the library holds the 64 KB until exit; ALL calls on a device share the one array, so
+ * two calls that overlap on the GPU (different streams, or graph branches without an edge between them) race on it --
+ * order them.  The array keeps the last call's contents; nothing needs clearing (every slot a call reads it has
+ * written first).  in / out / total are the caller's, as in gstex_cumsum_i32. */
+int gstex_cumsum_noalloc_max_n(void);
+int gstex_cumsum_i32_noalloc(const int32_t* in, int n, int32_t* out, int32_t* total, void* stream);
 
 /* ref: cuda/csrc/bindings.cu:77-121 map_gaussian_to_intersects_tensor -> kernel forward.cu:13-71
  * (wrapped=false).  Zero-fills isect_ids (I int64) and gaussian_ids (I int32) first, as the reference's
