@@ -57,6 +57,8 @@ _SIGNATURES = {
     "gstex_compute_sh_forward": (I, [I, I, I, P, P, P, P]),
     "gstex_compute_sh_backward": (I, [I, I, I, P, P, P, P]),
     "gstex_texture_sample_forward": (I, [I, I, P, P, P, P, P]),
+    "gstex_activations_forward": (I, [I] + [P] * 11),
+    "gstex_activations_backward": (I, [I] + [P] * 12),
     "gstex_texture_edit": (I, [I, I, I, I, I, I, ctypes.c_longlong] + [P] * 10 + [F] + [P] * 6 + [F, F, F, F, I] + [P, P, SZ, P]),
     "gstex_photometric_loss_scratch_bytes": (SZ, [I, I]),
     "gstex_photometric_loss_forward": (I, [I, I, I, P, P, P, P, P, P, F, I, F, P, P, P, P, SZ, P]),

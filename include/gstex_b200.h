@@ -268,6 +268,27 @@ int gstex_compute_sh_forward(int n, int degree, int degrees_to_use, const float*
 int gstex_compute_sh_backward(int n, int degree, int degrees_to_use, const float* viewdirs, const float* v_colors,
                               float* v_coeffs, void* stream);
 
+/* ---- next row (the other half): per-splat activations + uv maps ------------------- */
+
+/* ref: /root/reference/nerfstudio/models/gstex.py:1062-1066 (quats = raw / |raw|; scales = clamp(exp(raw[:, :2]), 1e-9)
+ * with scales[:, 2] = 1e-5 * mean of those two, detached; opacities = sigmoid(raw)) and get_uv_mapping, :975-990
+ * (uv0 = 0.5, umap = mappings[:, 0] * ax1, vmap = mappings[:, 1] * ax2 with ax1, ax2 the first two columns of
+ * R(F.normalize(quats)), gstex_cuda/_torch_impl.py:116-138; all three detached) -- ~30 torch launches over N per view in
+ * the reference, one kernel here.  quats_raw (n,4), scales_raw (n,3), opacities_raw (n,1), mappings (n,2) ->
+ * quats (n,4), scales (n,3), opacities (n,1), uv0 (n,1,2), umap (n,1,3), vmap (n,1,3); every element written.  The three
+ * map outputs may all be NULL (then `mappings` is not read).  Forward results are bit-identical to the torch ops on the
+ * same GPU.  quats_raw / quats must be 16-byte aligned. */
+int gstex_activations_forward(int n, const float* quats_raw, const float* scales_raw, const float* opacities_raw,
+                              const float* mappings, float* quats, float* scales, float* opacities, float* uv0,
+                              float* umap, float* vmap, void* stream);
+/* Gradients with respect to the raw parameters from the gradients of quats / scales / opacities (any of the three
+ * upstream pointers may be NULL = zero; any of the three outputs may be NULL = not wanted).  v_scales_raw[:, 2] = 0 and no
+ * gradient flows through the uv maps, as in the reference (detached). */
+int gstex_activations_backward(int n, const float* quats_raw, const float* scales_raw, const float* quats,
+                               const float* scales, const float* opacities, const float* v_quats, const float* v_scales,
+                               const float* v_opacities, float* v_quats_raw, float* v_scales_raw, float* v_opacities_raw,
+                               void* stream);
+
 /* ---- next row: jagged-texture sampling used by re-charting ------------------- */
 
 /* ref: cuda/csrc/texture_sample.cu:77-110 texture_sample_forward_tensor -> kernel :11-36.
