@@ -48,9 +48,8 @@ def parse_args():
     ap.add_argument("--size", type=int, default=None, help="override image size (debug)")
     ap.add_argument("--no-ref-cuda", action="store_true", help="skip timing the reference CUDA extension")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--binning-stream", default="auto", choices=["auto", "own", "current"],
-                    help="next view's projection + binning on a stream of their own or on the current stream; auto = own "
-                         "up to 4 ranks, current from 8 (measured: DESIGN.md section 6)")
+    ap.add_argument("--binning-stream", default="own", choices=["own", "current"],
+                    help="next view's projection + binning on a stream of their own (default) or on the current stream (A/B)")
     return ap.parse_args()
 
 
@@ -417,10 +416,9 @@ def ncu_capture(kernel_key):
 def main():
     global OWN_BINNING_STREAM
     args = parse_args()
-    # measured on one 8xB200 box (profiles/bench_r1_v29_n8*.json): at 8 ranks the two-stream sequence costs 13.93 ms per
-    # step against 12.70 ms on one stream; at 1 rank it is 11.1 against 11.9
-    OWN_BINNING_STREAM = args.binning_stream == "own" or (
-        args.binning_stream == "auto" and int(os.environ.get("WORLD_SIZE", "1")) < 8)
+    # second stream at every N: measured on one 8xB200 box (profiles/bench_r2_s1_n8_{own,current}.json) 3594 vs 3467 Mpix/s at
+    # 8 ranks, 498 vs 470 at one (round 1 needed a switch at 8 ranks; gone with the cheaper per-view host path)
+    OWN_BINNING_STREAM = args.binning_stream == "own"
     # stdout carries ONE JSON line and nothing else: libraries that log to file descriptor 1 (NCCL's version banner and
     # NCCL_DEBUG output go to stdout) are sent to stderr for the whole run, the line is written to the saved descriptor
     sys.stdout.flush()
