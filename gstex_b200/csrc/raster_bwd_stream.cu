@@ -212,10 +212,12 @@ __global__ void __launch_bounds__(kStreamWarps * 32, 2) texture_backward_stream_
                     if (q.b10 == q.b00) { c00 += c10; c10 = 0.f; }
                     if (q.b11 == q.b01) { c01 += c11; c11 = 0.f; }
                     const float g0 = vis * vt[0], g1 = vis * vt[1], g2 = vis * vt[2];
+#ifndef GSTEX_EXP_NO_TEXEL_RED  // experiment only (scripts/bwd_time.py): upper bound of what aggregating these could save
                     if (c00 != 0.f) red_add_v4(p.tex_acc + q.b00, c00 * g0, c00 * g1, c00 * g2, 0.f);
                     if (c01 != 0.f) red_add_v4(p.tex_acc + q.b01, c01 * g0, c01 * g1, c01 * g2, 0.f);
                     if (c10 != 0.f) red_add_v4(p.tex_acc + q.b10, c10 * g0, c10 * g1, c10 * g2, 0.f);
                     if (c11 != 0.f) red_add_v4(p.tex_acc + q.b11, c11 * g0, c11 * g1, c11 * g2, 0.f);
+#endif
                 }
                 {   // distortion_vjp, helpers.cuh:266-269, with the FINAL sums
                     const float d = use_ndc ? div_normal(kFar * t_view - kFar * kNear, (kFar - kNear) * t_view) : e.t;

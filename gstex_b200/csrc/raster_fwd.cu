@@ -34,11 +34,23 @@ __device__ unsigned long long g_fwd_stats[16];
 #define STAT_ADD(k, v)
 #endif
 
-constexpr int kFwdWarps = 5;    // warps per CTA; they share nothing but the camera (4 CTAs/SM = 20 warps)
-constexpr int kFwdCtasPerSm = 4;
+// Tuning knobs (scripts/gpu_fwd_sweep.sh builds and times the alternatives; the defaults are the measured best)
+#ifndef GSTEX_FWD_WARPS
+#define GSTEX_FWD_WARPS 5
+#endif
+#ifndef GSTEX_FWD_CTAS
+#define GSTEX_FWD_CTAS 4
+#endif
+#ifndef GSTEX_FWD_BATCH
+#define GSTEX_FWD_BATCH 16
+#endif
+constexpr int kFwdWarps = GSTEX_FWD_WARPS;    // warps per CTA; they share nothing but the camera (4 CTAs/SM = 20 warps)
+constexpr int kFwdCtasPerSm = GSTEX_FWD_CTAS;
 constexpr int kHits = 64;       // ring of contributing pairs waiting for their texture fetch (deferred, lane-dense)
-constexpr int kBatch = 32;      // records per stage = one TMA bulk copy per lane
-constexpr int kQueue = 128;     // survivor ring: current batch + prefetched batch + one culling round
+constexpr int kBatch = GSTEX_FWD_BATCH;       // records per stage (<= 32: one TMA bulk copy per lane)
+constexpr int kQueue = 128;                   // survivor ring: batch being composited + batch in flight + the next one
+                                              // filling + one culling round <= 3 * kBatch + 31 entries
+static_assert(kBatch <= 32 && 3 * kBatch + 31 <= kQueue, "survivor ring too small");
 
 struct FwdWarpShared {
     SplatRec rec[2][kBatch];  // 8 KB
