@@ -57,6 +57,11 @@ _SIGNATURES = {
     "gstex_compute_sh_forward": (I, [I, I, I, P, P, P, P]),
     "gstex_compute_sh_backward": (I, [I, I, I, P, P, P, P]),
     "gstex_texture_sample_forward": (I, [I, I, P, P, P, P, P]),
+    "gstex_chart_max_candidates": (I, []),
+    "gstex_chart_scores": (I, [I, P, F, I, P, ctypes.c_uint, P, P]),
+    "gstex_chart_dims": (I, [I, P, F, F, P, P, P, P]),
+    "gstex_chart_starts": (I, [I, P, P, P, P]),
+    "gstex_texture_resample": (I, [ctypes.c_longlong, I, I, P, P, P, P, P]),
     "gstex_activations_forward": (I, [I] + [P] * 11),
     "gstex_activations_backward": (I, [I] + [P] * 12),
     "gstex_texture_edit": (I, [I, I, I, I, I, I, ctypes.c_longlong] + [P] * 10 + [F] + [P] * 6 + [F, F, F, F, I] + [P, P, SZ, P]),
@@ -105,7 +110,7 @@ class _TimedLib:
                                                                                "gstex_launch_count", "gstex_debug_force_nocull", "gstex_debug_forward_variant",
                                                                                "gstex_pair_stream_supported",
                                                                                "gstex_tile_bucket_max_list", "gstex_tile_bucket_max_tiles",
-                                                                               "gstex_cumsum_noalloc_max_n"):
+                                                                               "gstex_cumsum_noalloc_max_n", "gstex_chart_max_candidates"):
             return fn
 
         def call(*args):

@@ -298,6 +298,27 @@ int gstex_activations_backward(int n, const float* quats_raw, const float* scale
 int gstex_texture_sample_forward(int num_queries, int channels, const int32_t* texture_dims, const float* uvs,
                                  const float* texture, float* out, void* stream);
 
+/* ref: /root/reference/nerfstudio/models/gstex.py:841-888 build_charts -- the texel-size bisection and what follows it.
+ *   gstex_chart_scores: for up to gstex_chart_max_candidates() = 32 candidate texel sizes x_k (a HOST array) at once,
+ *     scores[k] = sum_i ceil(sigma_factor * exp(s_i0) / x_k) * ceil(sigma_factor * exp(s_i1) / x_k)  (get_score, :847-849;
+ *     device doubles, exact: every term is an integer).  Bit k of recip_mask: divide the way `tensor / python_float` does
+ *     (the reference's first score, :859) instead of `tensor / tensor` (every later one, :868).  scales_raw (n,3) logs.
+ *   gstex_chart_dims: texture_dims[:, 0:2] = ceil(sigma_factor * exp(s) / texel_size) (:876-877), hw[i] = h * w,
+ *     mappings (n,2) = 1 / (2 * sigma_factor * exp(s)) (:882-883; may be NULL).
+ *   gstex_chart_starts: texture_dims[:, 2] = cum_hw - hw (:878-879; cum_hw = gstex_cumsum_i32 of hw). */
+int gstex_chart_max_candidates(void);
+int gstex_chart_scores(int n, const float* scales_raw, float sigma_factor, int num_candidates,
+                       const float* texel_sizes_host, unsigned recip_mask, double* scores, void* stream);
+int gstex_chart_dims(int n, const float* scales_raw, float sigma_factor, float texel_size, int32_t* texture_dims,
+                     int32_t* hw, float* mappings, void* stream);
+int gstex_chart_starts(int n, const int32_t* cum_hw, const int32_t* hw, int32_t* texture_dims, void* stream);
+/* ref: /root/reference/nerfstudio/models/jagged_texture.py:116-143 JaggedTexture.init_from_dims (+ texture_dims_to_query,
+ * :23-35): new_texture (num_new_texels, C), every texel the bilinear sample of its splat's OLD chart at the texel's
+ * integer coordinate over the new chart size.  new_dims / old_dims (n,3) int32 {h, w, start}; nothing per-texel is
+ * materialised (the reference builds ids, query_dims and uv tensors: 28 bytes per texel). */
+int gstex_texture_resample(long long num_new_texels, int n, int channels, const int32_t* new_dims, const int32_t* old_dims,
+                           const float* old_texture, float* new_texture, void* stream);
+
 /* ---- next row: texture editing (splat-painting of a canvas into the charts) ----- */
 
 /* ref: cuda/csrc/texture_edit.cu:238-346 texture_edit_tensor -> kernel :11-236 (bound at cuda/csrc/ext.cpp, called by
