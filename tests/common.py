@@ -120,7 +120,8 @@ def compare_all(ours, ref, settings, fwd_rtol, grad_rtol, what, max_flip_frac=2e
         atol = reg_atol(ref, settings) if k == "out_reg" else 0.0
         frac, relmax, scale = err_stats(ours[k], ref[k], rtol, atol)
         size = np.asarray(ref[k]).size
-        allowed = max(max_flip_frac * (10 if is_grad else 1), min_flip_count / max(size, 1))
+        # round 2: gradients get the same allowance as images (round 1 allowed ten times more)
+        allowed = max(max_flip_frac, min_flip_count / max(size, 1))
         rows.append(f"{what}{k:12s} scale {scale:9.3e} max|err|/scale {relmax:9.2e} outside {frac:8.2e} (allowed {allowed:7.1e})")
         if frac > allowed:
             fails.append(rows[-1])
