@@ -32,6 +32,7 @@ from gstex_b200.multiview import GradientBucket, shard_views  # noqa: E402
 METRIC = "fwd+bwd Mpix/s, 1M textured splats @800x800 (project+bin+sort+forward+backward)"
 UNIT = "Mpix/s"
 OWN_BINNING_STREAM = True  # --binning-stream own|current
+TEXEL_LOADS_128 = True     # --texel-loads scalar|128
 PARAM_KEYS = ["colors", "opacities", "means", "scales", "quats", "uv0", "umap", "vmap", "texture"]
 VOUT_KEYS = ["v_out_img", "v_out_depth", "v_out_reg", "v_out_alpha", "v_out_texture", "v_out_normal"]
 
@@ -50,6 +51,9 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--binning-stream", default="own", choices=["own", "current"],
                     help="next view's projection + binning on a stream of their own (default) or on the current stream (A/B)")
+    ap.add_argument("--texel-loads", default="128", choices=["scalar", "128"],
+                    help="128: the texture is padded to (T, 4) once per step (inside the timed region) and every view's "
+                         "forward fetches texels with 128-bit loads (gstex_b200.pad_texture)")
     return ap.parse_args()
 
 
@@ -148,6 +152,7 @@ class Workload:
         self.feeder = None
         self.binning = None  # BinningStream: the next view's projection + binning beside this view's compositing
         self.bucket = None  # one flat gradient buffer: fused accumulation, one all-reduce per step
+        self.padded = None  # --texel-loads 128: (T, 4) copy of the texture, refreshed at the start of every step
 
     def prep_view(self, viewmat, first=False):
         """Projection + the asynchronous half of the binning of one view (no host synchronisation), on the binning
@@ -170,7 +175,7 @@ class Workload:
         return G.texture_gaussians(s["texture_info"], self.texture_dims, centers, extents, depths, nth, p["colors"],
                                    p["opacities"], p["means"], p["scales"], 1, p["quats"], p["uv0"], p["umap"],
                                    p["vmap"], p["texture"], viewmat, c2w, *self.intr, self.H, self.W, self.bw,
-                                   s["settings"], self.background, binning=binning)
+                                   s["settings"], self.background, binning=binning, texture_padded=self.padded)
 
     def backward_view(self, outs, v):
         self.torch.autograd.backward(list(outs), [v["v_out_img"], v["v_out_depth"], v["v_out_reg"], v["v_out_alpha"],
@@ -183,6 +188,10 @@ class Workload:
             self.bucket = GradientBucket(list(self.params.values()))
             self.bucket.register()
         self.bucket.zero_()
+        if TEXEL_LOADS_128:  # the parameters change between steps: the padded copy is part of every step's work
+            import gstex_b200 as G
+
+            self.padded = G.pad_texture(self.params["texture"], out=self.padded)
 
     def reduce_grads(self, world):
         self.bucket.allreduce(world)
@@ -414,11 +423,12 @@ def ncu_capture(kernel_key):
 
 
 def main():
-    global OWN_BINNING_STREAM
+    global OWN_BINNING_STREAM, TEXEL_LOADS_128
     args = parse_args()
     # second stream at every N: measured on one 8xB200 box (profiles/bench_r2_s1_n8_{own,current}.json) 3594 vs 3467 Mpix/s at
     # 8 ranks, 498 vs 470 at one (round 1 needed a switch at 8 ranks; gone with the cheaper per-view host path)
     OWN_BINNING_STREAM = args.binning_stream == "own"
+    TEXEL_LOADS_128 = args.texel_loads == "128"
     # stdout carries ONE JSON line and nothing else: libraries that log to file descriptor 1 (NCCL's version banner and
     # NCCL_DEBUG output go to stdout) are sent to stderr for the whole run, the line is written to the saved descriptor
     sys.stdout.flush()
@@ -546,6 +556,7 @@ def main():
         "config": {"workload": f"{args.config}: {N} splats, {T} texels (C={C}), {W}x{H}, {args.views_per_gpu} views/GPU/step, "
                                f"fwd+bwd, settings {s['settings']}", "views_per_gpu": args.views_per_gpu,
                    "intersections_view0": I, "mean_tile_list": I / tiles, "ms_per_view": ms_per_step / args.views_per_gpu,
+                   "texel_loads": "128-bit from a (T,4) copy padded once per step inside the timed region" if TEXEL_LOADS_128 else "scalar",
                    "l2": "working set (texture+texel grads+records ~400 MB) exceeds the 126 MB L2; no explicit flush",
                    "parallelism": f"views sharded over {world} GPU(s), one NCCL all-reduce of the flat gradient bucket (9 tensors)" if world > 1
                    else "single GPU"},

@@ -50,6 +50,9 @@ _SIGNATURES = {
                                [P, SZ, I, P, SZ, P, SZ, ctypes.c_longlong, I, P]),
     "gstex_texture_forward_act": (I, [I, I, I, I, I, I] + [P] * 7 + [F] + [P] * 5 + [F, F] + [P] * 2 + [F, F, F, F, I] +
                                   [P] * 10 + [P, SZ, P, SZ, P]),
+    "gstex_texture_forward_padded": (I, [I, I, I, I, I, I] + [P] * 7 + [F] + [P] * 6 + [F, F] + [P] * 2 + [F, F, F, F, I] +
+                                     [P] * 10 + [P, SZ, P, SZ, P]),
+    "gstex_texture_pad4": (I, [ctypes.c_longlong, I, P, P, P]),
     "gstex_texture_backward_act": (I, [I, I, I, I, I, I] + [P] * 7 + [F] + [P] * 5 + [F, F] + [P] * 2 + [F, F, F, F, I] +
                                    [P] * 11 + [P] * 9 + [P, SZ, I, P, SZ, P, SZ, ctypes.c_longlong, I, P]),
     "gstex_grad_scratch_bytes": (SZ, [I, ctypes.c_longlong]),

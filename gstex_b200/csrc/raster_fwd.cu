@@ -197,13 +197,21 @@ __global__ void __launch_bounds__(kFwdWarps * 32, kFwdCtasPerSm) texture_forward
                 const float4 r4 = rr.q[4];
                 const int start = __float_as_int(rr.q[5].w);
                 const TexQuery tq = tex_query(__float_as_int(r4.z), __float_as_int(r4.w), start, ent.z, ent.w, bilinear);
-                const float* t00 = p.texture + (size_t)tq.b00 * C;
-                const float* t01 = p.texture + (size_t)tq.b01 * C;
-                const float* t10 = p.texture + (size_t)tq.b10 * C;
-                const float* t11 = p.texture + (size_t)tq.b11 * C;
-                val0 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00), __ldg(t01), __ldg(t10), __ldg(t11));
-                if (C > 1) val1 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00 + 1), __ldg(t01 + 1), __ldg(t10 + 1), __ldg(t11 + 1));
-                if (C > 2) val2 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00 + 2), __ldg(t01 + 2), __ldg(t10 + 2), __ldg(t11 + 2));
+                if (p.texture4 != nullptr) {  // padded layout: one 128-bit load per corner instead of C scalar loads
+                    const float4 a = __ldg(p.texture4 + tq.b00), b = __ldg(p.texture4 + tq.b01);
+                    const float4 c = __ldg(p.texture4 + tq.b10), d = __ldg(p.texture4 + tq.b11);
+                    val0 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, a.x, b.x, c.x, d.x);
+                    if (C > 1) val1 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, a.y, b.y, c.y, d.y);
+                    if (C > 2) val2 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, a.z, b.z, c.z, d.z);
+                } else {
+                    const float* t00 = p.texture + (size_t)tq.b00 * C;
+                    const float* t01 = p.texture + (size_t)tq.b01 * C;
+                    const float* t10 = p.texture + (size_t)tq.b10 * C;
+                    const float* t11 = p.texture + (size_t)tq.b11 * C;
+                    val0 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00), __ldg(t01), __ldg(t10), __ldg(t11));
+                    if (C > 1) val1 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00 + 1), __ldg(t01 + 1), __ldg(t10 + 1), __ldg(t11 + 1));
+                    if (C > 2) val2 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00 + 2), __ldg(t01 + 2), __ldg(t10 + 2), __ldg(t11 + 2));
+                }
                 // affine texel activation (SH2RGB of the caller folded into the fetch; the weights sum to one);
                 // (1, 0) leaves the sample bit for bit
                 val0 = __fmaf_rn(p.tex_scale, val0, p.tex_bias);
@@ -470,12 +478,12 @@ extern "C" size_t gstex_pair_stream_bytes(int img_height, int img_width, int blo
     return stream_fixed_bytes((int)units) + 256 + chunks * (sizeof(PairItem) * kChunkItems + sizeof(int32_t)) + 128;
 }
 
-extern "C" int gstex_texture_forward_act(int img_height, int img_width, int block_width, int channels, int n,
+static int forward_impl(int img_height, int img_width, int block_width, int channels, int n,
                                      int num_intersects, const int32_t* texture_dims,
                                      const int32_t* gaussian_ids_sorted, const int32_t* tile_bins, const float* colors,
                                      const float* opacities, const float* means, const float* scales, float glob_scale,
                                      const float* quats, const float* uv0, const float* umap, const float* vmap,
-                                     const float* texture, float tex_scale, float tex_bias, const float* viewmat, const float* c2w, float fx, float fy,
+                                     const float* texture, const float* texture4, float tex_scale, float tex_bias, const float* viewmat, const float* c2w, float fx, float fy,
                                      float cx, float cy, int settings, const float* background, float* out_img,
                                      float* out_depth, float* out_reg, float* out_texture, float* out_normal,
                                      float* final_Ts, int32_t* final_idx, int32_t* depth_idx, float* out_reg_s,
@@ -510,7 +518,8 @@ extern "C" int gstex_texture_forward_act(int img_height, int img_width, int bloc
     p.recs = n > 0 ? ws_recs(workspace) : nullptr;
     p.boxes = n > 0 ? ws_boxes(workspace, n) : nullptr;
     p.ids = gaussian_ids_sorted; p.tile_bins = reinterpret_cast<const int2*>(tile_bins);
-    p.texture = texture; p.viewmat = viewmat; p.c2w = c2w; p.background = background;
+    if (texture4 != nullptr && (channels > 3 || ((uintptr_t)texture4 & 15))) return GSTEX_E_BADARG;
+    p.texture = texture; p.texture4 = reinterpret_cast<const float4*>(texture4); p.viewmat = viewmat; p.c2w = c2w; p.background = background;
     p.fx = fx; p.fy = fy; p.cx = cx; p.cy = cy; p.settings = settings;
     p.out_img = out_img; p.out_depth = out_depth; p.out_reg = out_reg; p.out_texture = out_texture;
     p.out_normal = out_normal; p.final_Ts = final_Ts; p.out_reg_s = out_reg_s; p.final_idx = final_idx;
@@ -558,16 +567,58 @@ extern "C" int gstex_texture_forward_act(int img_height, int img_width, int bloc
     return GSTEX_OK;
 }
 
-extern "C" int gstex_texture_forward(int img_height, int img_width, int block_width, int channels, int n,
-                                     int num_intersects, const int32_t* texture_dims,
-                                     const int32_t* gaussian_ids_sorted, const int32_t* tile_bins, const float* colors,
-                                     const float* opacities, const float* means, const float* scales, float glob_scale,
-                                     const float* quats, const float* uv0, const float* umap, const float* vmap,
-                                     const float* texture, const float* viewmat, const float* c2w, float fx, float fy,
-                                     float cx, float cy, int settings, const float* background, float* out_img,
-                                     float* out_depth, float* out_reg, float* out_texture, float* out_normal,
-                                     float* final_Ts, int32_t* final_idx, int32_t* depth_idx, float* out_reg_s,
-                                     void* workspace, size_t workspace_bytes, void* pair_stream,
-                                     size_t pair_stream_bytes, void* stream) {
-    return gstex_texture_forward_act(img_height, img_width, block_width, channels, n, num_intersects, texture_dims, gaussian_ids_sorted, tile_bins, colors, opacities, means, scales, glob_scale, quats, uv0, umap, vmap, texture, 1.f, 0.f, viewmat, c2w, fx, fy, cx, cy, settings, background, out_img, out_depth, out_reg, out_texture, out_normal, final_Ts, final_idx, depth_idx, out_reg_s, workspace, workspace_bytes, pair_stream, pair_stream_bytes, stream);
+#define GSTEX_FWD_SIG_HEAD                                                                                            \
+    int img_height, int img_width, int block_width, int channels, int n, int num_intersects,                         \
+        const int32_t *texture_dims, const int32_t *gaussian_ids_sorted, const int32_t *tile_bins, const float *colors, \
+        const float *opacities, const float *means, const float *scales, float glob_scale, const float *quats,       \
+        const float *uv0, const float *umap, const float *vmap, const float *texture
+#define GSTEX_FWD_SIG_TAIL                                                                                            \
+    const float *viewmat, const float *c2w, float fx, float fy, float cx, float cy, int settings,                    \
+        const float *background, float *out_img, float *out_depth, float *out_reg, float *out_texture,               \
+        float *out_normal, float *final_Ts, int32_t *final_idx, int32_t *depth_idx, float *out_reg_s, void *workspace, \
+        size_t workspace_bytes, void *pair_stream, size_t pair_stream_bytes, void *stream
+#define GSTEX_FWD_ARGS_HEAD                                                                                           \
+    img_height, img_width, block_width, channels, n, num_intersects, texture_dims, gaussian_ids_sorted, tile_bins,   \
+        colors, opacities, means, scales, glob_scale, quats, uv0, umap, vmap, texture
+#define GSTEX_FWD_ARGS_TAIL                                                                                           \
+    viewmat, c2w, fx, fy, cx, cy, settings, background, out_img, out_depth, out_reg, out_texture, out_normal,        \
+        final_Ts, final_idx, depth_idx, out_reg_s, workspace, workspace_bytes, pair_stream, pair_stream_bytes, stream
+
+extern "C" int gstex_texture_forward(GSTEX_FWD_SIG_HEAD, GSTEX_FWD_SIG_TAIL) {
+    return forward_impl(GSTEX_FWD_ARGS_HEAD, nullptr, 1.f, 0.f, GSTEX_FWD_ARGS_TAIL);
+}
+
+extern "C" int gstex_texture_forward_act(GSTEX_FWD_SIG_HEAD, float tex_scale, float tex_bias, GSTEX_FWD_SIG_TAIL) {
+    return forward_impl(GSTEX_FWD_ARGS_HEAD, nullptr, tex_scale, tex_bias, GSTEX_FWD_ARGS_TAIL);
+}
+
+// The same forward with the texel fetch reading `texture4`, a (num_texels, 4) zero-padded copy of the (num_texels,
+// channels <= 3) texture made by gstex_texture_pad4: four 128-bit loads per contributing pair instead of 4 * channels
+// scalar ones.  Same arithmetic on the same values, so every output is bit-identical to gstex_texture_forward_act's.
+extern "C" int gstex_texture_forward_padded(GSTEX_FWD_SIG_HEAD, const float* texture4, float tex_scale, float tex_bias,
+                                            GSTEX_FWD_SIG_TAIL) {
+    if (!texture4) return GSTEX_E_BADARG;
+    return forward_impl(GSTEX_FWD_ARGS_HEAD, texture4, tex_scale, tex_bias, GSTEX_FWD_ARGS_TAIL);
+}
+
+namespace gstex {
+__global__ void __launch_bounds__(kThreads1D)
+texture_pad4_kernel(long long num_texels, int C, const float* __restrict__ texture, float4* __restrict__ texture4) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= num_texels) return;
+    const float* s = texture + (size_t)t * C;
+    texture4[t] = make_float4(s[0], C > 1 ? s[1] : 0.f, C > 2 ? s[2] : 0.f, 0.f);
+}
+}  // namespace gstex
+
+extern "C" int gstex_texture_pad4(long long num_texels, int channels, const float* texture, float* texture4, void* stream) {
+    if (num_texels < 0 || channels < 1 || channels > 3) return GSTEX_E_BADARG;
+    if (num_texels == 0) return GSTEX_OK;
+    if (!texture || !texture4 || ((uintptr_t)texture4 & 15)) return GSTEX_E_BADARG;
+    const long long blocks = (num_texels + kThreads1D - 1) / kThreads1D;
+    if (blocks > 0x7fffffffll) return GSTEX_E_TOO_LARGE;
+    gstex::texture_pad4_kernel<<<(unsigned)blocks, kThreads1D, 0, (cudaStream_t)stream>>>(
+        num_texels, channels, texture, reinterpret_cast<float4*>(texture4));
+    GSTEX_LAUNCH_CHECK();
+    return GSTEX_OK;
 }

@@ -14,6 +14,7 @@ struct FwdParams {
     const int32_t* ids;
     const int2* tile_bins;
     const float* texture;
+    const float4* texture4;  // optional (T,4) zero-padded copy of a <= 3-channel texture: 16-byte texel fetches (else nullptr)
     const float *viewmat, *c2w, *background;
     float fx, fy, cx, cy;
     int settings;

@@ -239,13 +239,21 @@ __global__ void __launch_bounds__(kDWarps * 32, kDCtasPerSm) texture_forward_den
                     const float4 r4 = rr.q[4];
                     const int start = __float_as_int(rr.q[5].w);
                     const TexQuery tq = tex_query(__float_as_int(r4.z), __float_as_int(r4.w), start, u, v, bilinear);
-                    const float* t00 = p.texture + (size_t)tq.b00 * C;
-                    const float* t01 = p.texture + (size_t)tq.b01 * C;
-                    const float* t10 = p.texture + (size_t)tq.b10 * C;
-                    const float* t11 = p.texture + (size_t)tq.b11 * C;
-                    val0 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00), __ldg(t01), __ldg(t10), __ldg(t11));
-                    if (C > 1) val1 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00 + 1), __ldg(t01 + 1), __ldg(t10 + 1), __ldg(t11 + 1));
-                    if (C > 2) val2 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00 + 2), __ldg(t01 + 2), __ldg(t10 + 2), __ldg(t11 + 2));
+                    if (p.texture4 != nullptr) {  // padded layout: one 128-bit load per corner
+                        const float4 a = __ldg(p.texture4 + tq.b00), b = __ldg(p.texture4 + tq.b01);
+                        const float4 c = __ldg(p.texture4 + tq.b10), d = __ldg(p.texture4 + tq.b11);
+                        val0 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, a.x, b.x, c.x, d.x);
+                        if (C > 1) val1 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, a.y, b.y, c.y, d.y);
+                        if (C > 2) val2 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, a.z, b.z, c.z, d.z);
+                    } else {
+                        const float* t00 = p.texture + (size_t)tq.b00 * C;
+                        const float* t01 = p.texture + (size_t)tq.b01 * C;
+                        const float* t10 = p.texture + (size_t)tq.b10 * C;
+                        const float* t11 = p.texture + (size_t)tq.b11 * C;
+                        val0 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00), __ldg(t01), __ldg(t10), __ldg(t11));
+                        if (C > 1) val1 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00 + 1), __ldg(t01 + 1), __ldg(t10 + 1), __ldg(t11 + 1));
+                        if (C > 2) val2 = bilinear_ref(tq.w00, tq.w01, tq.w10, tq.w11, __ldg(t00 + 2), __ldg(t01 + 2), __ldg(t10 + 2), __ldg(t11 + 2));
+                    }
                     // affine texel activation (SH2RGB of the caller folded into the fetch); (1, 0) leaves the sample as it is
                     val0 = __fmaf_rn(p.tex_scale, val0, p.tex_bias);
                     if (C > 1) val1 = __fmaf_rn(p.tex_scale, val1, p.tex_bias);

@@ -168,6 +168,7 @@ def texture_gaussians(
     *,
     binning: Optional[TileBinning] = None,
     texture_affine: Optional[Tuple[float, float]] = None,
+    texture_padded: Optional[Tensor] = None,
 ):
     """Rasterizes textured 2D gaussians (ref: texture.py:14-150).
 
@@ -179,7 +180,11 @@ def texture_gaussians(
     `scale * sample + bias`; the gradient returned for `texture` is with respect to the raw texels.  With
     `(C0, 0.5)` = `SH2RGB` this replaces the caller's `texture[:, 0:3] = SH2RGB(texture_dc)` (NS/models/gstex.py:
     1091-1121) -- two passes over all texels forward and two more backward per view -- by one multiply-add per
-    fetched sample."""
+    fetched sample.
+
+    `texture_padded` (not in the reference): `pad_texture(texture)`, the `(T, 4)` copy the forward then fetches with
+    one 128-bit load per bilinear corner; the outputs and gradients are bit-identical with or without it.  The caller
+    refreshes it whenever `texture` changes -- a stale copy renders the stale texels."""
     assert block_width > 1 and block_width <= 16, "block_width must be between 2 and 16"
     if use_torch_impl:
         raise NotImplementedError("gstex_b200 has no PyTorch/CPU rasterizer: the CUDA kernels are the only path")
@@ -203,12 +208,33 @@ def texture_gaussians(
         scales.contiguous(), glob_scale, quats.contiguous(), uv0.contiguous(), umap.contiguous(), vmap.contiguous(),
         texture.contiguous(), viewmat.contiguous(), c2w.contiguous(), fx, fy, cx, cy, img_height, img_width,
         block_width, settings, background.contiguous(), binning,
-        (1.0, 0.0) if texture_affine is None else (float(texture_affine[0]), float(texture_affine[1])))
+        (1.0, 0.0) if texture_affine is None else (float(texture_affine[0]), float(texture_affine[1])),
+        texture_padded)
+
+
+def pad_texture(texture: Tensor, out: Optional[Tensor] = None) -> Tensor:
+    """`(T, 4)` zero-padded copy of a `(T, C <= 3)` texture for `texture_gaussians(..., texture_padded=...)`: one pass
+    over the texels (28 bytes each at C = 3), once per optimiser step for all the views of a batch.  Detached."""
+    texture = texture.detach().contiguous()
+    dev = _lib.require_cuda(texture)
+    _lib.require_dtype(texture, torch.float32, "texture")
+    if texture.dim() != 2 or not 1 <= texture.shape[1] <= 3:
+        raise ValueError("pad_texture takes a (T, C) texture with 1 <= C <= 3")
+    T = texture.shape[0]
+    if out is None:
+        out = torch.empty((T, 4), dtype=torch.float32, device=dev)
+    elif tuple(out.shape) != (T, 4) or out.dtype != torch.float32 or out.device != dev or not out.is_contiguous():
+        raise ValueError("out must be a contiguous float32 (T, 4) tensor on the texture's device")
+    with torch.cuda.device(dev):
+        rc = _lib.load().gstex_texture_pad4(T, texture.shape[1], _lib.ptr(texture), _lib.ptr(out), _lib.stream_ptr(dev))
+    _lib.check(rc, "gstex_texture_pad4")
+    return out
 
 
 def _raster_forward(texture_info, texture_dims, gaussian_ids_sorted, tile_bins, colors, opacity, means, scales,
                     glob_scale, quats, uv0, umap, vmap, texture, viewmat, c2w, fx, fy, cx, cy, img_height, img_width,
-                    block_width, settings, background, num_intersects, record_pairs=False, texture_affine=(1.0, 0.0)):
+                    block_width, settings, background, num_intersects, record_pairs=False, texture_affine=(1.0, 0.0),
+                    texture_padded=None):
     """ref: `_C.texture_forward` (cuda/csrc/texture.cu:762-901).  Returns the 9 tensors + the workspace
     holding the per-view packed records (re-used by the backward)."""
     dev = _lib.require_cuda(texture_dims, colors, opacity, means, scales, quats, uv0, umap, vmap, texture, viewmat,
@@ -241,11 +267,18 @@ def _raster_forward(texture_info, texture_dims, gaussian_ids_sorted, tile_bins, 
             nbytes = min(nbytes, int(PairStreamPolicy.max_bytes))
         pairs = torch.empty((nbytes,), dtype=torch.uint8, device=dev)
     p = _lib.ptr
+    if texture_padded is not None:
+        if (tuple(texture_padded.shape) != (texture.shape[0], 4) or C > 3 or texture_padded.dtype != torch.float32
+                or texture_padded.device != dev or not texture_padded.is_contiguous()):
+            raise ValueError("texture_padded must be pad_texture(texture): contiguous float32 (T, 4) on the same device")
+        fwd, tex_args = lib.gstex_texture_forward_padded, (p(texture), p(texture_padded))
+    else:
+        fwd, tex_args = lib.gstex_texture_forward_act, (p(texture),)
     with torch.cuda.device(dev):
-        rc = lib.gstex_texture_forward_act(
+        rc = fwd(
             H, W, int(block_width), C, n, int(num_intersects), p(texture_dims), p(gaussian_ids_sorted), p(tile_bins),
             p(colors), p(opacity), p(means), p(scales), float(glob_scale), p(quats), p(uv0), p(umap), p(vmap),
-            p(texture), float(texture_affine[0]), float(texture_affine[1]), p(viewmat), p(c2w), float(fx), float(fy),
+            *tex_args, float(texture_affine[0]), float(texture_affine[1]), p(viewmat), p(c2w), float(fx), float(fy),
             float(cx), float(cy), int(settings), p(background),
             p(out_img), p(out_depth), p(out_reg), p(out_texture), p(out_normal), p(final_Ts), p(final_idx),
             p(depth_idx), p(out_reg_s), p(ws), ws.numel(), p(pairs), pairs.numel() if pairs is not None else 0,
@@ -262,7 +295,8 @@ class _TextureGaussians(Function):
     @staticmethod
     def forward(ctx, texture_info, texture_dims, centers, extents, depths, num_tiles_hit, colors, opacity, means,
                 scales, glob_scale, quats, uv0, umap, vmap, texture, viewmat, c2w, fx, fy, cx, cy, img_height,
-                img_width, block_width, settings, background=None, binning=None, texture_affine=(1.0, 0.0)):
+                img_width, block_width, settings, background=None, binning=None, texture_affine=(1.0, 0.0),
+                texture_padded=None):
         num_points = centers.size(0)
         tile_bounds = ((img_width + block_width - 1) // block_width, (img_height + block_width - 1) // block_width, 1)
         dev = centers.device
@@ -277,7 +311,8 @@ class _TextureGaussians(Function):
                                              opacity, means, scales, glob_scale, quats, uv0, umap, vmap, texture,
                                              viewmat, c2w, fx, fy, cx, cy, img_height, img_width, block_width,
                                              settings, background, max(num_intersects, 0),
-                                             record_pairs=any(ctx.needs_input_grad), texture_affine=texture_affine)
+                                             record_pairs=any(ctx.needs_input_grad), texture_affine=texture_affine,
+                                             texture_padded=texture_padded)
         out_img, out_depth, out_reg, out_texture, out_normal, final_Ts, final_idx, depth_idx, out_reg_s = outputs
         ctx.img_width, ctx.img_height = img_width, img_height
         ctx.texture_info = texture_info
@@ -384,6 +419,7 @@ class _TextureGaussians(Function):
                 _GRAD_SCRATCH.clear()
             _GRAD_SCRATCH[scratch_key] = scratch
         if targets is not None:  # already added to the registered tensors
-            return (None,) * 29
+            return (None,) * 30
         return (None, None, None, None, None, None, v_colors, v_opacity, v_means, v_scales, None, v_quats, v_uv0,
-                v_umap, v_vmap, v_texture, None, None, None, None, None, None, None, None, None, None, None, None, None)
+                v_umap, v_vmap, v_texture, None, None, None, None, None, None, None, None, None, None, None, None, None,
+                None)

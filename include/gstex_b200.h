@@ -239,6 +239,25 @@ int gstex_texture_forward_act(int img_height, int img_width, int block_width, in
                           float* out_depth, float* out_reg, float* out_texture, float* out_normal, float* final_Ts,
                           int32_t* final_idx, int32_t* depth_idx, float* out_reg_s, void* workspace,
                           size_t workspace_bytes, void* pair_stream, size_t pair_stream_bytes, void* stream);
+/* gstex_texture_forward_act with the texel fetch reading `texture4`, a (num_texels, 4) zero-padded, 16-byte aligned
+ * copy of the (num_texels, channels <= 3) `texture` written by gstex_texture_pad4: one 128-bit load per bilinear
+ * corner instead of `channels` scalar loads (the "128-bit texel loads" of BASELINE.json's north star).  The
+ * arithmetic and its inputs are the same, so every output is bit-identical to gstex_texture_forward_act's.  The caller
+ * owns the copy and refreshes it whenever `texture` changes (once per optimiser step for a multi-view batch); the
+ * backward takes the unpadded texture.  No counterpart in the reference, whose kernels query the chart once per channel,
+ * four scalar loads each (texture.cu:260-268, query_jagged_chart). */
+int gstex_texture_forward_padded(int img_height, int img_width, int block_width, int channels, int n, int num_intersects,
+                          const int32_t* texture_dims, const int32_t* gaussian_ids_sorted, const int32_t* tile_bins,
+                          const float* colors, const float* opacities, const float* means, const float* scales,
+                          float glob_scale, const float* quats, const float* uv0, const float* umap,
+                          const float* vmap, const float* texture, const float* texture4, float tex_scale,
+                          float tex_bias, const float* viewmat, const float* c2w, float fx,
+                          float fy, float cx, float cy, int settings, const float* background, float* out_img,
+                          float* out_depth, float* out_reg, float* out_texture, float* out_normal, float* final_Ts,
+                          int32_t* final_idx, int32_t* depth_idx, float* out_reg_s, void* workspace,
+                          size_t workspace_bytes, void* pair_stream, size_t pair_stream_bytes, void* stream);
+/* texture4[t] = (texture[t][0], texture[t][1] or 0, texture[t][2] or 0, 0) for channels in 1..3. */
+int gstex_texture_pad4(long long num_texels, int channels, const float* texture, float* texture4, void* stream);
 int gstex_texture_backward_act(int img_height, int img_width, int block_width, int channels, int n, int num_intersects,
                            const int32_t* texture_dims, const int32_t* gaussian_ids_sorted, const int32_t* tile_bins,
                            const float* colors, const float* opacities, const float* means, const float* scales,

@@ -18,10 +18,24 @@ _, depths, centers, extents, nth = G.project_bounds(sd["means"], sd["scales"], 1
 tb = ((W + bw - 1) // bw, (H + bw - 1) // bw, 1)
 I, ids, bins = G.bin_gaussians_to_tiles(s["N"], centers, extents, depths, nth, tb, bw)
 lib = _lib.load()
-def fwd(rec):
+padded = G.pad_texture(sd["texture"]) if s["texture_info"][2] <= 3 else None
+def fwd(rec, pad=False):
     return T._raster_forward(s["texture_info"], sd["texture_dims"], ids, bins, sd["colors"], sd["opacities"], sd["means"], sd["scales"], 1,
                              sd["quats"], sd["uv0"], sd["umap"], sd["vmap"], sd["texture"], sd["viewmat"], sd["c2w"], *intr, H, W, bw,
-                             s["settings"], sd["background"], I, record_pairs=rec)
+                             s["settings"], sd["background"], I, record_pairs=rec, texture_padded=padded if pad else None)
+ts = []
+for it in range(25):
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(); G.pad_texture(sd["texture"], out=padded); e1.record(); torch.cuda.synchronize()
+    if it >= 5: ts.append(e0.elapsed_time(e1))
+print(f"{name}: pad_texture of {sd['texture'].shape[0]} texels median {statistics.median(ts):.3f} ms", flush=True)
+for pad in (False, True, False, True):
+    ts = []
+    for it in range(45):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); out = fwd(True, pad); e1.record(); torch.cuda.synchronize()
+        if it >= 5: ts.append(e0.elapsed_time(e1))
+    print(f"{name} texel loads {'128-bit' if pad else 'scalar '}: forward entry median {statistics.median(ts):.4f} ms  min {min(ts):.4f}", flush=True)
 for v in variants:
     lib.gstex_debug_forward_variant(v)
     for rec in (True, False):

@@ -58,8 +58,9 @@ def test_python_surface_mirrors_reference():
                "cx", "cy", "img_height", "img_width", "block_width", "settings", "background", "use_torch_impl"]
     params = inspect.signature(G.texture_gaussians).parameters
     assert [k for k, v in params.items() if v.kind != v.KEYWORD_ONLY] == ref_sig  # texture.py:14-43
-    # ours, keyword-only: the multi-view pipelining hook and the fused texel activation
-    assert [k for k, v in params.items() if v.kind == v.KEYWORD_ONLY] == ["binning", "texture_affine"]
+    # ours, keyword-only: the multi-view pipelining hook, the fused texel activation
+    # and the (T, 4) texture copy for 128-bit texel loads
+    assert [k for k, v in params.items() if v.kind == v.KEYWORD_ONLY] == ["binning", "texture_affine", "texture_padded"]
     assert list(inspect.signature(G.get_aabb_2d).parameters) == ["means", "scales", "glob_scale", "quats", "viewmat", "intrins"]
     assert list(inspect.signature(G.get_num_tiles_hit_2d).parameters) == ["centers", "extents", "img_height", "img_width", "block_width"]
     assert list(inspect.signature(G.project_points).parameters)[:3] == ["points", "viewmat", "intrins"]

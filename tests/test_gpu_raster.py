@@ -480,3 +480,62 @@ def test_texture_affine_matches_activated_texture(backward_path):
         err = float((a - b).abs().max())
         assert err <= 3e-5 * scale + 1e-30, f"{k}: fused activation differs ({err:.3e} at scale {scale:.3e})"
     assert float(g_ref[8].abs().max()) > 0
+
+
+@pytest.mark.parametrize("channels", [3, 1])
+@pytest.mark.parametrize("affine", [None, (0.28209479177387814, 0.5)], ids=["plain", "affine"])
+def test_padded_texture_forward_is_bit_identical(channels, affine, backward_path):
+    """`texture_padded=pad_texture(texture)` only changes HOW the four bilinear corners are loaded (one 128-bit load
+    each instead of `channels` scalar ones): all six images bit for bit, and the gradients -- computed from the same
+    recorded pairs -- within the atomics' reordering noise."""
+    import gstex_b200 as G
+    from gstex_b200.synthetic import make_scene, make_upstream_grads
+
+    s = make_scene("cfg2", n=20000, width=256, height=256)
+    v = {k: x.cuda() for k, x in make_upstream_grads(s).items()}
+    sd = {k: (x.cuda() if isinstance(x, torch.Tensor) else x) for k, x in s.items()}
+    intr = (s["fx"], s["fy"], s["cx"], s["cy"])
+    H, W, bw = s["H"], s["W"], 16
+    keys = ["colors", "opacities", "means", "scales", "quats", "uv0", "umap", "vmap", "texture"]
+    info = (s["texture_info"][0], s["texture_info"][1], channels)
+    tex0 = sd["texture"][:, :channels].contiguous()
+    vm, c2w = s["viewmats"][0].cuda().contiguous(), s["c2ws"][0].cuda().contiguous()
+    padded = G.pad_texture(tex0)
+    assert padded.shape == (tex0.shape[0], 4)
+    assert torch.equal(padded[:, :channels], tex0) and not padded[:, channels:].any()
+
+    def run(use_padded):
+        pd = {k: sd[k].clone().requires_grad_(True) for k in keys}
+        pd["texture"] = tex0.clone().requires_grad_(True)
+        _, depths, centers, extents, nth = G.project_bounds(pd["means"].detach(), pd["scales"].detach(), 1,
+                                                            pd["quats"].detach(), vm, intr, H, W, bw)
+        outs = G.texture_gaussians(info, sd["texture_dims"], centers, extents, depths, nth, pd["colors"],
+                                   pd["opacities"], pd["means"], pd["scales"], 1, pd["quats"], pd["uv0"], pd["umap"],
+                                   pd["vmap"], pd["texture"], vm, c2w, *intr, H, W, bw, s["settings"], sd["background"],
+                                   texture_affine=affine, texture_padded=padded if use_padded else None)
+        torch.autograd.backward(list(outs), [v["v_out_img"], v["v_out_depth"], v["v_out_reg"], v["v_out_alpha"],
+                                             v["v_out_texture"][..., :channels].contiguous(), v["v_out_normal"]])
+        return [o.detach() for o in outs], [pd[k].grad for k in keys]
+
+    (o_ref, g_ref), (o_pad, g_pad) = run(False), run(True)
+    for nm, a, b in zip(["out_img", "out_depth", "out_reg", "out_alpha", "out_texture", "out_normal"], o_ref, o_pad):
+        assert torch.equal(a, b), f"{nm}: {int((a != b).sum())} elements differ with the padded texture"
+    for k, a, b in zip(keys, g_ref, g_pad):
+        scale = float(a.abs().max())
+        assert float((a - b).abs().max()) <= 3e-5 * scale + 1e-30, k
+    assert float(g_ref[8].abs().max()) > 0
+
+
+def test_padded_texture_errors_are_loud():
+    import gstex_b200 as G
+    from gstex_b200 import _lib
+
+    with pytest.raises(ValueError):
+        G.pad_texture(torch.zeros(10, 4, device="cuda"))
+    with pytest.raises(ValueError):
+        G.pad_texture(torch.zeros(10, 3, device="cuda"), out=torch.zeros(9, 4, device="cuda"))
+    assert G.pad_texture(torch.zeros(0, 3, device="cuda")).shape == (0, 4)
+    lib = _lib.load()
+    t = torch.zeros(8, 4, device="cuda")
+    assert lib.gstex_texture_pad4(2, 4, _lib.ptr(t), _lib.ptr(t), None) == -1            # channels > 3
+    assert lib.gstex_texture_pad4(1, 3, _lib.ptr(t), t.data_ptr() + 4, None) == -1       # unaligned destination
