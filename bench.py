@@ -33,6 +33,7 @@ METRIC = "fwd+bwd Mpix/s, 1M textured splats @800x800 (project+bin+sort+forward+
 UNIT = "Mpix/s"
 OWN_BINNING_STREAM = True  # --binning-stream own|current
 TEXEL_LOADS_128 = True     # --texel-loads scalar|128
+ALLREDUCE = "auto"         # --allreduce auto|peer|multimem|nccl (N > 1)
 PARAM_KEYS = ["colors", "opacities", "means", "scales", "quats", "uv0", "umap", "vmap", "texture"]
 VOUT_KEYS = ["v_out_img", "v_out_depth", "v_out_reg", "v_out_alpha", "v_out_texture", "v_out_normal"]
 
@@ -51,6 +52,10 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--binning-stream", default="own", choices=["own", "current"],
                     help="next view's projection + binning on a stream of their own (default) or on the current stream (A/B)")
+    ap.add_argument("--allreduce", default="auto", choices=["auto", "peer", "multimem", "nccl"],
+                    help="N > 1: the gradient sum at the end of a step as our kernel over NVLink peer memory -- plain peer "
+                         "loads/stores, the NVSwitch-multicast variant, or whichever the library picks for N (default) -- "
+                         "or NCCL's all-reduce (A/B)")
     ap.add_argument("--texel-loads", default="128", choices=["scalar", "128"],
                     help="128: the texture is padded to (T, 4) once per step (inside the timed region) and every view's "
                          "forward fetches texels with 128-bit loads (gstex_b200.pad_texture)")
@@ -152,6 +157,7 @@ class Workload:
         self.feeder = None
         self.binning = None  # BinningStream: the next view's projection + binning beside this view's compositing
         self.bucket = None  # one flat gradient buffer: fused accumulation, one all-reduce per step
+        self.reduce_events = None  # list while the resident leg is timed
         self.padded = None  # --texel-loads 128: (T, 4) copy of the texture, refreshed at the start of every step
 
     def prep_view(self, viewmat, first=False):
@@ -185,7 +191,13 @@ class Workload:
         """Gradients of all nine parameter tensors live in one flat bucket; the backward of every view adds into it
         (GradientTargets), the step ends with one all-reduce when there are several ranks."""
         if self.bucket is None:
-            self.bucket = GradientBucket(list(self.params.values()))
+            group = None
+            if world > 1 and ALLREDUCE != "nccl":
+                import torch.distributed as dist
+
+                group = dist.group.WORLD
+            self.bucket = GradientBucket(list(self.params.values()), peer_group=group, peer_fallback=True,
+                                         multicast={"auto": None, "peer": False, "multimem": True}.get(ALLREDUCE))
             self.bucket.register()
         self.bucket.zero_()
         if TEXEL_LOADS_128:  # the parameters change between steps: the padded copy is part of every step's work
@@ -194,6 +206,13 @@ class Workload:
             self.padded = G.pad_texture(self.params["texture"], out=self.padded)
 
     def reduce_grads(self, world):
+        if self.reduce_events is not None:  # the resident leg times the exchange step (flush + sum over the ranks)
+            e0, e1 = self.torch.cuda.Event(enable_timing=True), self.torch.cuda.Event(enable_timing=True)
+            e0.record()
+            self.bucket.allreduce(world)
+            e1.record()
+            self.reduce_events.append((e0, e1))
+            return
         self.bucket.allreduce(world)
 
     def step(self, world):
@@ -423,12 +442,13 @@ def ncu_capture(kernel_key):
 
 
 def main():
-    global OWN_BINNING_STREAM, TEXEL_LOADS_128
+    global OWN_BINNING_STREAM, TEXEL_LOADS_128, ALLREDUCE
     args = parse_args()
     # second stream at every N: measured on one 8xB200 box (profiles/bench_r2_s1_n8_{own,current}.json) 3594 vs 3467 Mpix/s at
     # 8 ranks, 498 vs 470 at one (round 1 needed a switch at 8 ranks; gone with the cheaper per-view host path)
     OWN_BINNING_STREAM = args.binning_stream == "own"
     TEXEL_LOADS_128 = args.texel_loads == "128"
+    ALLREDUCE = args.allreduce
     # stdout carries ONE JSON line and nothing else: libraries that log to file descriptor 1 (NCCL's version banner and
     # NCCL_DEBUG output go to stdout) are sent to stderr for the whole run, the line is written to the saved descriptor
     sys.stdout.flush()
@@ -499,8 +519,14 @@ def main():
         launches0[0] = lib.gstex_launch_count()
         _lib.Timing.start()
 
-    ms_per_step, per_step = timed(lambda: wl.step(world), before=begin_timed_region)
+    def begin_resident():
+        begin_timed_region()
+        wl.reduce_events = []
+
+    ms_per_step, per_step = timed(lambda: wl.step(world), before=begin_resident)
     per_call = _lib.Timing.stop()
+    reduce_ms = [a.elapsed_time(b) for a, b in wl.reduce_events]
+    wl.reduce_events = None
     launches = lib.gstex_launch_count() - launches0[0]
     clk = clocks.stop() if rank == 0 else None
     value = total_views * P / (ms_per_step * 1e-3) / 1e6
@@ -524,7 +550,8 @@ def main():
     ab = alg_bytes(N, I, T, C, P, tiles)
     entry_ms = {k: (sum(x) / len(x), len(x), sum(x)) for k, x in per_call.items() if x}
     dom = max(entry_ms, key=lambda k: entry_ms[k][2])
-    base = dom[:-4] if dom.endswith("_act") else dom  # the `_act` entry points run the same kernels (scale 1, bias 0)
+    # the `_act` / `_padded` entry points run the same kernels (scale 1, bias 0; texels from the (T,4) copy)
+    base = dom[:-4] if dom.endswith("_act") else dom[:-7] if dom.endswith("_padded") else dom
     key = {"gstex_texture_backward": "backward", "gstex_texture_forward": "forward", "gstex_sort_isects": "sort"}.get(base, "total")
     peak, peak_src = measured_peak_gbs()
     achieved = ab[key] / (entry_ms[dom][0] * 1e-3) / 1e9
@@ -558,8 +585,12 @@ def main():
                    "intersections_view0": I, "mean_tile_list": I / tiles, "ms_per_view": ms_per_step / args.views_per_gpu,
                    "texel_loads": "128-bit from a (T,4) copy padded once per step inside the timed region" if TEXEL_LOADS_128 else "scalar",
                    "l2": "working set (texture+texel grads+records ~400 MB) exceeds the 126 MB L2; no explicit flush",
-                   "parallelism": f"views sharded over {world} GPU(s), one NCCL all-reduce of the flat gradient bucket (9 tensors)" if world > 1
-                   else "single GPU"},
+                   "parallelism": (f"views sharded over {world} GPU(s); the flat gradient bucket (9 tensors, "
+                                   f"{wl.bucket.flat.numel() * 4 / 1e6:.0f} MB) is summed over the ranks by "
+                                   + ("one NCCL all-reduce" if wl.bucket.peer is None else
+                                      "one kernel of ours over NVLink peer memory (gstex_peer_allreduce_f32"
+                                      + (", NVSwitch multimem variant)" if wl.bucket.peer.multicast_ptr else ")")))
+                   if world > 1 else "single GPU"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_ms, "step_ms": stats3(e2e_per),
                 "what": "per view: camera + uint8 ground-truth image from pinned host memory, render, on-device compose + "
@@ -570,6 +601,8 @@ def main():
                                "h2d_bytes_per_step": hb["upstream"][0], "d2h_bytes_per_step": hb["upstream"][1],
                                "what": "round-1 leg: six fp32 upstream-gradient images per view from the host, rendered image back"},
         "step_ms": stats3(per_step),
+        # the exchange step of rank 0: deferred-gradient flush (unpack sweep) + the sum over the ranks, CUDA events
+        "exchange_ms": stats3(reduce_ms) if reduce_ms else None,
         "gpu_launches": int(launches),
         "kernel_ms_per_step": step_ms_kernels,
         "roofline": roofline,

@@ -52,6 +52,8 @@ _SIGNATURES = {
                                   [P] * 10 + [P, SZ, P, SZ, P]),
     "gstex_texture_forward_padded": (I, [I, I, I, I, I, I] + [P] * 7 + [F] + [P] * 6 + [F, F] + [P] * 2 + [F, F, F, F, I] +
                                      [P] * 10 + [P, SZ, P, SZ, P]),
+    "gstex_peer_allreduce_max_world": (I, []),
+    "gstex_peer_allreduce_f32": (I, [I, I, P, ctypes.c_longlong, P, I, P]),
     "gstex_texture_pad4": (I, [ctypes.c_longlong, I, P, P, P]),
     "gstex_texture_backward_act": (I, [I, I, I, I, I, I] + [P] * 7 + [F] + [P] * 5 + [F, F] + [P] * 2 + [F, F, F, F, I] +
                                    [P] * 11 + [P] * 9 + [P, SZ, I, P, SZ, P, SZ, ctypes.c_longlong, I, P]),
@@ -113,7 +115,8 @@ class _TimedLib:
                                                                                "gstex_launch_count", "gstex_debug_force_nocull", "gstex_debug_forward_variant",
                                                                                "gstex_pair_stream_supported",
                                                                                "gstex_tile_bucket_max_list", "gstex_tile_bucket_max_tiles",
-                                                                               "gstex_cumsum_noalloc_max_n", "gstex_chart_max_candidates"):
+                                                                               "gstex_cumsum_noalloc_max_n", "gstex_chart_max_candidates",
+                                                                               "gstex_peer_allreduce_max_world"):
             return fn
 
         def call(*args):

@@ -13,6 +13,8 @@ from typing import Iterable, List, Optional
 
 import torch
 
+from . import _lib
+
 
 def shard_views(num_views: int, rank: int, world: int) -> List[int]:
     """Round-robin: rank r renders views r, r+world, ...  (equal counts when world divides num_views)."""
@@ -210,9 +212,16 @@ class GradientBucket:
     """All parameter gradients of a multi-view step in ONE flat buffer: `p.grad` of every parameter is a view into
     it, autograd accumulates the per-view gradients in place, and the step ends with a single all-reduce over
     the whole buffer (208 MB at the headline size) instead of one collective per tensor.  Slices start on
-    128-byte boundaries.  Works on any device / backend (NCCL on the GPUs, gloo in the CPU tests)."""
+    128-byte boundaries.  Works on any device / backend (NCCL on the GPUs, gloo in the CPU tests).
 
-    def __init__(self, params):
+    `peer_group` (a process group whose ranks share one NVLink / NVSwitch domain, e.g. `dist.group.WORLD` on one
+    node): the buffer is allocated as torch symmetric memory, every rank maps every other rank's bucket, and
+    `allreduce` becomes ONE kernel of ours over that peer memory (`gstex_peer_allreduce_f32`, csrc/peer_reduce.cu:
+    each rank sums its 1/W slice over all ranks and stores it to all ranks) between two cross-rank barriers, instead of
+    an NCCL all-reduce.  `self.peer` says which one is in use; when the mapping cannot be set up (no peer access, an
+    old torch) the constructor raises unless `peer_fallback=True`, in which case it warns and uses NCCL."""
+
+    def __init__(self, params, peer_group=None, peer_fallback: bool = False, multicast: Optional[bool] = None):
         self.params = list(params)
         if not self.params:
             raise ValueError("GradientBucket: no parameters")
@@ -223,7 +232,22 @@ class GradientBucket:
                 raise ValueError("GradientBucket: parameters must share device and dtype")
             offs.append(total)
             total += (p.numel() + 31) // 32 * 32
-        self.flat = torch.zeros(max(total, 1), dtype=dt, device=dev)
+        total = max((total + 3) // 4 * 4, 4)
+        self.peer = None  # _PeerMapping when the all-reduce runs over NVLink peer memory
+        self.flat = None
+        if peer_group is not None:
+            try:
+                self.peer = _PeerMapping(total, dt, dev, peer_group, multicast)
+                self.flat = self.peer.local
+            except Exception as exc:
+                if not peer_fallback:
+                    raise
+                import warnings
+
+                warnings.warn(f"GradientBucket: no peer-memory mapping ({exc!r}); the all-reduce goes through NCCL")
+                self.peer = None
+        if self.flat is None:
+            self.flat = torch.zeros(total, dtype=dt, device=dev)
         self.views = [self.flat[o:o + p.numel()].view(p.shape) for o, p in zip(offs, self.params)]
 
     def zero_(self) -> None:
@@ -264,6 +288,68 @@ class GradientBucket:
                 p.grad = v
         if world <= 1:
             return
+        if self.peer is not None:
+            if group is not None and group is not self.peer.group:
+                raise ValueError("GradientBucket.allreduce: the bucket is mapped over another process group")
+            self.peer.allreduce()
+            return
         import torch.distributed as dist
 
         dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
+
+
+class _PeerMapping:
+    """The plumbing of the peer-memory all-reduce: a symmetric-memory allocation of `count` floats on every rank of
+    `group`, the device addresses under which this process sees each rank's copy, and the cross-rank barriers.
+    torch.distributed._symmetric_memory does the handle exchange (CUDA VMM handles over the group's store); the data
+    path is `gstex_peer_allreduce_f32`."""
+
+    # NVLink bytes per GPU and direction for a bucket of B bytes: 2 B (W-1)/W with peer loads/stores (the slice is read
+    # from and written to W-1 peers, and the peers do the same to this GPU), B (1 + 1/W) with the switch-reduced variant
+    # (all of this GPU's data is pulled once, every store comes back replicated).  Equal at W = 3, the multicast variant
+    # wins from W = 4 on and loses at W = 2 (measured: profiles/peer_allreduce_r2.txt).
+    MULTICAST_FROM_WORLD = 4
+
+    def __init__(self, count: int, dtype, device, group, multicast: Optional[bool] = None):
+        import ctypes
+
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+
+        if dtype != torch.float32:
+            raise ValueError("peer-memory all-reduce: float32 buckets only")
+        if device.type != "cuda":
+            raise ValueError("peer-memory all-reduce needs CUDA devices")
+        self.group = group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        if self.world > _lib.load().gstex_peer_allreduce_max_world():
+            raise ValueError(f"peer-memory all-reduce: at most {_lib.load().gstex_peer_allreduce_max_world()} ranks")
+        self.count = int(count)
+        with torch.cuda.device(device):
+            self.local = symm_mem.empty(self.count, dtype=dtype, device=device)
+            self.handle = symm_mem.rendezvous(self.local, group)
+        self.local.zero_()
+        ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        if len(ptrs) != self.world or ptrs[self.rank] != self.local.data_ptr():
+            raise RuntimeError("peer-memory all-reduce: unexpected symmetric-memory mapping")
+        self.ptrs = (ctypes.c_void_p * self.world)(*ptrs)
+        self.multicast_ptr = None
+        mc = int(getattr(self.handle, "multicast_ptr", 0) or 0)
+        if multicast is None:  # automatic: the NVSwitch-reduced variant where it exists and pays
+            multicast = mc != 0 and self.world >= self.MULTICAST_FROM_WORLD
+        if multicast:
+            if mc == 0:
+                raise RuntimeError("peer-memory all-reduce: no NVSwitch multicast mapping on this system")
+            self.multicast_ptr = ctypes.c_void_p(mc)
+        self.device = device
+        self.max_ctas = 0
+        self.handle.barrier(channel=0)  # every rank's zeros are in place before anyone's first reduce
+
+    def allreduce(self) -> None:
+        dev = self.device
+        self.handle.barrier(channel=0)  # every rank's bucket is complete (its stream reached this point)
+        with torch.cuda.device(dev):
+            rc = _lib.load().gstex_peer_allreduce_f32(self.rank, self.world, self.ptrs, self.count, self.multicast_ptr,
+                                                      int(self.max_ctas), _lib.stream_ptr(dev))
+        _lib.check(rc, "gstex_peer_allreduce_f32")
+        self.handle.barrier(channel=1)  # every rank's stores have landed before anyone reads or zeroes its bucket

@@ -385,6 +385,21 @@ int gstex_photometric_loss_backward(int img_height, int img_width, int channels,
                                     float win_sigma, const float* ssim_maps, const float* v_main_loss, float* v_out_img,
                                     float* v_out_texture, float* v_out_alpha, void* stream);
 
+/* ---- multi-GPU: the gradient sum of a view-sharded step over NVLink peer memory ----
+ * Replaces the NCCL all-reduce torch DDP issues for the reference (NS/pipelines/base_pipeline.py:282) over the flat
+ * gradient bucket.  `peer_bufs[world]` (a HOST array) holds, for every rank in rank order, this process's device
+ * mapping of that rank's bucket of `count` floats (count % 4 == 0, 16-byte aligned; peer_bufs[rank] is the local
+ * one).  The call sums slice `rank` (1/world of the bucket) over all ranks, in rank order, and stores the result into
+ * that slice of every rank's bucket: once every rank has made the call, all buckets hold the full sum, bit-identical
+ * on every rank.  The CALLER orders it: a barrier over the ranks before (every bucket complete) and after (every
+ * store landed) -- torch symmetric memory's in gstex_b200.multiview.  `multicast_buf`, when not NULL, is an NVSwitch
+ * multicast mapping of the same buckets: the slice is then reduced and replicated by the switch
+ * (multimem.ld_reduce / multimem.st) and peer_bufs is not read.  `max_ctas` <= 0: the library picks (2 per SM).
+ * world <= gstex_peer_allreduce_max_world() = 8 (one NVSwitch domain). */
+int gstex_peer_allreduce_max_world(void);
+int gstex_peer_allreduce_f32(int rank, int world, const void* const* peer_bufs, long long count, void* multicast_buf,
+                             int max_ctas, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

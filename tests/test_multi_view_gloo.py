@@ -54,7 +54,17 @@ def _worker(rank, world, port, out_dir):
     from gstex_b200.multiview import GradientBucket
 
     params = [torch.zeros_like(a).requires_grad_(True) for a in acc]
-    bucket = GradientBucket(params)
+    import warnings
+
+    with warnings.catch_warnings(record=True) as caught:  # no peer memory on the CPU: says so, then sums through the group
+        warnings.simplefilter("always")
+        bucket = GradientBucket(params, peer_group=dist.group.WORLD, peer_fallback=True)
+    assert bucket.peer is None and any("peer-memory" in str(w.message) for w in caught)
+    try:
+        GradientBucket(params, peer_group=dist.group.WORLD)
+        raise AssertionError("a peer-memory bucket on CPU tensors must fail loudly without peer_fallback")
+    except ValueError:
+        pass
     bucket.zero_()
     for view in shard_views(NUM_VIEWS, rank, world):
         g = _view_grads(s, v, view)
