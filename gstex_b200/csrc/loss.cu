@@ -17,19 +17,29 @@
 // the SSIM algebra + the three partial-derivative maps the backward needs), a one-block reduction of the per-block
 // partial sums in a fixed order (deterministic), and one backward kernel that pulls the derivative maps back through
 // the window (again separably in shared memory) and writes v_out_img / v_out_texture / v_out_alpha in the same pass.
-// By contract an HBM stream: forward reads 4*(10 + C) B and writes 48 B per pixel, backward reads 4*(19 + C) B and writes
-// 4*(4 + C) B.  sm_100a.
+// Algorithmic bytes: forward reads 4*(10 + C) B and writes 48 B per pixel, backward reads 4*(19 + C) B and writes
+// 4*(4 + C) B; measured limiter: instruction issue (330 multiply-adds per pixel and channel in the two passes alone),
+// see the kernel comments.  sm_100a.
 #include "common.cuh"
 
 namespace gstex {
 
-constexpr int kWin = 11;              // pytorch_msssim default win_size
-constexpr int kLossTile = 16;         // owned pixels per block edge
-constexpr int kHalo = kLossTile + kWin - 1;  // 26
-constexpr int kHaloE = kHalo * 3;     // floats per halo row (three interleaved channels)
-constexpr int kRowPitch = 80;         // shared-memory row pitch: 16 banks from row to row
+constexpr int kWin = 11;               // pytorch_msssim default win_size
+constexpr int kTileH = 16;             // owned pixels per block: 16 rows x 32 columns
+constexpr int kTileW = 32;
+constexpr int kHaloH = kTileH + kWin - 1;  // 26
+constexpr int kHaloW = kTileW + kWin - 1;  // 42
+constexpr int kHaloE = kHaloW * 3;     // 126 floats per halo row (three interleaved channels)
+constexpr int kOwnE = kTileW * 3;      // 96 floats per owned row
+constexpr int kPitch = 127;            // shared-memory row pitch, in elements
+constexpr int kLossThreads = 256;
+constexpr int kOut1 = 8;               // outputs per thread of the pass along H (two halves of the 16 rows)
+constexpr int kOut2 = 8;               // outputs per thread of the pass along W
 
-struct LossWindow { float g[kWin]; };
+struct LossWindow {
+    float g[kWin];
+    float2 g2[kWin];  // (g, g): operand of the packed FFMA2 of sm_100
+};
 
 struct LossDims {
     int H, W, C;       // image size, channels of out_texture (>= 3; only the first three are composited)
@@ -51,132 +61,170 @@ __device__ __forceinline__ float block_sum_256(float v, float* red) {
     return s;  // valid on thread 0
 }
 
-// One block = 16x16 owned pixels (the SSIM positions whose window STARTS there) + the 26x26 pixels their windows cover.
+// Rows of an owned tile (kOwnE floats each) from shared memory to `dst` (row pitch `W * 3` floats), whole 16-byte
+// vectors when the geometry allows it.
+__device__ __forceinline__ void store_tile_rows(float* __restrict__ dst, const float* tile, int i0, int j0, const LossDims& d) {
+    const bool vec = (d.W & 3) == 0 && j0 + kTileW <= d.W;
+    if (vec) {
+        for (int t = threadIdx.x; t < kTileH * (kOwnE / 4); t += kLossThreads) {
+            const int r = t / (kOwnE / 4), q = t - r * (kOwnE / 4);
+            if (i0 + r < d.H) {
+                const float* s = tile + r * kOwnE + 4 * q;
+                *reinterpret_cast<float4*>(dst + ((size_t)(i0 + r) * d.W + j0) * 3 + 4 * q) = make_float4(s[0], s[1], s[2], s[3]);
+            }
+        }
+    } else {
+        for (int t = threadIdx.x; t < kTileH * kOwnE; t += kLossThreads) {
+            const int r = t / kOwnE, e = t - r * kOwnE;
+            if (i0 + r < d.H && j0 + e / 3 < d.W) dst[((size_t)(i0 + r) * d.W + j0) * 3 + e] = tile[r * kOwnE + e];
+        }
+    }
+}
+
+struct LossFwdShared {
+    float2 sxy[kHaloH][kPitch];      // (gt, predicted), both masked: [row][column * 3 + channel]
+    float2 s01[kTileH][kPitch];      // after the pass along H: (E[x], E[y]) ...
+    float2 s23[kTileH][kPitch];      // ... (E[x^2], E[y^2]) ...
+    float s4[kTileH][kPitch];        // ... E[xy]
+    float red[8];
+};
+static_assert(sizeof(float2) * kHaloH * kPitch >= sizeof(float) * 3 * kTileH * kOwnE, "the map staging tile aliases sxy");
+
+// One block = 16x32 owned pixels (the SSIM positions whose window STARTS there) + the 26x42 pixels their windows cover.
 // maps: [3][H][W][3] = d ssim / d mu_pred, d ssim / d E[pred^2], d ssim / d E[gt*pred] per position and channel,
 // zero where the position is not a valid window start (written only when maps != nullptr).
-// Shared-memory traffic is what bounds a naive version (one output per thread = 2 loads per 5 FMAs; ncu: L1/shared
-// pipe 87 % busy, mio_throttle the top stall), so both passes are register-tiled: a pass-1 thread walks 18 rows of one
-// (column, channel) and produces 8 output rows of all five moments (36 loads for 440 FMAs), a pass-2 thread walks 14
-// columns and produces 4 outputs (70 loads for 220 FMAs).  Pixels stay channel-interleaved in shared memory, as in
-// HBM, so the global loads/stores are contiguous row segments and consecutive threads hit consecutive banks.
-__global__ void __launch_bounds__(256) loss_forward_kernel(LossDims d, LossWindow win, const float* __restrict__ out_img,
+// The kernel is instruction-issue bound (ncu, round 1: issue slots 65 % busy, DRAM 6 %), so everything here is about
+// instructions per pixel: a wide tile (2.1 halo elements loaded per owned one, 1.3 for the pass along H), both passes
+// register-tiled (a thread of the first walks 18 rows of one (column, channel) for 8 output rows of all five moments,
+// a thread of the second walks 18 columns for 8 outputs), moments kept as float2 pairs in shared memory and registers
+// so that four of the five multiply-adds per tap are two packed FFMA2 (each half an IEEE fma: the same bits as five
+// scalar ones), no integer division in the load loop, and the three derivative maps staged through shared memory so
+// that they leave as whole rows.  Pixels stay channel-interleaved in shared memory, as in HBM.
+__global__ void __launch_bounds__(kLossThreads) loss_forward_kernel(LossDims d, LossWindow win, const float* __restrict__ out_img,
                                                            const float* __restrict__ out_texture,
                                                            const float* __restrict__ out_alpha,
                                                            const float* __restrict__ background,
                                                            const float* __restrict__ gt, const float* __restrict__ mask,
                                                            float* __restrict__ rgb, float* __restrict__ maps,
                                                            float2* __restrict__ partials) {
-    __shared__ float sx[kHalo][kRowPitch];             // gt (masked), [row][column * 3 + channel]
-    __shared__ float sy[kHalo][kRowPitch];             // predicted (masked)
-    __shared__ float st[5][kLossTile][kRowPitch];      // the five moments after pass 1
-    __shared__ float red[8];
-    const int i0 = blockIdx.y * kLossTile, j0 = blockIdx.x * kLossTile;
+    extern __shared__ __align__(16) unsigned char loss_smem[];
+    LossFwdShared& sh = *reinterpret_cast<LossFwdShared*>(loss_smem);
+    const int i0 = blockIdx.y * kTileH, j0 = blockIdx.x * kTileW;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const float bg[3] = {__ldg(background), __ldg(background + 1), __ldg(background + 2)};
     float l1 = 0.f;
-    for (int t = threadIdx.x; t < kHalo * kHaloE; t += 256) {
-        const int r = t / kHaloE, e = t - r * kHaloE, c = e / 3, k = e - c * 3;
-        const int gi = i0 + r, gj = j0 + c;
-        float x = 0.f, y = 0.f;
-        if (gi < d.H && gj < d.W) {
-            const size_t pix = (size_t)gi * d.W + gj;
-            // gstex.py:1204-1205 as torch evaluates it (no contraction: every product and sum rounded on its own)
-            const float om = __fsub_rn(1.f, __ldg(out_alpha + pix));
-            const float pre = __fadd_rn(__fadd_rn(__ldg(out_img + pix * 3 + k), __ldg(out_texture + pix * d.C + k)),
-                                        __fmul_rn(om, __ldg(background + k)));
-            const float v = clamp_unit(pre);
-            const float m = mask ? __ldg(mask + pix) : 1.f;
-            x = __fmul_rn(__ldg(gt + pix * 3 + k), m);  // gstex.py:1297-1298 (gt_img * mask, pred_img * mask)
-            y = __fmul_rn(v, m);
-            if (r < kLossTile && c < kLossTile) {
-                rgb[pix * 3 + k] = v;
-                l1 += fabsf(x - y);
+    for (int r = warp; r < kHaloH; r += kLossThreads / 32) {
+        const int gi = i0 + r;
+#pragma unroll
+        for (int it = 0; it < (kHaloE + 31) / 32; ++it) {
+            const int e = lane + 32 * it;
+            if (e < kHaloE) {
+                const int c = e / 3, k = e - c * 3;
+                const int gj = j0 + c;
+                float x = 0.f, y = 0.f;
+                if (gi < d.H && gj < d.W) {
+                    const size_t pix = (size_t)gi * d.W + gj;
+                    // gstex.py:1204-1205 as torch evaluates it (no contraction: every product and sum rounded on its own)
+                    const float om = __fsub_rn(1.f, __ldg(out_alpha + pix));
+                    const float pre = __fadd_rn(__fadd_rn(__ldg(out_img + pix * 3 + k), __ldg(out_texture + pix * d.C + k)),
+                                                __fmul_rn(om, k == 0 ? bg[0] : k == 1 ? bg[1] : bg[2]));
+                    const float v = clamp_unit(pre);
+                    const float m = mask ? __ldg(mask + pix) : 1.f;
+                    x = __fmul_rn(__ldg(gt + pix * 3 + k), m);  // gstex.py:1297-1298 (gt_img * mask, pred_img * mask)
+                    y = __fmul_rn(v, m);
+                    if (r < kTileH && c < kTileW) {
+                        rgb[pix * 3 + k] = v;
+                        l1 += fabsf(x - y);
+                    }
+                }
+                sh.sxy[r][e] = make_float2(x, y);
             }
         }
-        sx[r][e] = x; sy[r][e] = y;
     }
     __syncthreads();
     // pass 1, along H (pytorch_msssim filters dim 2 first)
     if (threadIdx.x < 2 * kHaloE) {
-        const int half = threadIdx.x / kHaloE, e = threadIdx.x - half * kHaloE, r0 = half * 8;
-        float acc[8][5];
+        const int half = threadIdx.x / kHaloE, e = threadIdx.x - half * kHaloE, r0 = half * kOut1;
+        float2 a01[kOut1], a23[kOut1];
+        float a4[kOut1];
 #pragma unroll
-        for (int o = 0; o < 8; ++o)
+        for (int o = 0; o < kOut1; ++o) { a01[o] = make_float2(0.f, 0.f); a23[o] = make_float2(0.f, 0.f); a4[o] = 0.f; }
 #pragma unroll
-            for (int m = 0; m < 5; ++m) acc[o][m] = 0.f;
+        for (int rin = 0; rin < kOut1 + kWin - 1; ++rin) {
+            const float2 xy = sh.sxy[r0 + rin][e];
+            const float2 sq = __fmul2_rn(xy, xy);         // (x*x, y*y)
+            const float pxy = __fmul_rn(xy.x, xy.y);
 #pragma unroll
-        for (int rin = 0; rin < 8 + kWin - 1; ++rin) {
-            const float x = sx[r0 + rin][e], y = sy[r0 + rin][e];
-            const float xx = x * x, yy = y * y, xy = x * y;
-#pragma unroll
-            for (int o = 0; o < 8; ++o) {
+            for (int o = 0; o < kOut1; ++o) {
                 const int q = rin - o;
                 if (q >= 0 && q < kWin) {
-                    const float g = win.g[q];
-                    acc[o][0] = fmaf(g, x, acc[o][0]); acc[o][1] = fmaf(g, y, acc[o][1]);
-                    acc[o][2] = fmaf(g, xx, acc[o][2]); acc[o][3] = fmaf(g, yy, acc[o][3]);
-                    acc[o][4] = fmaf(g, xy, acc[o][4]);
+                    a01[o] = __ffma2_rn(win.g2[q], xy, a01[o]);
+                    a23[o] = __ffma2_rn(win.g2[q], sq, a23[o]);
+                    a4[o] = __fmaf_rn(win.g[q], pxy, a4[o]);
                 }
             }
         }
 #pragma unroll
-        for (int o = 0; o < 8; ++o)
-#pragma unroll
-            for (int m = 0; m < 5; ++m) st[m][r0 + o][e] = acc[o][m];
+        for (int o = 0; o < kOut1; ++o) { sh.s01[r0 + o][e] = a01[o]; sh.s23[r0 + o][e] = a23[o]; sh.s4[r0 + o][e] = a4[o]; }
     }
     __syncthreads();
-    // pass 2, along W, then the SSIM algebra (_ssim of pytorch_msssim/ssim.py); 4 positions of one channel per thread
+    // pass 2, along W, then the SSIM algebra (_ssim of pytorch_msssim/ssim.py); 8 positions of one channel per thread.
+    // sxy is dead from here on: its memory stages the three derivative maps of the owned tile.
+    float* stage = reinterpret_cast<float*>(&sh.sxy[0][0]);  // [3][kTileH][kOwnE]
     float ssim = 0.f;
-    if (threadIdx.x < 3 * 4 * kLossTile) {
-        const int k = threadIdx.x % 3, cg = (threadIdx.x / 3) & 3, r = threadIdx.x / 12;
-        float acc[4][5];
+    if (threadIdx.x < 3 * (kTileW / kOut2) * kTileH) {
+        const int k = threadIdx.x % 3, cg = (threadIdx.x / 3) % (kTileW / kOut2), r = threadIdx.x / (3 * (kTileW / kOut2));
+        float2 a01[kOut2], a23[kOut2];
+        float a4[kOut2];
 #pragma unroll
-        for (int o = 0; o < 4; ++o)
+        for (int o = 0; o < kOut2; ++o) { a01[o] = make_float2(0.f, 0.f); a23[o] = make_float2(0.f, 0.f); a4[o] = 0.f; }
 #pragma unroll
-            for (int m = 0; m < 5; ++m) acc[o][m] = 0.f;
+        for (int cin = 0; cin < kOut2 + kWin - 1; ++cin) {
+            const int e = (kOut2 * cg + cin) * 3 + k;
+            const float2 v01 = sh.s01[r][e], v23 = sh.s23[r][e];
+            const float v4 = sh.s4[r][e];
 #pragma unroll
-        for (int cin = 0; cin < 4 + kWin - 1; ++cin) {
-            float v[5];
-#pragma unroll
-            for (int m = 0; m < 5; ++m) v[m] = st[m][r][(4 * cg + cin) * 3 + k];
-#pragma unroll
-            for (int o = 0; o < 4; ++o) {
+            for (int o = 0; o < kOut2; ++o) {
                 const int q = cin - o;
                 if (q >= 0 && q < kWin) {
-                    const float g = win.g[q];
-#pragma unroll
-                    for (int m = 0; m < 5; ++m) acc[o][m] = fmaf(g, v[m], acc[o][m]);
+                    a01[o] = __ffma2_rn(win.g2[q], v01, a01[o]);
+                    a23[o] = __ffma2_rn(win.g2[q], v23, a23[o]);
+                    a4[o] = __fmaf_rn(win.g[q], v4, a4[o]);
                 }
             }
         }
         const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;  // (K1 * data_range)^2, (K2 * data_range)^2
         const int gi = i0 + r;
-        const size_t plane = (size_t)d.H * d.W * 3;
 #pragma unroll
-        for (int o = 0; o < 4; ++o) {
-            const int gj = j0 + 4 * cg + o;
+        for (int o = 0; o < kOut2; ++o) {
+            const int gj = j0 + kOut2 * cg + o;
             const bool valid = gi < d.Hv && gj < d.Wv;
-            const float mu1 = acc[o][0], mu2 = acc[o][1];
+            const float mu1 = a01[o].x, mu2 = a01[o].y;
             const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
-            const float s1 = acc[o][2] - mu1_sq, s2 = acc[o][3] - mu2_sq, s12 = acc[o][4] - mu12;
+            const float s1 = a23[o].x - mu1_sq, s2 = a23[o].y - mu2_sq, s12 = a4[o] - mu12;
             const float A1 = 2.f * mu12 + C1, A2 = 2.f * s12 + C2, B1 = mu1_sq + mu2_sq + C1, B2 = s1 + s2 + C2;
             const float rB1 = 1.f / B1, rB2 = 1.f / B2;
             const float cs = A2 * rB2, lum = A1 * rB1;
             if (valid) ssim += lum * cs;
-            if (maps != nullptr && gi < d.H && gj < d.W) {
-                // partial derivatives of lum*cs with E[y], E[y^2], E[xy] as the independent moments of the prediction y
-                float dmu = 0.f, dyy = 0.f, dxy = 0.f;
-                if (valid) {
-                    dyy = -lum * cs * rB2;
-                    dxy = 2.f * lum * rB2;
-                    dmu = 2.f * rB1 * (mu1 * cs - mu2 * lum * cs) - 2.f * mu2 * dyy - mu1 * dxy;
-                }
-                const size_t idx = ((size_t)gi * d.W + gj) * 3 + k;
-                maps[idx] = dmu; maps[plane + idx] = dyy; maps[2 * plane + idx] = dxy;
+            // partial derivatives of lum*cs with E[y], E[y^2], E[xy] as the independent moments of the prediction y
+            float dmu = 0.f, dyy = 0.f, dxy = 0.f;
+            if (valid) {
+                dyy = -lum * cs * rB2;
+                dxy = 2.f * lum * rB2;
+                dmu = 2.f * rB1 * (mu1 * cs - mu2 * lum * cs) - 2.f * mu2 * dyy - mu1 * dxy;
             }
+            const int se = r * kOwnE + (kOut2 * cg + o) * 3 + k;
+            stage[se] = dmu; stage[kTileH * kOwnE + se] = dyy; stage[2 * kTileH * kOwnE + se] = dxy;
         }
     }
-    const float l1_sum = block_sum_256(l1, red);
-    const float ssim_sum = block_sum_256(ssim, red);
+    const float l1_sum = block_sum_256(l1, sh.red);      // (its barriers also publish the staged maps)
+    const float ssim_sum = block_sum_256(ssim, sh.red);
     if (threadIdx.x == 0) partials[blockIdx.y * gridDim.x + blockIdx.x] = make_float2(l1_sum, ssim_sum);
+    if (maps != nullptr) {
+        const size_t plane = (size_t)d.H * d.W * 3;
+#pragma unroll
+        for (int m = 0; m < 3; ++m) store_tile_rows(maps + m * plane, stage + m * kTileH * kOwnE, i0, j0, d);
+    }
 }
 
 // out[0] = Ll1, out[1] = SSIM, out[2] = main loss; partial sums added in block order, in double (deterministic)
@@ -199,10 +247,19 @@ __global__ void __launch_bounds__(256) loss_finalize_kernel(const float2* __rest
     }
 }
 
-// One block = 16x16 owned pixels; the window positions that cover them start up to 10 rows/columns earlier.
-// Same register tiling as the forward; the transpose of pass 2 then of pass 1 (the window is symmetric, so the
-// adjoint is the same filter read from 10 positions earlier).
-__global__ void __launch_bounds__(256) loss_backward_kernel(LossDims d, LossWindow win, float ssim_lambda,
+struct LossBwdShared {
+    float2 mab[kHaloH][kPitch];   // (d/d mu, d/d E[y^2]) maps, [row][column * 3 + channel], origin (i0 - 10, j0 - 10)
+    float mf[kHaloH][kPitch];     // d/d E[xy] map
+    float2 uab[kTileH][kPitch];   // after the pass along H
+    float uf[kTileH][kPitch];
+    float sg[kTileH][kOwnE + 1];  // gradient * background per (pixel, channel)
+};
+static_assert(sizeof(float2) * kHaloH * kPitch >= sizeof(float) * kTileH * kOwnE, "the gradient staging tile aliases mab");
+
+// One block = 16x32 owned pixels; the window positions that cover them start up to 10 rows/columns earlier.
+// Same tiling as the forward; the transpose of pass 2 then of pass 1 (the window is symmetric, so the adjoint is the
+// same filter read from 10 positions earlier).
+__global__ void __launch_bounds__(kLossThreads) loss_backward_kernel(LossDims d, LossWindow win, float ssim_lambda,
                                                             const float* __restrict__ v_main,
                                                             const float* __restrict__ out_img,
                                                             const float* __restrict__ out_texture,
@@ -212,59 +269,73 @@ __global__ void __launch_bounds__(256) loss_backward_kernel(LossDims d, LossWind
                                                             const float* __restrict__ maps, float* __restrict__ v_out_img,
                                                             float* __restrict__ v_out_texture,
                                                             float* __restrict__ v_out_alpha) {
-    __shared__ float sm[3][kHalo][kRowPitch];      // [map][row][column * 3 + channel], origin (i0 - 10, j0 - 10)
-    __shared__ float su[3][kLossTile][kRowPitch];  // after the column pass
-    __shared__ float sg[kLossTile][kLossTile * 3 + 1];  // gradient * background per (pixel, channel)
-    const int i0 = blockIdx.y * kLossTile, j0 = blockIdx.x * kLossTile;
+    extern __shared__ __align__(16) unsigned char loss_smem[];
+    LossBwdShared& sh = *reinterpret_cast<LossBwdShared*>(loss_smem);
+    const int i0 = blockIdx.y * kTileH, j0 = blockIdx.x * kTileW;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const size_t plane = (size_t)d.H * d.W * 3;
-    for (int t = threadIdx.x; t < kHalo * kHaloE; t += 256) {
-        const int r = t / kHaloE, e = t - r * kHaloE, c = e / 3;
-        const int gi = i0 - (kWin - 1) + r, gj = j0 - (kWin - 1) + c;
-        float a = 0.f, b = 0.f, f = 0.f;
-        if (gi >= 0 && gj >= 0 && gi < d.H && gj < d.W) {
-            const size_t idx = ((size_t)gi * d.W + gj) * 3 + (e - c * 3);
-            a = __ldg(maps + idx); b = __ldg(maps + plane + idx); f = __ldg(maps + 2 * plane + idx);
+    for (int r = warp; r < kHaloH; r += kLossThreads / 32) {
+        const int gi = i0 - (kWin - 1) + r;
+#pragma unroll
+        for (int it = 0; it < (kHaloE + 31) / 32; ++it) {
+            const int e = lane + 32 * it;
+            if (e < kHaloE) {
+                const int c = e / 3;
+                const int gj = j0 - (kWin - 1) + c;
+                float a = 0.f, b = 0.f, f = 0.f;
+                if (gi >= 0 && gj >= 0 && gi < d.H && gj < d.W) {
+                    const size_t idx = ((size_t)gi * d.W + gj) * 3 + (e - c * 3);
+                    a = __ldg(maps + idx); b = __ldg(maps + plane + idx); f = __ldg(maps + 2 * plane + idx);
+                }
+                sh.mab[r][e] = make_float2(a, b);
+                sh.mf[r][e] = f;
+            }
         }
-        sm[0][r][e] = a; sm[1][r][e] = b; sm[2][r][e] = f;
     }
     __syncthreads();
     // position q = p - s contributes to pixel p with weight g[s]; in the local frame that is row (p - i0) + (10 - s)
     if (threadIdx.x < 2 * kHaloE) {
-        const int half = threadIdx.x / kHaloE, e = threadIdx.x - half * kHaloE, r0 = half * 8;
-        float acc[8][3];
+        const int half = threadIdx.x / kHaloE, e = threadIdx.x - half * kHaloE, r0 = half * kOut1;
+        float2 aab[kOut1];
+        float af[kOut1];
 #pragma unroll
-        for (int o = 0; o < 8; ++o) acc[o][0] = acc[o][1] = acc[o][2] = 0.f;
+        for (int o = 0; o < kOut1; ++o) { aab[o] = make_float2(0.f, 0.f); af[o] = 0.f; }
 #pragma unroll
-        for (int rin = 0; rin < 8 + kWin - 1; ++rin) {
-            const float a = sm[0][r0 + rin][e], b = sm[1][r0 + rin][e], f = sm[2][r0 + rin][e];
+        for (int rin = 0; rin < kOut1 + kWin - 1; ++rin) {
+            const float2 ab = sh.mab[r0 + rin][e];
+            const float f = sh.mf[r0 + rin][e];
 #pragma unroll
-            for (int o = 0; o < 8; ++o) {
+            for (int o = 0; o < kOut1; ++o) {
                 const int q = rin - o;
                 if (q >= 0 && q < kWin) {
-                    const float g = win.g[kWin - 1 - q];
-                    acc[o][0] = fmaf(g, a, acc[o][0]); acc[o][1] = fmaf(g, b, acc[o][1]); acc[o][2] = fmaf(g, f, acc[o][2]);
+                    aab[o] = __ffma2_rn(win.g2[kWin - 1 - q], ab, aab[o]);
+                    af[o] = __fmaf_rn(win.g[kWin - 1 - q], f, af[o]);
                 }
             }
         }
 #pragma unroll
-        for (int o = 0; o < 8; ++o) { su[0][r0 + o][e] = acc[o][0]; su[1][r0 + o][e] = acc[o][1]; su[2][r0 + o][e] = acc[o][2]; }
+        for (int o = 0; o < kOut1; ++o) { sh.uab[r0 + o][e] = aab[o]; sh.uf[r0 + o][e] = af[o]; }
     }
     __syncthreads();
-    if (threadIdx.x < 3 * 4 * kLossTile) {
-        const int k = threadIdx.x % 3, cg = (threadIdx.x / 3) & 3, r = threadIdx.x / 12;
-        float acc[4][3];
+    // mab is dead from here on: its memory stages the gradient of the owned tile
+    float* stage = reinterpret_cast<float*>(&sh.mab[0][0]);  // [kTileH][kOwnE]
+    if (threadIdx.x < 3 * (kTileW / kOut2) * kTileH) {
+        const int k = threadIdx.x % 3, cg = (threadIdx.x / 3) % (kTileW / kOut2), r = threadIdx.x / (3 * (kTileW / kOut2));
+        float2 aab[kOut2];
+        float af[kOut2];
 #pragma unroll
-        for (int o = 0; o < 4; ++o) acc[o][0] = acc[o][1] = acc[o][2] = 0.f;
+        for (int o = 0; o < kOut2; ++o) { aab[o] = make_float2(0.f, 0.f); af[o] = 0.f; }
 #pragma unroll
-        for (int cin = 0; cin < 4 + kWin - 1; ++cin) {
-            const int e = (4 * cg + cin) * 3 + k;
-            const float a = su[0][r][e], b = su[1][r][e], f = su[2][r][e];
+        for (int cin = 0; cin < kOut2 + kWin - 1; ++cin) {
+            const int e = (kOut2 * cg + cin) * 3 + k;
+            const float2 ab = sh.uab[r][e];
+            const float f = sh.uf[r][e];
 #pragma unroll
-            for (int o = 0; o < 4; ++o) {
+            for (int o = 0; o < kOut2; ++o) {
                 const int q = cin - o;
                 if (q >= 0 && q < kWin) {
-                    const float g = win.g[kWin - 1 - q];
-                    acc[o][0] = fmaf(g, a, acc[o][0]); acc[o][1] = fmaf(g, b, acc[o][1]); acc[o][2] = fmaf(g, f, acc[o][2]);
+                    aab[o] = __ffma2_rn(win.g2[kWin - 1 - q], ab, aab[o]);
+                    af[o] = __fmaf_rn(win.g[kWin - 1 - q], f, af[o]);
                 }
             }
         }
@@ -274,9 +345,9 @@ __global__ void __launch_bounds__(256) loss_backward_kernel(LossDims d, LossWind
         const float bgk = __ldg(background + k);
         const int gi = i0 + r;
 #pragma unroll
-        for (int o = 0; o < 4; ++o) {
-            const int gj = j0 + 4 * cg + o;
-            float gb = 0.f;
+        for (int o = 0; o < kOut2; ++o) {
+            const int gj = j0 + kOut2 * cg + o;
+            float g = 0.f, gb = 0.f;
             if (gi < d.H && gj < d.W) {
                 const size_t pix = (size_t)gi * d.W + gj;
                 const float om = __fsub_rn(1.f, __ldg(out_alpha + pix));
@@ -286,23 +357,34 @@ __global__ void __launch_bounds__(256) loss_backward_kernel(LossDims d, LossWind
                 const float x = __fmul_rn(__ldg(gt + pix * 3 + k), m), y = __fmul_rn(clamp_unit(pre), m);
                 const float diff = x - y;  // Ll1 = mean |gt - pred|: d/dpred = -sign(gt - pred)
                 const float sgn = diff > 0.f ? -1.f : (diff < 0.f ? 1.f : 0.f);
-                float g = w_l1 * sgn + w_ss * (acc[o][0] + 2.f * y * acc[o][1] + x * acc[o][2]);
+                g = w_l1 * sgn + w_ss * (aab[o].x + 2.f * y * aab[o].y + x * af[o]);
                 g *= m;                                    // pred_img * mask
                 if (!(pre >= 0.f && pre <= 1.f)) g = 0.f;  // torch.clamp passes the gradient on [min, max] only
-                v_out_img[pix * 3 + k] = g;
-                v_out_texture[pix * d.C + k] = g;
                 gb = g * bgk;  // d/d out_alpha of (1 - out_alpha) * background, summed over the channels below
             }
-            sg[r][(4 * cg + o) * 3 + k] = gb;
+            const int se = (kOut2 * cg + o) * 3 + k;
+            stage[r * kOwnE + se] = g;
+            sh.sg[r][se] = gb;
         }
     }
     __syncthreads();
-    const int pr = threadIdx.x >> 4, pc = threadIdx.x & 15;
-    const int gi = i0 + pr, gj = j0 + pc;
-    if (gi < d.H && gj < d.W) {
-        const size_t pix = (size_t)gi * d.W + gj;
-        for (int k = 3; k < d.C; ++k) v_out_texture[pix * d.C + k] = 0.f;  // channels the composite does not read
-        v_out_alpha[pix] = ((0.f - sg[pr][pc * 3]) - sg[pr][pc * 3 + 1]) - sg[pr][pc * 3 + 2];
+    store_tile_rows(v_out_img, stage, i0, j0, d);
+    if (d.C == 3) {
+        store_tile_rows(v_out_texture, stage, i0, j0, d);
+    } else {
+        for (int t = threadIdx.x; t < kTileH * kTileW; t += kLossThreads) {
+            const int pr = t / kTileW, pc = t - pr * kTileW;
+            if (i0 + pr < d.H && j0 + pc < d.W) {
+                float* o = v_out_texture + ((size_t)(i0 + pr) * d.W + j0 + pc) * d.C;
+                for (int k = 0; k < 3; ++k) o[k] = stage[pr * kOwnE + pc * 3 + k];
+                for (int k = 3; k < d.C; ++k) o[k] = 0.f;  // channels the composite does not read
+            }
+        }
+    }
+    for (int t = threadIdx.x; t < kTileH * kTileW; t += kLossThreads) {
+        const int pr = t / kTileW, pc = t - pr * kTileW;
+        if (i0 + pr < d.H && j0 + pc < d.W)
+            v_out_alpha[(size_t)(i0 + pr) * d.W + j0 + pc] = ((0.f - sh.sg[pr][pc * 3]) - sh.sg[pr][pc * 3 + 1]) - sh.sg[pr][pc * 3 + 2];
     }
 }
 
@@ -315,7 +397,10 @@ static LossWindow make_window(float sigma) {
         w.g[i] = expf(-(x * x) / (2.f * sigma * sigma));
         s += w.g[i];
     }
-    for (int i = 0; i < kWin; ++i) w.g[i] /= s;
+    for (int i = 0; i < kWin; ++i) {
+        w.g[i] /= s;
+        w.g2[i] = make_float2(w.g[i], w.g[i]);
+    }
     return w;
 }
 
@@ -325,7 +410,7 @@ using namespace gstex;
 
 extern "C" size_t gstex_photometric_loss_scratch_bytes(int img_height, int img_width) {
     if (img_height < 1 || img_width < 1) return 0;
-    return (size_t)div_up(img_height, kLossTile) * div_up(img_width, kLossTile) * sizeof(float2);
+    return (size_t)div_up(img_height, kTileH) * div_up(img_width, kTileW) * sizeof(float2);
 }
 
 extern "C" int gstex_photometric_loss_forward(int img_height, int img_width, int channels, const float* out_img,
@@ -337,9 +422,12 @@ extern "C" int gstex_photometric_loss_forward(int img_height, int img_width, int
     if (!out_img || !out_texture || !out_alpha || !background || !gt_img || !rgb || !losses || !scratch) return GSTEX_E_BADARG;
     if (scratch_bytes < gstex_photometric_loss_scratch_bytes(img_height, img_width)) return GSTEX_E_WORKSPACE;
     const LossDims d{img_height, img_width, channels, img_height - (kWin - 1), img_width - (kWin - 1)};
-    const dim3 grid(div_up(img_width, kLossTile), div_up(img_height, kLossTile));
+    const dim3 grid(div_up(img_width, kTileW), div_up(img_height, kTileH));
     cudaStream_t st = (cudaStream_t)stream;
-    loss_forward_kernel<<<grid, 256, 0, st>>>(d, make_window(win_sigma), out_img, out_texture, out_alpha, background, gt_img,
+    // > 48 KB of shared memory: opt in (per device, cheap: done at every launch)
+    GSTEX_CUDA_TRY(cudaFuncSetAttribute(loss_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)sizeof(LossFwdShared)));
+    loss_forward_kernel<<<grid, kLossThreads, sizeof(LossFwdShared), st>>>(d, make_window(win_sigma), out_img, out_texture, out_alpha, background, gt_img,
                                               mask, rgb, ssim_maps, reinterpret_cast<float2*>(scratch));
     GSTEX_LAUNCH_CHECK();
     loss_finalize_kernel<<<1, 256, 0, st>>>(reinterpret_cast<const float2*>(scratch), (int)(grid.x * grid.y), d, ssim_lambda,
@@ -358,8 +446,10 @@ extern "C" int gstex_photometric_loss_backward(int img_height, int img_width, in
         !v_out_alpha)
         return GSTEX_E_BADARG;
     const LossDims d{img_height, img_width, channels, img_height - (kWin - 1), img_width - (kWin - 1)};
-    const dim3 grid(div_up(img_width, kLossTile), div_up(img_height, kLossTile));
-    loss_backward_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(d, make_window(win_sigma), ssim_lambda, v_main_loss, out_img,
+    const dim3 grid(div_up(img_width, kTileW), div_up(img_height, kTileH));
+    GSTEX_CUDA_TRY(cudaFuncSetAttribute(loss_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)sizeof(LossBwdShared)));
+    loss_backward_kernel<<<grid, kLossThreads, sizeof(LossBwdShared), (cudaStream_t)stream>>>(d, make_window(win_sigma), ssim_lambda, v_main_loss, out_img,
                                                                  out_texture, out_alpha, background, gt_img, mask, ssim_maps,
                                                                  v_out_img, v_out_texture, v_out_alpha);
     GSTEX_LAUNCH_CHECK();

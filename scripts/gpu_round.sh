@@ -10,6 +10,7 @@ python -m pytest tests -m gpu -x -q > $OUT/pytest_$TAG.log 2>&1; echo "pytest rc
 tail -4 $OUT/pytest_$TAG.log
 python bench.py --steps 20 --warmup 3 > $OUT/bench_$TAG.json 2> $OUT/bench_$TAG.err; echo "bench rc=$?"
 python bench.py --impl reference --steps 2 --warmup 1 > $OUT/bench_ref_$TAG.json 2>> $OUT/bench_$TAG.err; echo "ref rc=$?"
+python scripts/bench_loss.py 2>/dev/null | tail -1 > $OUT/bench_loss_$TAG.json
 SMALL="python bench.py --steps 1 --warmup 1 --views-per-gpu 2 --no-ref-cuda --no-cpu-baseline"
 $SMALL > $OUT/plain_$TAG.log 2>&1 || { echo "plain run failed"; exit 1; }
 ncu --metrics gpu__time_duration.sum --clock-control none -c 800 --csv --log-file $OUT/launches_$TAG.csv $SMALL > $OUT/ncu_launch_$TAG.log 2>&1; echo "ncu launches rc=$?"
