@@ -100,6 +100,7 @@ class ClockSampler:
         self.idx = gpu_index
         self.proc = None
         self.lines = []
+        self.first = 0  # samples before this one were taken before the timed region
 
     def start(self):
         try:
@@ -108,6 +109,11 @@ class ClockSampler:
             threading.Thread(target=self._pump, daemon=True).start()
         except Exception:
             self.proc = None
+
+    def mark(self):
+        """The timed region starts here.  nvidia-smi is started before the warm-up steps, so that its start-up (NVML
+        attaches to every GPU of the box) is over by now; only the samples taken from now on are reported."""
+        self.first = len(self.lines)
 
     def _pump(self):
         for line in self.proc.stdout:
@@ -119,7 +125,7 @@ class ClockSampler:
         time.sleep(0.15)
         self.proc.terminate()
         sm, mx, reasons = [], [], set()
-        for ln in self.lines:
+        for ln in self.lines[self.first:] or self.lines[-1:]:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 9:
                 continue
@@ -198,6 +204,8 @@ class Workload:
                 group = dist.group.WORLD
             self.bucket = GradientBucket(list(self.params.values()), peer_group=group, peer_fallback=True,
                                          multicast={"auto": None, "peer": False, "multimem": True}.get(ALLREDUCE))
+            if self.bucket.peer is not None and os.environ.get("BENCH_PEER_CTAS"):  # experiment knob
+                self.bucket.peer.max_ctas = int(os.environ["BENCH_PEER_CTAS"])
             self.bucket.register()
         self.bucket.zero_()
         if TEXEL_LOADS_128:  # the parameters change between steps: the padded copy is part of every step's work
@@ -493,9 +501,11 @@ def main():
     P = H * W
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
 
-    def timed(step_fn, before=None):
+    def timed(step_fn, before=None, first=None):
         """W warm-up steps, then EXACTLY K steps between barrier + synchronize on both sides; one CUDA event per step
         boundary.  Returns (ms per step from the first to the last event, max over ranks; per-step ms of this rank)."""
+        if first is not None:
+            first()
         for _ in range(max(args.warmup, 3 if args.steps > 1 else 1)):
             step_fn()
         barrier()
@@ -508,6 +518,8 @@ def main():
             ev[k + 1].record()
         barrier()
         per = [ev[k].elapsed_time(ev[k + 1]) for k in range(args.steps)]
+        if os.environ.get("BENCH_DUMP_STEPS"):  # diagnosis: the per-step times of this rank
+            print("per-step ms:", " ".join(f"{x:.2f}" for x in per), file=sys.stderr)
         return max_over_ranks(ev[0].elapsed_time(ev[-1])) / args.steps, per
 
     clocks = ClockSampler(local_rank)
@@ -515,7 +527,7 @@ def main():
 
     def begin_timed_region():
         if rank == 0:
-            clocks.start()
+            clocks.mark()
         launches0[0] = lib.gstex_launch_count()
         _lib.Timing.start()
 
@@ -523,7 +535,8 @@ def main():
         begin_timed_region()
         wl.reduce_events = []
 
-    ms_per_step, per_step = timed(lambda: wl.step(world), before=begin_resident)
+    ms_per_step, per_step = timed(lambda: wl.step(world), before=begin_resident,
+                                  first=clocks.start if rank == 0 else None)
     per_call = _lib.Timing.stop()
     reduce_ms = [a.elapsed_time(b) for a, b in wl.reduce_events]
     wl.reduce_events = None

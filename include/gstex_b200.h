@@ -394,7 +394,7 @@ int gstex_photometric_loss_backward(int img_height, int img_width, int channels,
  * on every rank.  The CALLER orders it: a barrier over the ranks before (every bucket complete) and after (every
  * store landed) -- torch symmetric memory's in gstex_b200.multiview.  `multicast_buf`, when not NULL, is an NVSwitch
  * multicast mapping of the same buckets: the slice is then reduced and replicated by the switch
- * (multimem.ld_reduce / multimem.st) and peer_bufs is not read.  `max_ctas` <= 0: the library picks (2 per SM).
+ * (multimem.ld_reduce / multimem.st) and peer_bufs is not read.  `max_ctas` <= 0: the library picks (every SM for peer loads/stores, 16 CTAs for the multicast variant).
  * world <= gstex_peer_allreduce_max_world() = 8 (one NVSwitch domain). */
 int gstex_peer_allreduce_max_world(void);
 int gstex_peer_allreduce_f32(int rank, int world, const void* const* peer_bufs, long long count, void* multicast_buf,

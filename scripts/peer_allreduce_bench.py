@@ -52,15 +52,12 @@ for name, mc in (("p2p", False), ("multimem", True)):
     flat = b.flat
     sweep = os.environ.get("PEER_SWEEP")
     if mc and sweep:
-        for u in (1, 2, 4, 8):
-            os.environ["GSTEX_EXP_MULTIMEM_UNROLL"] = str(u)
-            for ctas in (8, 16, 32, 64, 148, 0):
-                b.peer.max_ctas = ctas
-                run(f"mm u{u}/{ctas or 'all'}", b.peer.allreduce, "gstex_peer_allreduce_f32")
-        os.environ.pop("GSTEX_EXP_MULTIMEM_UNROLL")
+        for ctas in (8, 16, 32, 64, 148, 296):
+            b.peer.max_ctas = ctas
+            run(f"mm/{ctas}", b.peer.allreduce, "gstex_peer_allreduce_f32")
     for ctas in ((0,) if mc else (0, 74, 37)):
         b.peer.max_ctas = ctas
-        run(f"{name}/{ctas or 'all'}", b.peer.allreduce, "gstex_peer_allreduce_f32")
+        run(f"{name}/{ctas or 'default'}", b.peer.allreduce, "gstex_peer_allreduce_f32")
     del b
 flat = torch.zeros(count, device=dev)
 run("nccl", lambda: dist.all_reduce(flat))
