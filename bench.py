@@ -33,6 +33,7 @@ METRIC = "fwd+bwd Mpix/s, 1M textured splats @800x800 (project+bin+sort+forward+
 UNIT = "Mpix/s"
 OWN_BINNING_STREAM = True  # --binning-stream own|current
 TEXEL_LOADS_128 = True     # --texel-loads scalar|128
+PACK_EARLY = False         # --pack early|forward
 ALLREDUCE = "auto"         # --allreduce auto|peer|multimem|nccl (N > 1)
 PARAM_KEYS = ["colors", "opacities", "means", "scales", "quats", "uv0", "umap", "vmap", "texture"]
 VOUT_KEYS = ["v_out_img", "v_out_depth", "v_out_reg", "v_out_alpha", "v_out_texture", "v_out_normal"]
@@ -56,6 +57,9 @@ def parse_args():
                     help="N > 1: the gradient sum at the end of a step as our kernel over NVLink peer memory -- plain peer "
                          "loads/stores, the NVSwitch-multicast variant, or whichever the library picks for N (default) -- "
                          "or NCCL's all-reduce (A/B)")
+    ap.add_argument("--pack", default="forward", choices=["early", "forward"],
+                    help="forward: the per-view records are packed inside the forward call, on the current stream (default); "
+                         "early: on the binning stream, ahead of the forward (A/B: measured 3 %% slower per step, DESIGN.md 3)")
     ap.add_argument("--texel-loads", default="128", choices=["scalar", "128"],
                     help="128: the texture is padded to (T, 4) once per step (inside the timed region) and every view's "
                          "forward fetches texels with 128-bit loads (gstex_b200.pad_texture)")
@@ -178,6 +182,16 @@ class Workload:
         return self.binning.begin(p["means"], p["scales"], 1, p["quats"], viewmat, self.intr, self.H, self.W, self.bw,
                                   wait_for_current=first)
 
+    def finish_view(self, pre, c2w):
+        """The host waits for the view's sizes; emit, sort and (--pack early) the forward's per-view records go to the
+        binning stream."""
+        p = self.params
+        pack = None
+        if PACK_EARLY:
+            pack = dict(texture_dims=self.texture_dims, colors=p["colors"], opacity=p["opacities"], uv0=p["uv0"],
+                        umap=p["umap"], vmap=p["vmap"], c2w=c2w, settings=self.s["settings"])
+        self.binning.finish(pre, pack=pack)
+
     def forward_view(self, pre, viewmat, c2w):
         """The reference's call (NS/models/gstex.py:1075-1170) on a prepared view."""
         import gstex_b200 as G
@@ -230,13 +244,13 @@ class Workload:
         self.zero_grad(world)
         nv = len(self.viewmats)
         pre = self.prep_view(self.viewmats[0], first=True)
-        self.binning.finish(pre)
+        self.finish_view(pre, self.c2ws[0])
         for i in range(nv):
             outs = self.forward_view(pre, self.viewmats[i], self.c2ws[i])
             pre = self.prep_view(self.viewmats[i + 1]) if i + 1 < nv else None
             self.backward_view(outs, self.v)
             if pre is not None:
-                self.binning.finish(pre)
+                self.finish_view(pre, self.c2ws[i + 1])
         self.reduce_grads(world)
 
     def _e2e_loop(self, world, host, view_in, backward, results):
@@ -256,7 +270,7 @@ class Workload:
         fd.prefetch(view_in(0))
         d = fd.take(also=side)
         pre = self.prep_view(d["vm"], first=True)
-        self.binning.finish(pre)
+        self.finish_view(pre, d["c2w"])
         if nv > 1:
             fd.prefetch(view_in(1))
         for i in range(nv):
@@ -265,7 +279,7 @@ class Workload:
             pre = self.prep_view(d_next["vm"]) if d_next is not None else None
             res = backward(outs, d)
             if pre is not None:
-                self.binning.finish(pre)
+                self.finish_view(pre, d_next["c2w"])
             if i + 2 < nv:  # view i's staging slot is free once its backward is enqueued
                 fd.prefetch(view_in(i + 2))
             for dev_t, host_t in results(i, outs, res):
@@ -450,13 +464,14 @@ def ncu_capture(kernel_key):
 
 
 def main():
-    global OWN_BINNING_STREAM, TEXEL_LOADS_128, ALLREDUCE
+    global OWN_BINNING_STREAM, TEXEL_LOADS_128, ALLREDUCE, PACK_EARLY
     args = parse_args()
     # second stream at every N: measured on one 8xB200 box (profiles/bench_r2_s1_n8_{own,current}.json) 3594 vs 3467 Mpix/s at
     # 8 ranks, 498 vs 470 at one (round 1 needed a switch at 8 ranks; gone with the cheaper per-view host path)
     OWN_BINNING_STREAM = args.binning_stream == "own"
     TEXEL_LOADS_128 = args.texel_loads == "128"
     ALLREDUCE = args.allreduce
+    PACK_EARLY = args.pack == "early"
     # stdout carries ONE JSON line and nothing else: libraries that log to file descriptor 1 (NCCL's version banner and
     # NCCL_DEBUG output go to stdout) are sent to stderr for the whole run, the line is written to the saved descriptor
     sys.stdout.flush()
@@ -564,7 +579,7 @@ def main():
     entry_ms = {k: (sum(x) / len(x), len(x), sum(x)) for k, x in per_call.items() if x}
     dom = max(entry_ms, key=lambda k: entry_ms[k][2])
     # the `_act` / `_padded` entry points run the same kernels (scale 1, bias 0; texels from the (T,4) copy)
-    base = dom[:-4] if dom.endswith("_act") else dom[:-7] if dom.endswith("_padded") else dom
+    base = dom[:-4] if dom.endswith("_act") else dom[:-7] if dom.endswith(("_padded", "_packed")) else dom
     key = {"gstex_texture_backward": "backward", "gstex_texture_forward": "forward", "gstex_sort_isects": "sort"}.get(base, "total")
     peak, peak_src = measured_peak_gbs()
     achieved = ab[key] / (entry_ms[dom][0] * 1e-3) / 1e9
@@ -596,6 +611,7 @@ def main():
         "config": {"workload": f"{args.config}: {N} splats, {T} texels (C={C}), {W}x{H}, {args.views_per_gpu} views/GPU/step, "
                                f"fwd+bwd, settings {s['settings']}", "views_per_gpu": args.views_per_gpu,
                    "intersections_view0": I, "mean_tile_list": I / tiles, "ms_per_view": ms_per_step / args.views_per_gpu,
+                   "pack": "per-view records packed on the binning stream (BinningStream.finish(pack=...))" if PACK_EARLY else "inside the forward call",
                    "texel_loads": "128-bit from a (T,4) copy padded once per step inside the timed region" if TEXEL_LOADS_128 else "scalar",
                    "l2": "working set (texture+texel grads+records ~400 MB) exceeds the 126 MB L2; no explicit flush",
                    "parallelism": (f"views sharded over {world} GPU(s); the flat gradient bucket (9 tensors, "

@@ -54,6 +54,9 @@ _SIGNATURES = {
                                      [P] * 10 + [P, SZ, P, SZ, P]),
     "gstex_peer_allreduce_max_world": (I, []),
     "gstex_peer_allreduce_f32": (I, [I, I, P, ctypes.c_longlong, P, I, P]),
+    "gstex_texture_forward_packed": (I, [I, I, I, I, I, I] + [P] * 7 + [F] + [P] * 6 + [F, F] + [P] * 2 + [F, F, F, F, I] +
+                                     [P] * 10 + [P, SZ, P, SZ, P]),
+    "gstex_texture_pack_records": (I, [I, I, I, I] + [P] * 6 + [F] + [P] * 6 + [F, F, F, F, I] + [P, SZ, P]),
     "gstex_texture_pad4": (I, [ctypes.c_longlong, I, P, P, P]),
     "gstex_texture_backward_act": (I, [I, I, I, I, I, I] + [P] * 7 + [F] + [P] * 5 + [F, F] + [P] * 2 + [F, F, F, F, I] +
                                    [P] * 11 + [P] * 9 + [P, SZ, I, P, SZ, P, SZ, ctypes.c_longlong, I, P]),

@@ -483,7 +483,7 @@ static int forward_impl(int img_height, int img_width, int block_width, int chan
                                      const int32_t* gaussian_ids_sorted, const int32_t* tile_bins, const float* colors,
                                      const float* opacities, const float* means, const float* scales, float glob_scale,
                                      const float* quats, const float* uv0, const float* umap, const float* vmap,
-                                     const float* texture, const float* texture4, float tex_scale, float tex_bias, const float* viewmat, const float* c2w, float fx, float fy,
+                                     const float* texture, const float* texture4, int records_valid, float tex_scale, float tex_bias, const float* viewmat, const float* c2w, float fx, float fy,
                                      float cx, float cy, int settings, const float* background, float* out_img,
                                      float* out_depth, float* out_reg, float* out_texture, float* out_normal,
                                      float* final_Ts, int32_t* final_idx, int32_t* depth_idx, float* out_reg_s,
@@ -504,12 +504,13 @@ static int forward_impl(int img_height, int img_width, int block_width, int chan
     if (num_intersects > 0 && !gaussian_ids_sorted) return GSTEX_E_BADARG;
     if (workspace_bytes < ws_bytes(n)) return GSTEX_E_WORKSPACE;
     const int num_tiles = ((img_width + block_width - 1) / block_width) * ((img_height + block_width - 1) / block_width);
-    if (n > 0) {
+    if (n > 0 && !records_valid) {
         const int rc = launch_pack_records(n, texture_dims, colors, opacities, means, scales, glob_scale, quats, uv0, umap,
                                            vmap, viewmat, c2w, fx, fy, cx, cy, settings, workspace, st, tile_bins,
                                            num_tiles);
         if (rc != GSTEX_OK) return rc;
-    } else {  // the pack kernel zeroes the unit cursor; without splats nobody did
+    } else {  // the pack kernel zeroes the unit cursor; without splats nobody did, and an earlier forward over the same
+              // packed records has left it at the end
         GSTEX_CUDA_TRY(cudaMemsetAsync(ws_counters(workspace), 0, sizeof(uint32_t), st));
     }
     FwdParams p;
@@ -585,11 +586,11 @@ static int forward_impl(int img_height, int img_width, int block_width, int chan
         final_Ts, final_idx, depth_idx, out_reg_s, workspace, workspace_bytes, pair_stream, pair_stream_bytes, stream
 
 extern "C" int gstex_texture_forward(GSTEX_FWD_SIG_HEAD, GSTEX_FWD_SIG_TAIL) {
-    return forward_impl(GSTEX_FWD_ARGS_HEAD, nullptr, 1.f, 0.f, GSTEX_FWD_ARGS_TAIL);
+    return forward_impl(GSTEX_FWD_ARGS_HEAD, nullptr, 0, 1.f, 0.f, GSTEX_FWD_ARGS_TAIL);
 }
 
 extern "C" int gstex_texture_forward_act(GSTEX_FWD_SIG_HEAD, float tex_scale, float tex_bias, GSTEX_FWD_SIG_TAIL) {
-    return forward_impl(GSTEX_FWD_ARGS_HEAD, nullptr, tex_scale, tex_bias, GSTEX_FWD_ARGS_TAIL);
+    return forward_impl(GSTEX_FWD_ARGS_HEAD, nullptr, 0, tex_scale, tex_bias, GSTEX_FWD_ARGS_TAIL);
 }
 
 // The same forward with the texel fetch reading `texture4`, a (num_texels, 4) zero-padded copy of the (num_texels,
@@ -598,7 +599,34 @@ extern "C" int gstex_texture_forward_act(GSTEX_FWD_SIG_HEAD, float tex_scale, fl
 extern "C" int gstex_texture_forward_padded(GSTEX_FWD_SIG_HEAD, const float* texture4, float tex_scale, float tex_bias,
                                             GSTEX_FWD_SIG_TAIL) {
     if (!texture4) return GSTEX_E_BADARG;
-    return forward_impl(GSTEX_FWD_ARGS_HEAD, texture4, tex_scale, tex_bias, GSTEX_FWD_ARGS_TAIL);
+    return forward_impl(GSTEX_FWD_ARGS_HEAD, texture4, 0, tex_scale, tex_bias, GSTEX_FWD_ARGS_TAIL);
+}
+
+// The per-view packed records of gstex_texture_forward* as a call of their own, so that a multi-view caller can issue
+// them early, on another stream, beside the compositing kernels of the view before (the pack is an HBM stream over
+// all splats, ~65 us per view for 1 M splats; the compositing kernels are issue-bound).
+extern "C" int gstex_texture_pack_records(int img_height, int img_width, int block_width, int n, const int32_t* texture_dims,
+                                          const int32_t* tile_bins, const float* colors, const float* opacities,
+                                          const float* means, const float* scales, float glob_scale, const float* quats,
+                                          const float* uv0, const float* umap, const float* vmap, const float* viewmat,
+                                          const float* c2w, float fx, float fy, float cx, float cy, int settings,
+                                          void* workspace, size_t workspace_bytes, void* stream) {
+    if (img_height <= 0 || img_width <= 0 || block_width < 2 || block_width > 16 || n < 0) return GSTEX_E_BADARG;
+    if (settings & ~GSTEX_SETTINGS_SUPPORTED) return GSTEX_E_UNSUPPORTED;
+    if (!workspace || !tile_bins || !viewmat || !c2w) return GSTEX_E_BADARG;
+    if (workspace_bytes < ws_bytes(n)) return GSTEX_E_WORKSPACE;
+    if (n == 0) return GSTEX_OK;
+    if (!texture_dims || !colors || !opacities || !means || !scales || !quats || !uv0 || !umap || !vmap) return GSTEX_E_BADARG;
+    const int num_tiles = ((img_width + block_width - 1) / block_width) * ((img_height + block_width - 1) / block_width);
+    return launch_pack_records(n, texture_dims, colors, opacities, means, scales, glob_scale, quats, uv0, umap, vmap, viewmat,
+                               c2w, fx, fy, cx, cy, settings, workspace, (cudaStream_t)stream, tile_bins, num_tiles);
+}
+
+// gstex_texture_forward_padded (`texture4` may be NULL here: scalar texel loads) over records that
+// gstex_texture_pack_records has already written into `workspace` for exactly these inputs.
+extern "C" int gstex_texture_forward_packed(GSTEX_FWD_SIG_HEAD, const float* texture4, float tex_scale, float tex_bias,
+                                            GSTEX_FWD_SIG_TAIL) {
+    return forward_impl(GSTEX_FWD_ARGS_HEAD, texture4, 1, tex_scale, tex_bias, GSTEX_FWD_ARGS_TAIL);
 }
 
 namespace gstex {

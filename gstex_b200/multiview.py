@@ -149,7 +149,7 @@ class BinningStream:
     """
 
     class Prepared:
-        __slots__ = ("centers", "extents", "depths", "num_tiles_hit", "binning", "ready")
+        __slots__ = ("centers", "extents", "depths", "num_tiles_hit", "binning", "ready", "view")
 
         @property
         def args(self):
@@ -184,12 +184,19 @@ class BinningStream:
             pre.binning = begin_binning(means.shape[0], pre.centers, pre.extents, pre.depths, pre.num_tiles_hit,
                                         tile_bounds, block_width)
         pre.ready = False
+        pre.view = (means, scales, glob_scale, quats, viewmat, intrins, img_height, img_width, block_width)
         return pre
 
-    def finish(self, pre: "BinningStream.Prepared"):
+    def finish(self, pre: "BinningStream.Prepared", pack: Optional[dict] = None):
         """Second half (`finish_binning`: the host waits for the view's sizes, emit + per-tile sort go to the binning
         stream), then the CURRENT stream is made to wait for the result.  Returns `(num_intersects,
-        gaussian_ids_sorted, tile_bins)`; `texture_gaussians(..., binning=pre.binning)` picks the same result up."""
+        gaussian_ids_sorted, tile_bins)`; `texture_gaussians(..., binning=pre.binning)` picks the same result up.
+
+        `pack`: the remaining inputs of `texture_gaussians` the forward's per-view records are made from --
+        `dict(texture_dims=, colors=, opacity=, uv0=, umap=, vmap=, c2w=, settings=)` -- to have them packed here, on the
+        binning stream (`texture.pack_view_records`: an HBM pass over all splats, 65 us for 1 M, that otherwise
+        sits on the current stream in front of the compositing kernel).  `texture_gaussians` uses the packed records
+        when it is then called with exactly the tensors given here and to `begin`, unchanged; otherwise it packs again."""
         from .utils import finish_binning
 
         if pre.ready:
@@ -197,10 +204,18 @@ class BinningStream:
         cur = torch.cuda.current_stream(self.device)
         with torch.cuda.stream(self.stream):
             result = finish_binning(pre.binning)
+            if pack is not None and result[0] > 0:
+                from .texture import pack_view_records
+
+                means, scales, glob_scale, quats, viewmat, intrins, H, W, bw = pre.view
+                pre.binning.records = pack_view_records(
+                    pack["texture_dims"], result[2], pack["colors"], pack["opacity"], means, scales, glob_scale, quats,
+                    pack["uv0"], pack["umap"], pack["vmap"], viewmat, pack["c2w"], *intrins, H, W, bw, pack["settings"])
             ev = torch.cuda.Event()
             ev.record(self.stream)
         # allocated on the binning stream, consumed on the current one: keep the allocator from recycling them early
-        for t in (pre.centers, pre.extents, pre.depths, pre.num_tiles_hit, result[1], result[2]):
+        extra = [pre.binning.records.workspace] if pre.binning.records is not None else []
+        for t in [pre.centers, pre.extents, pre.depths, pre.num_tiles_hit, result[1], result[2]] + extra:
             if t.is_cuda and t.numel() > 0:
                 t.record_stream(cur)
         cur.wait_event(ev)

@@ -231,10 +231,58 @@ def pad_texture(texture: Tensor, out: Optional[Tensor] = None) -> Tensor:
     return out
 
 
+class PackedRecords:
+    """The per-view packed records of the forward (`gstex_texture_pack_records`), made ahead of `texture_gaussians` --
+    typically by `BinningStream.finish(pre, pack=...)` on the binning stream, beside the compositing kernels of the
+    view before.  Holds the workspace and the identity (address, shape, version counter) of every tensor it was
+    computed from; the forward uses it only if it is handed exactly those tensors, unchanged, and packs again
+    otherwise."""
+
+    __slots__ = ("workspace", "signature")
+
+    @staticmethod
+    def _sig(tensors, scalars):
+        return tuple((t.data_ptr(), tuple(t.shape), t._version) for t in tensors) + tuple(scalars)
+
+    def matches(self, tensors, scalars) -> bool:
+        return self.signature == PackedRecords._sig(tensors, scalars)
+
+
+def pack_view_records(texture_dims, tile_bins, colors, opacity, means, scales, glob_scale, quats, uv0, umap, vmap,
+                      viewmat, c2w, fx, fy, cx, cy, img_height, img_width, block_width, settings) -> PackedRecords:
+    """ref: the per-splat part of `texture_forward_kernel` (cuda/csrc/texture.cu:129-200), once per (view, splat)
+    instead of once per (pixel, splat).  Runs on the current stream; see `PackedRecords`."""
+    tensors = [t.detach() for t in (texture_dims, tile_bins, colors, opacity, means, scales, quats, uv0, umap, vmap,
+                                    viewmat, c2w)]
+    dev = _lib.require_cuda(*tensors)
+    _lib.require_dtype(tensors[0], torch.int32, "texture_dims")
+    _lib.require_dtype(tensors[1], torch.int32, "tile_bins")
+    for t in tensors[2:]:
+        _lib.require_dtype(t, torch.float32, "pack_view_records input")
+    if colors.dim() != 2 or colors.shape[-1] != 3:
+        raise ValueError("colors must be (N, 3)")
+    n = means.shape[0]
+    lib, p = _lib.load(), _lib.ptr
+    rec = PackedRecords()
+    rec.workspace = torch.empty((lib.gstex_texture_workspace_bytes(n),), dtype=torch.uint8, device=dev)
+    scalars = (float(glob_scale), float(fx), float(fy), float(cx), float(cy), int(img_height), int(img_width),
+               int(block_width), int(settings))
+    with torch.cuda.device(dev):
+        rc = lib.gstex_texture_pack_records(int(img_height), int(img_width), int(block_width), n, p(tensors[0]),
+                                            p(tensors[1]), p(tensors[2]), p(tensors[3]), p(tensors[4]), p(tensors[5]),
+                                            float(glob_scale), p(tensors[6]), p(tensors[7]), p(tensors[8]),
+                                            p(tensors[9]), p(tensors[10]), p(tensors[11]), float(fx), float(fy),
+                                            float(cx), float(cy), int(settings), p(rec.workspace),
+                                            rec.workspace.numel(), _lib.stream_ptr(dev))
+    _lib.check(rc, "gstex_texture_pack_records")
+    rec.signature = PackedRecords._sig(tensors, scalars)
+    return rec
+
+
 def _raster_forward(texture_info, texture_dims, gaussian_ids_sorted, tile_bins, colors, opacity, means, scales,
                     glob_scale, quats, uv0, umap, vmap, texture, viewmat, c2w, fx, fy, cx, cy, img_height, img_width,
                     block_width, settings, background, num_intersects, record_pairs=False, texture_affine=(1.0, 0.0),
-                    texture_padded=None):
+                    texture_padded=None, packed=None):
     """ref: `_C.texture_forward` (cuda/csrc/texture.cu:762-901).  Returns the 9 tensors + the workspace
     holding the per-view packed records (re-used by the backward)."""
     dev = _lib.require_cuda(texture_dims, colors, opacity, means, scales, quats, uv0, umap, vmap, texture, viewmat,
@@ -258,7 +306,12 @@ def _raster_forward(texture_info, texture_dims, gaussian_ids_sorted, tile_bins, 
     depth_idx = torch.empty((H, W), **i32)
     out_reg_s = torch.empty((H, W, 3), **f32)
     lib = _lib.load()
-    ws = torch.empty((lib.gstex_texture_workspace_bytes(n),), dtype=torch.uint8, device=dev)
+    if packed is not None and not packed.matches(
+            (texture_dims, tile_bins, colors, opacity, means, scales, quats, uv0, umap, vmap, viewmat, c2w),
+            (float(glob_scale), float(fx), float(fy), float(cx), float(cy), H, W, int(block_width), int(settings))):
+        packed = None  # made from other tensors (or the tensors have changed since): pack again
+    ws = (packed.workspace if packed is not None else
+          torch.empty((lib.gstex_texture_workspace_bytes(n),), dtype=torch.uint8, device=dev))
     pairs = None
     if (record_pairs and PairStreamPolicy.enabled and num_intersects > 0
             and lib.gstex_pair_stream_supported(C, n, int(settings))):
@@ -271,6 +324,9 @@ def _raster_forward(texture_info, texture_dims, gaussian_ids_sorted, tile_bins, 
         if (tuple(texture_padded.shape) != (texture.shape[0], 4) or C > 3 or texture_padded.dtype != torch.float32
                 or texture_padded.device != dev or not texture_padded.is_contiguous()):
             raise ValueError("texture_padded must be pad_texture(texture): contiguous float32 (T, 4) on the same device")
+    if packed is not None:
+        fwd, tex_args = lib.gstex_texture_forward_packed, (p(texture), p(texture_padded))
+    elif texture_padded is not None:
         fwd, tex_args = lib.gstex_texture_forward_padded, (p(texture), p(texture_padded))
     else:
         fwd, tex_args = lib.gstex_texture_forward_act, (p(texture),)
@@ -312,7 +368,8 @@ class _TextureGaussians(Function):
                                              viewmat, c2w, fx, fy, cx, cy, img_height, img_width, block_width,
                                              settings, background, max(num_intersects, 0),
                                              record_pairs=any(ctx.needs_input_grad), texture_affine=texture_affine,
-                                             texture_padded=texture_padded)
+                                             texture_padded=texture_padded,
+                                             packed=getattr(binning, "records", None))
         out_img, out_depth, out_reg, out_texture, out_normal, final_Ts, final_idx, depth_idx, out_reg_s = outputs
         ctx.img_width, ctx.img_height = img_width, img_height
         ctx.texture_info = texture_info

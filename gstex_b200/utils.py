@@ -127,7 +127,7 @@ class TileBinning:
     host synchronisation of the stage (the reference's `.item()`, utils.py:58) no longer drains the GPU."""
 
     __slots__ = ("num_points", "centers", "extents", "depths", "nth", "cum", "total", "tile_bounds", "block_size", "num_tiles",
-                 "block_counts", "tile_start", "tile_bins", "stats_host", "event", "fast", "result")
+                 "block_counts", "tile_start", "tile_bins", "stats_host", "event", "fast", "result", "records")
 
 
 _PINNED_FREE = []  # pinned 2-int read-back buffers not owned by any outstanding request
@@ -161,6 +161,7 @@ def begin_binning(num_points: int, centers: Tensor, extents: Tensor, depths: Ten
     b.tile_bounds, b.block_size = tile_bounds, int(block_size)
     b.num_tiles = int(tile_bounds[0]) * int(tile_bounds[1])
     b.result = None
+    b.records = None  # texture.PackedRecords made ahead of the forward (multiview.BinningStream.finish(pack=...))
     b.event = b.stats_host = b.block_counts = b.tile_start = b.tile_bins = None
     i32 = dict(dtype=torch.int32, device=dev)
     if nth.numel() == 0:

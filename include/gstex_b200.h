@@ -256,6 +256,30 @@ int gstex_texture_forward_padded(int img_height, int img_width, int block_width,
                           float* out_depth, float* out_reg, float* out_texture, float* out_normal, float* final_Ts,
                           int32_t* final_idx, int32_t* depth_idx, float* out_reg_s, void* workspace,
                           size_t workspace_bytes, void* pair_stream, size_t pair_stream_bytes, void* stream);
+/* The packing stage of gstex_texture_forward* (the per-view 128-byte records, support boxes and tile order the
+ * compositing kernels read, written into `workspace`) as a call of its own, and the forward that takes them as given.
+ * A multi-view caller issues the pack of view i+1 on another stream while view i's compositing kernels run: the pack is
+ * an HBM stream over all splats, the compositing kernels are issue-bound, so the two overlap almost for free.  The
+ * inputs of the two calls (and the workspace) must be the same and unchanged in between; the outputs are bit-identical
+ * to gstex_texture_forward_padded's (`texture4` may be NULL here: scalar texel loads).  The backward takes the same
+ * workspace with records_valid = 1, as after any forward.  No counterpart in the reference, which recomputes the
+ * per-splat terms in every pixel thread (texture.cu:129-200). */
+int gstex_texture_pack_records(int img_height, int img_width, int block_width, int n, const int32_t* texture_dims,
+                               const int32_t* tile_bins, const float* colors, const float* opacities, const float* means,
+                               const float* scales, float glob_scale, const float* quats, const float* uv0,
+                               const float* umap, const float* vmap, const float* viewmat, const float* c2w, float fx,
+                               float fy, float cx, float cy, int settings, void* workspace, size_t workspace_bytes,
+                               void* stream);
+int gstex_texture_forward_packed(int img_height, int img_width, int block_width, int channels, int n, int num_intersects,
+                          const int32_t* texture_dims, const int32_t* gaussian_ids_sorted, const int32_t* tile_bins,
+                          const float* colors, const float* opacities, const float* means, const float* scales,
+                          float glob_scale, const float* quats, const float* uv0, const float* umap,
+                          const float* vmap, const float* texture, const float* texture4, float tex_scale,
+                          float tex_bias, const float* viewmat, const float* c2w, float fx,
+                          float fy, float cx, float cy, int settings, const float* background, float* out_img,
+                          float* out_depth, float* out_reg, float* out_texture, float* out_normal, float* final_Ts,
+                          int32_t* final_idx, int32_t* depth_idx, float* out_reg_s, void* workspace,
+                          size_t workspace_bytes, void* pair_stream, size_t pair_stream_bytes, void* stream);
 /* texture4[t] = (texture[t][0], texture[t][1] or 0, texture[t][2] or 0, 0) for channels in 1..3. */
 int gstex_texture_pad4(long long num_texels, int channels, const float* texture, float* texture4, void* stream);
 int gstex_texture_backward_act(int img_height, int img_width, int block_width, int channels, int n, int num_intersects,

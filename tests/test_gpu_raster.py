@@ -539,3 +539,67 @@ def test_padded_texture_errors_are_loud():
     t = torch.zeros(8, 4, device="cuda")
     assert lib.gstex_texture_pad4(2, 4, _lib.ptr(t), _lib.ptr(t), None) == -1            # channels > 3
     assert lib.gstex_texture_pad4(1, 3, _lib.ptr(t), t.data_ptr() + 4, None) == -1       # unaligned destination
+
+
+def test_records_packed_ahead_give_identical_results(backward_path):
+    """`BinningStream.finish(pre, pack=...)` moves the forward's per-view packing to the binning stream; the forward then
+    takes the records as given (`gstex_texture_forward_packed`).  Same kernels on the same inputs: images bit for bit,
+    gradients within the atomics' noise -- also when the same packed records are rendered twice, and when a tensor
+    differs from the one that was packed (the forward must notice and pack again)."""
+    import gstex_b200 as G
+    from gstex_b200 import _lib
+    from gstex_b200.multiview import BinningStream
+    from gstex_b200.synthetic import make_scene, make_upstream_grads
+
+    s = make_scene("cfg2", n=20000, width=256, height=256)
+    v = {k: x.cuda() for k, x in make_upstream_grads(s).items()}
+    sd = {k: (x.cuda() if isinstance(x, torch.Tensor) else x) for k, x in s.items()}
+    intr = (s["fx"], s["fy"], s["cx"], s["cy"])
+    H, W, bw = s["H"], s["W"], 16
+    keys = ["colors", "opacities", "means", "scales", "quats", "uv0", "umap", "vmap", "texture"]
+    vm, c2w = s["viewmats"][0].cuda().contiguous(), s["c2ws"][0].cuda().contiguous()
+    bs = BinningStream(torch.device("cuda"))
+    calls = []
+    lib = _lib.load()
+
+    def run(mode):
+        pd = {k: sd[k].clone().requires_grad_(True) for k in keys}
+        pre = bs.begin(pd["means"], pd["scales"], 1, pd["quats"], vm, intr, H, W, bw)
+        pack = dict(texture_dims=sd["texture_dims"], colors=pd["colors"], opacity=pd["opacities"], uv0=pd["uv0"],
+                    umap=pd["umap"], vmap=pd["vmap"], c2w=c2w, settings=s["settings"])
+        bs.finish(pre, pack=None if mode == "plain" else pack)
+        assert (pre.binning.records is not None) == (mode != "plain")
+        colors = pd["colors"]
+        if mode == "stale":  # another tensor with other values than the one that was packed
+            with torch.no_grad():
+                pd["colors"] = (pd["colors"] * 0.5).requires_grad_(True)
+            colors = pd["colors"]
+        outs = None
+        for _ in range(2 if mode == "twice" else 1):
+            n0 = lib.gstex_launch_count()
+            outs = G.texture_gaussians(s["texture_info"], sd["texture_dims"], *pre.args, colors, pd["opacities"],
+                                       pd["means"], pd["scales"], 1, pd["quats"], pd["uv0"], pd["umap"], pd["vmap"],
+                                       pd["texture"], vm, c2w, *intr, H, W, bw, s["settings"], sd["background"],
+                                       binning=pre.binning)
+            calls.append((mode, lib.gstex_launch_count() - n0))
+        torch.autograd.backward(list(outs), [v["v_out_img"], v["v_out_depth"], v["v_out_reg"], v["v_out_alpha"],
+                                             v["v_out_texture"], v["v_out_normal"]])
+        return [o.detach() for o in outs], [pd[k].grad for k in keys]
+
+    (o_ref, g_ref), (o_pk, g_pk), (o_tw, g_tw) = run("plain"), run("packed"), run("twice")
+    for nm, a, b, c in zip(["out_img", "out_depth", "out_reg", "out_alpha", "out_texture", "out_normal"], o_ref, o_pk, o_tw):
+        assert torch.equal(a, b), f"{nm}: {int((a != b).sum())} elements differ with records packed ahead"
+        assert torch.equal(a, c), f"{nm}: {int((a != c).sum())} elements differ on the second render of the same records"
+    for k, a, b, c in zip(keys, g_ref, g_pk, g_tw):
+        scale = float(a.abs().max())
+        assert float((a - b).abs().max()) <= 3e-5 * scale + 1e-30, k
+        assert float((a - c).abs().max()) <= 3e-5 * scale + 1e-30, k
+    launches = dict((m, n) for m, n in calls)
+    assert launches["packed"] == launches["plain"] - 1, f"the packed forward must not pack again: {calls}"
+    # stale records: the colours given to the forward are not the packed ones -> same result as a plain call on them
+    sd2 = dict(sd)
+    o_stale, _ = run("stale")
+    sd["colors"] = sd["colors"] * 0.5
+    o_half, _ = run("plain")
+    sd.update(colors=sd2["colors"])
+    assert torch.equal(o_stale[0], o_half[0]) and not torch.equal(o_stale[0], o_ref[0])
