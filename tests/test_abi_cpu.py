@@ -106,3 +106,29 @@ def test_texture_edit_argument_errors_need_no_gpu():
     assert lib.gstex_texture_edit(128, 128, 17, 5, 10, 10, 100, *ptrs10, 1.0, *ptrs6, 1.0, 1.0, 1.0, 1.0, 0, z, z, 0, z) == -1
     assert lib.gstex_texture_edit(128, 128, 16, 3, 10, 10, 100, *ptrs10, 1.0, *ptrs6, 1.0, 1.0, 1.0, 1.0, 0, z, z, 0, z) == -2
     assert b"gstex" in lib.gstex_error_string(-2)
+
+
+def test_toolchain_is_the_one_the_bit_exact_forms_were_checked_with():
+    """The per-pair arithmetic that must match the reference bit for bit is written with explicit round-to-nearest
+    intrinsics (csrc/raster_common.cuh, binning.cu, pack.cu), which no compiler may contract or reorder.  Everything
+    around it (accumulations written as plain C) was verified bit-identical to the reference's sm_100 build with nvcc
+    12.9 (tests/test_gpu_fullsize.py).  Another nvcc may contract those differently: fail loudly here, so that whoever
+    upgrades the toolchain re-runs the full-size parity tests on a GPU and then moves this pin."""
+    import shutil
+    import subprocess
+
+    import pytest
+
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        pytest.skip("no nvcc here: the prebuilt library is used as it is")
+    out = subprocess.run([nvcc, "--version"], capture_output=True, text=True).stdout
+    m = re.search(r"release (\d+\.\d+)", out)
+    assert m and m.group(1) == "12.9", f"nvcc {m.group(1) if m else '?'}: re-run tests/test_gpu_fullsize.py, then update this pin"
+    # the pinned helpers themselves must stay free of contractible arithmetic: no bare float '*' or '+' inside them
+    src = open(os.path.join(ROOT, "gstex_b200", "csrc", "raster_common.cuh")).read()
+    for name in ("dot3_ref", "bilinear_ref", "eval_pair"):
+        i = src.index(name + "(")
+        body = src[src.index("{", i):src.index("\n}", i)]
+        code = re.sub(r"//[^\n]*", "", body)
+        assert not re.search(r"[\w\)]\s*[\*\+]\s*[\w\(]", code), f"{name}: plain-C arithmetic in a pinned helper"
