@@ -107,9 +107,14 @@ class ClockSampler:
         self.first = 0  # samples before this one were taken before the timed region
 
     def start(self):
+        # the recipe's interval (200 ms); BENCH_CLOCKS=smi<ms>|off is a diagnosis knob (step outliers of 10-80 ms were
+        # seen once per ~100 steps with and without the sampler: scripts/gpu_clk.sh)
+        mode = os.environ.get("BENCH_CLOCKS", "smi200")
+        if mode == "off":
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
-                                          str(self.idx), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+                                          str(self.idx), "-lms", mode[3:]], stdout=subprocess.PIPE, text=True)
             threading.Thread(target=self._pump, daemon=True).start()
         except Exception:
             self.proc = None

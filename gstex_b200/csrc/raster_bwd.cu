@@ -169,15 +169,18 @@ __global__ void __launch_bounds__(kMaxTileThreads + 32, 2) texture_backward_kern
     float T = p.final_Ts[id];
     const float3 ts_final = make_float3(p.final_s[3 * id], p.final_s[3 * id + 1], p.final_s[3 * id + 2]);
     const int depth_final = p.depth_idx[id];
-    const float3 v_out = make_float3(p.v_output[3 * id], p.v_output[3 * id + 1], p.v_output[3 * id + 2]);
-    const float v_out_depth = p.v_output_depth[id], v_out_reg = p.v_output_reg[id];
+    // a NULL upstream gradient is a zero gradient (autograd's None): nothing is read for it
+    const float3 v_out = p.v_output ? make_float3(p.v_output[3 * id], p.v_output[3 * id + 1], p.v_output[3 * id + 2])
+                                    : make_float3(0.f, 0.f, 0.f);
+    const float v_out_depth = p.v_output_depth ? p.v_output_depth[id] : 0.f, v_out_reg = p.v_output_reg ? p.v_output_reg[id] : 0.f;
     const float3 v_out_normal =
-        make_float3(p.v_output_normal[3 * id], p.v_output_normal[3 * id + 1], p.v_output_normal[3 * id + 2]);
+        p.v_output_normal ? make_float3(p.v_output_normal[3 * id], p.v_output_normal[3 * id + 1], p.v_output_normal[3 * id + 2])
+                          : make_float3(0.f, 0.f, 0.f);
     float v_tex[CMAX];
 #pragma unroll
-    for (int k = 0; k < CMAX; ++k) v_tex[k] = (k < C) ? p.v_output_texture[(size_t)C * id + k] : 0.f;
+    for (int k = 0; k < CMAX; ++k) v_tex[k] = (p.v_output_texture && k < C) ? p.v_output_texture[(size_t)C * id + k] : 0.f;
     float v_T_running = __ldg(p.background) * v_out.x + __ldg(p.background + 1) * v_out.y +
-                        __ldg(p.background + 2) * v_out.z - p.v_output_alpha[id];
+                        __ldg(p.background + 2) * v_out.z - (p.v_output_alpha ? p.v_output_alpha[id] : 0.f);
 
     // where this lane's reduced slot goes
     float* slot_base;
@@ -378,8 +381,7 @@ extern "C" int gstex_texture_backward_act(
     if (n == 0 || num_intersects == 0) return zero(true);  // gradients are zero (texture.py:331-340)
     if (!texture_dims || !gaussian_ids_sorted || !tile_bins || !colors || !opacities || !means || !scales || !quats ||
         !uv0 || !umap || !vmap || !texture || !viewmat || !c2w || !background || !final_Ts || !final_idx ||
-        !depth_idx || !final_s || !v_output || !v_output_depth || !v_output_reg || !v_output_alpha ||
-        !v_output_texture || !v_output_normal || !v_colors || !v_opacity || !v_means || !v_scales || !v_quats ||
+        !depth_idx || !final_s || !v_colors || !v_opacity || !v_means || !v_scales || !v_quats ||
         !v_uv0 || !v_umap || !v_vmap || !v_texture || !workspace)
         return GSTEX_E_BADARG;
     if (workspace_bytes < ws_bytes(n)) return GSTEX_E_WORKSPACE;

@@ -88,19 +88,24 @@ __global__ void __launch_bounds__(kStreamWarps * 32, 2) texture_backward_stream_
             const int id = pix.pix_id;
             tab[F_RAYX][lane] = pix.ray.x; tab[F_RAYY][lane] = pix.ray.y; tab[F_RAYZ][lane] = pix.ray.z;
             tab[F_PX][lane] = pix.px; tab[F_PY][lane] = pix.py; tab[F_VDEPTH][lane] = pix.view_depth;
-            const float vo0 = p.v_output[3 * id], vo1 = p.v_output[3 * id + 1], vo2 = p.v_output[3 * id + 2];
+            // a NULL upstream gradient is a zero gradient (autograd's None): nothing is read for it
+            const bool has_o = p.v_output != nullptr, has_n = p.v_output_normal != nullptr, has_t = p.v_output_texture != nullptr;
+            const float vo0 = has_o ? p.v_output[3 * id] : 0.f, vo1 = has_o ? p.v_output[3 * id + 1] : 0.f,
+                        vo2 = has_o ? p.v_output[3 * id + 2] : 0.f;
             tab[F_VOUTX][lane] = vo0; tab[F_VOUTY][lane] = vo1; tab[F_VOUTZ][lane] = vo2;
-            tab[F_VNX][lane] = p.v_output_normal[3 * id]; tab[F_VNY][lane] = p.v_output_normal[3 * id + 1];
-            tab[F_VNZ][lane] = p.v_output_normal[3 * id + 2];
-            tab[F_VT0][lane] = p.v_output_texture[(size_t)C * id];
-            tab[F_VT1][lane] = (C > 1) ? p.v_output_texture[(size_t)C * id + 1] : 0.f;
-            tab[F_VT2][lane] = (C > 2) ? p.v_output_texture[(size_t)C * id + 2] : 0.f;
-            tab[F_VDEP][lane] = p.v_output_depth[id]; tab[F_VREG][lane] = p.v_output_reg[id];
+            tab[F_VNX][lane] = has_n ? p.v_output_normal[3 * id] : 0.f;
+            tab[F_VNY][lane] = has_n ? p.v_output_normal[3 * id + 1] : 0.f;
+            tab[F_VNZ][lane] = has_n ? p.v_output_normal[3 * id + 2] : 0.f;
+            tab[F_VT0][lane] = has_t ? p.v_output_texture[(size_t)C * id] : 0.f;
+            tab[F_VT1][lane] = (has_t && C > 1) ? p.v_output_texture[(size_t)C * id + 1] : 0.f;
+            tab[F_VT2][lane] = (has_t && C > 2) ? p.v_output_texture[(size_t)C * id + 2] : 0.f;
+            tab[F_VDEP][lane] = p.v_output_depth ? p.v_output_depth[id] : 0.f;
+            tab[F_VREG][lane] = p.v_output_reg ? p.v_output_reg[id] : 0.f;
             tab[F_TS0][lane] = p.final_s[3 * id]; tab[F_TS1][lane] = p.final_s[3 * id + 1];
             tab[F_TS2][lane] = p.final_s[3 * id + 2];
             tab[F_DFINAL][lane] = __int_as_float(p.depth_idx[id]);
             // seed of the d(loss)/d(T) recurrence, texture.cu:470-475
-            tab[F_VTRUN][lane] = bg0 * vo0 + bg1 * vo1 + bg2 * vo2 - p.v_output_alpha[id];
+            tab[F_VTRUN][lane] = bg0 * vo0 + bg1 * vo1 + bg2 * vo2 - (p.v_output_alpha ? p.v_output_alpha[id] : 0.f);
         }
         __syncwarp();
 

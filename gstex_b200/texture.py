@@ -353,6 +353,7 @@ class _TextureGaussians(Function):
                 scales, glob_scale, quats, uv0, umap, vmap, texture, viewmat, c2w, fx, fy, cx, cy, img_height,
                 img_width, block_width, settings, background=None, binning=None, texture_affine=(1.0, 0.0),
                 texture_padded=None):
+        ctx.set_materialize_grads(False)  # unused outputs reach backward as None, not as zero images
         num_points = centers.size(0)
         tile_bounds = ((img_width + block_width - 1) // block_width, (img_height + block_width - 1) // block_width, 1)
         dev = centers.device
@@ -398,17 +399,21 @@ class _TextureGaussians(Function):
         C = int(ctx.texture_info[2])
         dev = means.device
 
-        def grad_or_zero(g, shape):
+        def grad_or_none(g, shape):
+            # an output the loss does not use arrives as None (set_materialize_grads(False) in forward) and goes to
+            # the library as a NULL pointer = zero: no zero image is allocated, filled and read per view
             if g is None:
-                return torch.zeros(shape, dtype=torch.float32, device=dev)
+                return None
+            if tuple(g.shape) != shape:
+                raise ValueError(f"upstream gradient of shape {tuple(g.shape)}, expected {shape}")
             return g.contiguous().float()
 
-        v_out_img = grad_or_zero(v_out_img, (H, W, 3))
-        v_out_depth = grad_or_zero(v_out_depth, (H, W))
-        v_out_reg = grad_or_zero(v_out_reg, (H, W))
-        v_out_alpha = grad_or_zero(v_out_alpha, (H, W))  # ref: texture.py:306-307
-        v_out_texture = grad_or_zero(v_out_texture, (H, W, C))
-        v_out_normal = grad_or_zero(v_out_normal, (H, W, 3))
+        v_out_img = grad_or_none(v_out_img, (H, W, 3))
+        v_out_depth = grad_or_none(v_out_depth, (H, W))
+        v_out_reg = grad_or_none(v_out_reg, (H, W))
+        v_out_alpha = grad_or_none(v_out_alpha, (H, W))  # ref: texture.py:306-307
+        v_out_texture = grad_or_none(v_out_texture, (H, W, C))
+        v_out_normal = grad_or_none(v_out_normal, (H, W, 3))
 
         targets = ctx.grad_targets
         if targets is not None:

@@ -190,6 +190,8 @@ int gstex_texture_forward(int img_height, int img_width, int block_width, int ch
  * unpack kernel then adds every non-zero accumulator word to the reference's gradient tensors and clears it
  * again, so the scratch LEAVES every call all-zero.
  * num_texels = rows of `texture`.
+ * Any of the six upstream gradients v_output* may be NULL = all zero (autograd's None for an output the loss does
+ * not use -- the reference's trainer uses three of the six): nothing is allocated, cleared or read for it.
  * zero_fill, low two bits -- 1: the nine gradient buffers are uninitialised on entry and the library clears them
  * first; 0: they are zero-filled by the caller; 2: they hold running sums (a multi-view step's accumulated
  * gradients) and this view's gradients are ADDED to them -- what autograd's AccumulateGrad would do in a separate

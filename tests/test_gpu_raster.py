@@ -603,3 +603,39 @@ def test_records_packed_ahead_give_identical_results(backward_path):
     o_half, _ = run("plain")
     sd.update(colors=sd2["colors"])
     assert torch.equal(o_stale[0], o_half[0]) and not torch.equal(o_stale[0], o_ref[0])
+
+
+def test_unused_outputs_need_no_zero_gradients(backward_path):
+    """A loss that reads only some of the six outputs (the reference trainer's reads rgb, texture and alpha) hands None
+    for the others; they reach the library as NULL = zero.  Same gradients as with explicit zero images."""
+    import gstex_b200 as G
+    from gstex_b200.synthetic import make_scene, make_upstream_grads
+
+    s = make_scene("cfg2", n=20000, width=256, height=256)
+    v = {k: x.cuda() for k, x in make_upstream_grads(s).items()}
+    sd = {k: (x.cuda() if isinstance(x, torch.Tensor) else x) for k, x in s.items()}
+    intr = (s["fx"], s["fy"], s["cx"], s["cy"])
+    H, W, bw = s["H"], s["W"], 16
+    keys = ["colors", "opacities", "means", "scales", "quats", "uv0", "umap", "vmap", "texture"]
+    vm, c2w = s["viewmats"][0].cuda().contiguous(), s["c2ws"][0].cuda().contiguous()
+
+    def run(used):
+        pd = {k: sd[k].clone().requires_grad_(True) for k in keys}
+        _, depths, centers, extents, nth = G.project_bounds(pd["means"].detach(), pd["scales"].detach(), 1,
+                                                            pd["quats"].detach(), vm, intr, H, W, bw)
+        outs = G.texture_gaussians(s["texture_info"], sd["texture_dims"], centers, extents, depths, nth, pd["colors"],
+                                   pd["opacities"], pd["means"], pd["scales"], 1, pd["quats"], pd["uv0"], pd["umap"],
+                                   pd["vmap"], pd["texture"], vm, c2w, *intr, H, W, bw, s["settings"], sd["background"])
+        names = ["out_img", "out_depth", "out_reg", "out_alpha", "out_texture", "out_normal"]
+        if used is None:  # all six, zeros for the unused ones
+            grads = [v["v_" + nm] if nm in ("out_img", "out_alpha") else torch.zeros_like(o) for nm, o in zip(names, outs)]
+            torch.autograd.backward(list(outs), grads)
+        else:
+            sum((o * v["v_" + nm]).sum() for nm, o in zip(names, outs) if nm in used).backward()
+        return [pd[k].grad for k in keys]
+
+    g_zero, g_none = run(None), run(("out_img", "out_alpha"))
+    for k, a, b in zip(keys, g_zero, g_none):
+        scale = float(a.abs().max())
+        assert float((a - b).abs().max()) <= 3e-5 * scale + 1e-30, k
+    assert float(g_none[2].abs().max()) > 0
