@@ -29,11 +29,16 @@ class PairStreamPolicy:
     """Sizing of the pair stream (the forward's record of contributing (pixel, splat) pairs the stream backward
     reads, include/gstex_b200.h).  No counterpart in the reference, which always recomputes.  The pool is sized
     from the pairs the previous views actually produced (read back asynchronously, never synchronising); a pool
-    that turns out too small only costs speed: the backward then recomputes and the next pool is larger."""
+    that turns out too small only costs speed: the backward then recomputes and the next pool is larger.  The size moves
+    in steps of 4 M pairs (128 MB) and only grows, unless 32 views in a row needed less than a quarter of it: views of one
+    scene differ by tens of per cent in their pair counts, and a pool that followed every view would ask the caching
+    allocator for a new size every time (a `cudaMalloc`, sometimes a synchronising `cudaFree`, in the middle of a
+    step)."""
 
     enabled = os.environ.get("GSTEX_B200_PAIR_STREAM", "1") != "0"
     pairs_per_pixel = float(os.environ.get("GSTEX_B200_PAIRS_PER_PIXEL", "40"))
     headroom = 1.5
+    quantum = 1 << 22  # pairs
     max_bytes = None  # optional hard cap of the pool in bytes (tests use it to provoke the overflow fallback)
     _state = {}  # (device index, H, W, block_width) -> {"pairs": int, "pending": (pinned tensor, event) | None}
 
@@ -45,10 +50,16 @@ class PairStreamPolicy:
             hdr = pend[0]
             used, overflow = int(hdr[0]) * 128, int(hdr[1])
             st["last"] = (used, overflow)  # pairs' worth of chunks taken, overflow flag of the last reported view
-            if overflow:
-                st["pairs"] = max(2 * st["pairs"], 1 << 20)
+            want = 2 * st["pairs"] if overflow else int(cls.headroom * used)
+            want = max((want + cls.quantum - 1) // cls.quantum, 1) * cls.quantum
+            if want > st["pairs"]:
+                st["pairs"], st["low"] = want, 0
+            elif want <= st["pairs"] // 4:
+                st["low"] = st.get("low", 0) + 1
+                if st["low"] >= 32:
+                    st["pairs"], st["low"] = want, 0
             else:
-                st["pairs"] = max(int(cls.headroom * used), st["pairs"] // 2, 1 << 20)
+                st["low"] = 0
             st["pending"] = None
         return st["pairs"]
 

@@ -1,13 +1,16 @@
 #!/bin/bash
 mkdir -p gpurun_out
-for M in smi100 off smi200 nvml smi1000 off smi100; do
-BENCH_CLOCKS=$M BENCH_DUMP_STEPS=1 timeout 300 python bench.py --steps 150 --warmup 3 --no-ref-cuda --no-cpu-baseline > gpurun_out/bench_clk_$M.json 2> gpurun_out/bench_clk_$M.err
+for M in a b c; do
+BENCH_DUMP_STEPS=1 timeout 300 python bench.py --steps 150 --warmup 3 --no-ref-cuda --no-cpu-baseline > gpurun_out/bench_clk_$M.json 2> gpurun_out/bench_clk_$M.err
 python - <<PY
 import json,re
 d=json.loads(open('gpurun_out/bench_clk_$M.json').read().strip().splitlines()[-1])
 err=open('gpurun_out/bench_clk_$M.err').read()
-per=[float(x) for x in re.findall(r'per-step ms: (.*)',err)[0].split()]
-out=[round(x,1) for x in per if x>10.6]
-print('$M','value %.1f'%d['value'],'median %.2f'%d['step_ms']['median'],'outliers>10.6:',len(out),out[:12],'clocks',d.get('clocks'))
+for i,l in enumerate(re.findall(r'per-step ms: (.*)',err)):
+    per=[float(x) for x in l.split()]
+    out=[(j,round(x,1)) for j,x in enumerate(per) if x>1.06*sorted(per)[len(per)//2]]
+    print('$M leg',i,'median %.2f'%sorted(per)[len(per)//2],'outliers:',len(out),out[:12])
+print(re.findall(r'cudaMalloc.*',err))
+print('value %.1f'%d['value'],'e2e %.1f'%d['e2e']['value'])
 PY
 done
