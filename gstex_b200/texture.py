@@ -50,8 +50,14 @@ class PairStreamPolicy:
             hdr = pend[0]
             used, overflow = int(hdr[0]) * 128, int(hdr[1])
             st["last"] = (used, overflow)  # pairs' worth of chunks taken, overflow flag of the last reported view
-            want = 2 * st["pairs"] if overflow else int(cls.headroom * used)
+            if overflow and pend[2]:
+                want = st["pairs"]  # the pool was cut by `max_bytes`, not by this policy: nothing to learn
+            else:
+                want = 2 * st["pairs"] if overflow else int(cls.headroom * used)
             want = max((want + cls.quantum - 1) // cls.quantum, 1) * cls.quantum
+            # every contributing pair has alpha >= 1/255, so a pixel is finished (T <= 1e-4) after at most
+            # ln(1e4) / -ln(1 - 1/255) = 2345 of them: no view can need more than that per pixel
+            want = min(want, max(2400 * H * W, cls.quantum))
             if want > st["pairs"]:
                 st["pairs"], st["low"] = want, 0
             elif want <= st["pairs"] // 4:
@@ -64,8 +70,9 @@ class PairStreamPolicy:
         return st["pairs"]
 
     @classmethod
-    def report(cls, dev, H, W, bw, stream_buf) -> None:
-        """Queue an async read-back of the stream header (chunks used, overflow flag)."""
+    def report(cls, dev, H, W, bw, stream_buf, capped: bool = False) -> None:
+        """Queue an async read-back of the stream header (chunks used, overflow flag).  `capped`: the pool was smaller
+        than this policy asked for (`max_bytes`)."""
         st = cls._state.get((dev.index, H, W, bw))
         if st is None or st["pending"] is not None:
             return
@@ -75,7 +82,7 @@ class PairStreamPolicy:
         host.copy_(stream_buf[:16].view(torch.int32), non_blocking=True)
         ev = torch.cuda.Event()
         ev.record()
-        st["pending"] = (host, ev)
+        st["pending"] = (host, ev, bool(capped))
 
 
 class GradientTargets:
@@ -327,8 +334,9 @@ def _raster_forward(texture_info, texture_dims, gaussian_ids_sorted, tile_bins, 
     if (record_pairs and PairStreamPolicy.enabled and num_intersects > 0
             and lib.gstex_pair_stream_supported(C, n, int(settings))):
         nbytes = lib.gstex_pair_stream_bytes(H, W, int(block_width), PairStreamPolicy.max_pairs(dev, H, W, int(block_width)))
-        if PairStreamPolicy.max_bytes is not None:
-            nbytes = min(nbytes, int(PairStreamPolicy.max_bytes))
+        pool_capped = PairStreamPolicy.max_bytes is not None and nbytes > int(PairStreamPolicy.max_bytes)
+        if pool_capped:
+            nbytes = int(PairStreamPolicy.max_bytes)
         pairs = torch.empty((nbytes,), dtype=torch.uint8, device=dev)
     p = _lib.ptr
     if texture_padded is not None:
@@ -352,7 +360,7 @@ def _raster_forward(texture_info, texture_dims, gaussian_ids_sorted, tile_bins, 
             _lib.stream_ptr(dev))
     _lib.check(rc, "gstex_texture_forward")
     if pairs is not None:
-        PairStreamPolicy.report(dev, H, W, int(block_width), pairs)
+        PairStreamPolicy.report(dev, H, W, int(block_width), pairs, capped=pool_capped)
     return (out_img, out_depth, out_reg, out_texture, out_normal, final_Ts, final_idx, depth_idx, out_reg_s), ws, pairs
 
 
