@@ -26,15 +26,23 @@ namespace gstex {
 
 constexpr int kWin = 11;               // pytorch_msssim default win_size
 constexpr int kTileH = 16;             // owned pixels per block: 16 rows x 32 columns
-constexpr int kTileW = 32;
+#ifndef GSTEX_LOSS_TILE_W
+#define GSTEX_LOSS_TILE_W 32
+#endif
+#ifndef GSTEX_LOSS_OUT2
+#define GSTEX_LOSS_OUT2 8
+#endif
+constexpr int kTileW = GSTEX_LOSS_TILE_W;
 constexpr int kHaloH = kTileH + kWin - 1;  // 26
 constexpr int kHaloW = kTileW + kWin - 1;  // 42
 constexpr int kHaloE = kHaloW * 3;     // 126 floats per halo row (three interleaved channels)
 constexpr int kOwnE = kTileW * 3;      // 96 floats per owned row
-constexpr int kPitch = 127;            // shared-memory row pitch, in elements
+constexpr int kPitch = kHaloE + 1;     // shared-memory row pitch, in elements
 constexpr int kLossThreads = 256;
 constexpr int kOut1 = 8;               // outputs per thread of the pass along H (two halves of the 16 rows)
-constexpr int kOut2 = 8;               // outputs per thread of the pass along W
+constexpr int kOut2 = GSTEX_LOSS_OUT2; // outputs per thread of the pass along W
+static_assert(kTileW % kOut2 == 0 && 3 * (kTileW / kOut2) * kTileH <= kLossThreads && 2 * kHaloE <= kLossThreads &&
+              (kOwnE % 4) == 0, "loss tile geometry");
 
 struct LossWindow {
     float g[kWin];
