@@ -443,13 +443,17 @@ def measured_peak_gbs():
 
 
 def kernel_source_stamp():
-    """sha256 over the CUDA sources: ties profiles/traffic.json (written by scripts/ncu_traffic.py from an ncu capture)
-    to the build it was captured from -- the GPU box has no .git to ask."""
+    """sha256 over the CUDA sources of the hot path (every kernel the bench's timed region launches): ties
+    profiles/traffic.json (written by scripts/ncu_traffic.py from an ncu capture) to the build it was captured from -- the
+    GPU box has no .git to ask.  The sources of the next-row kernels the timed region never launches are left out."""
     import glob
     import hashlib
 
+    other = {"loss.cu", "sh.cu", "texture_edit.cu", "texture_sample.cu", "activations.cu", "charts.cu", "peer_reduce.cu"}
     h = hashlib.sha256()
     for f in sorted(glob.glob(os.path.join(ROOT, "gstex_b200", "csrc", "*.cu*"))):
+        if os.path.basename(f) in other:
+            continue
         h.update(os.path.basename(f).encode())
         h.update(open(f, "rb").read())
     return h.hexdigest()[:16]
