@@ -538,16 +538,23 @@ def main():
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
         ms0 = torch.cuda.memory_stats(dev)
         ev[0].record()
+        grow = []  # (step, cudaMalloc calls, bytes reserved) whenever the allocator went to the driver (diagnosis only)
+        dump = bool(os.environ.get("BENCH_DUMP_STEPS"))
         for k in range(args.steps):
             step_fn()
             ev[k + 1].record()
+            if dump:
+                m = torch.cuda.memory_stats(dev)
+                if m["num_device_alloc"] != (grow[-1][1] if grow else ms0["num_device_alloc"]):
+                    grow.append((k, m["num_device_alloc"], m["reserved_bytes.all.current"]))
         barrier()
         per = [ev[k].elapsed_time(ev[k + 1]) for k in range(args.steps)]
         if os.environ.get("BENCH_DUMP_STEPS"):  # diagnosis: the per-step times of this rank, allocator traffic to the driver
             ms1 = torch.cuda.memory_stats(dev)
             print("per-step ms:", " ".join(f"{x:.2f}" for x in per), file=sys.stderr)
             print("cudaMalloc / cudaFree calls inside the timed region:", ms1["num_device_alloc"] - ms0["num_device_alloc"],
-                  ms1["num_device_free"] - ms0["num_device_free"], file=sys.stderr)
+                  ms1["num_device_free"] - ms0["num_device_free"], "reserved MB at start", ms0["reserved_bytes.all.current"] >> 20,
+                  "growth (step, calls, reserved MB):", [(k, c, r >> 20) for k, c, r in grow], file=sys.stderr)
         return max_over_ranks(ev[0].elapsed_time(ev[-1])) / args.steps, per
 
     clocks = ClockSampler(local_rank)

@@ -130,6 +130,7 @@ class TileBinning:
                  "block_counts", "tile_start", "tile_bins", "stats_host", "event", "fast", "result", "records")
 
 
+_ISECT_QUANTUM = 1 << 20  # allocation granularity of the intersection lists (elements)
 _PINNED_FREE = []  # pinned 2-int read-back buffers not owned by any outstanding request
 
 
@@ -219,8 +220,13 @@ def finish_binning(b: TileBinning):
     if num_intersects < 1 or max_list > lib.gstex_tile_bucket_max_list():
         b.result = general(num_intersects)
         return b.result
-    keys = torch.empty((num_intersects,), dtype=torch.int64, device=dev)
-    ids_sorted = torch.empty((num_intersects,), **i32)
+    # Sized in steps of 1 M intersections: the views of a scene differ by a few per cent in `num_intersects`, and a
+    # caching allocator that is asked for a slightly different size every view sooner or later finds none of its free
+    # blocks large enough and goes to the driver in the middle of a step (a cudaMalloc of 12 MB was seen to take from
+    # 1 to 87 ms there: scripts/gpu_clk.sh).  The list handed back is the first `num_intersects` elements.
+    cap = (int(num_intersects) + _ISECT_QUANTUM - 1) // _ISECT_QUANTUM * _ISECT_QUANTUM
+    keys = torch.empty((cap,), dtype=torch.int64, device=dev)
+    ids_sorted = torch.empty((cap,), **i32)[:num_intersects]
     p = _lib.ptr
     with torch.cuda.device(dev):
         rc = lib.gstex_tile_bucket_sort(b.num_points, int(num_intersects), int(max_list), p(b.centers), p(b.extents),
