@@ -105,3 +105,62 @@ def test_binning_stream_matches_single_stream():
             scale = float(a.abs().max())
             err = float((a - b).abs().max())
             assert err <= 2e-5 * scale + 1e-30, f"{k}: {err:.3e} at scale {scale:.3e}"
+
+
+def test_multi_view_step_issues_no_implicit_synchronisation():
+    """A steady-state multi-view step (BinningStream + GradientBucket with deferred unpack, as bench.py runs it) must
+    not contain a single implicitly synchronising torch call (`.item()`, `.tolist()` on device memory, a blocking
+    copy, `nonzero`): `torch.cuda.set_sync_debug_mode("error")` turns any of them into an exception.  The one host wait
+    per view that remains is explicit -- `finish_binning` waits for the event behind the view's two sizes in pinned
+    memory (the reference's blocking `.item()`, utils.py:58, drains the whole stream instead)."""
+    import gstex_b200 as G
+    from gstex_b200.multiview import BinningStream, GradientBucket
+    from gstex_b200.synthetic import make_scene, make_upstream_grads
+    from gstex_b200.texture import GradientTargets
+
+    s = make_scene("cfg2", n=30000, width=320, height=256, views=4)
+    dev = torch.device("cuda", 0)
+    sd = {k: (x.to(dev) if isinstance(x, torch.Tensor) else x) for k, x in s.items()}
+    v = {k: x.to(dev) for k, x in make_upstream_grads(s).items()}
+    up = [v["v_out_img"], v["v_out_depth"], v["v_out_reg"], v["v_out_alpha"], v["v_out_texture"], v["v_out_normal"]]
+    intr = (s["fx"], s["fy"], s["cx"], s["cy"])
+    H, W, bw = s["H"], s["W"], 16
+    keys = ["colors", "opacities", "means", "scales", "quats", "uv0", "umap", "vmap", "texture"]
+    vms = [m.to(dev).contiguous() for m in s["viewmats"]]
+    c2ws = [m.to(dev).contiguous() for m in s["c2ws"]]
+    pd = {k: sd[k].clone().requires_grad_(True) for k in keys}
+    bucket = GradientBucket([pd[k] for k in keys])
+    bucket.register()
+    bs = BinningStream(dev)
+
+    def step():
+        bucket.zero_()
+        tex4 = G.pad_texture(pd["texture"])
+        pre = bs.begin(pd["means"], pd["scales"], 1, pd["quats"], vms[0], intr, H, W, bw)
+        bs.finish(pre)
+        for i in range(len(vms)):
+            outs = G.texture_gaussians(s["texture_info"], sd["texture_dims"], *pre.args, pd["colors"], pd["opacities"],
+                                       pd["means"], pd["scales"], 1, pd["quats"], pd["uv0"], pd["umap"], pd["vmap"],
+                                       pd["texture"], vms[i], c2ws[i], *intr, H, W, bw, s["settings"], sd["background"],
+                                       binning=pre.binning, texture_padded=tex4)
+            nxt = bs.begin(pd["means"], pd["scales"], 1, pd["quats"], vms[i + 1], intr, H, W, bw,
+                           wait_for_current=False) if i + 1 < len(vms) else None
+            torch.autograd.backward(list(outs), up)
+            if nxt is not None:
+                bs.finish(nxt)
+            pre = nxt
+        bucket.allreduce(1)
+
+    try:
+        step()  # warm-up: pinned buffers, pool sizes, the library itself
+        step()
+        torch.cuda.synchronize()
+        torch.cuda.set_sync_debug_mode("error")
+        try:
+            step()
+        finally:
+            torch.cuda.set_sync_debug_mode("default")
+        torch.cuda.synchronize()
+        assert float(pd["means"].grad.abs().max()) > 0
+    finally:
+        GradientTargets.clear()
