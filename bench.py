@@ -301,8 +301,8 @@ class Workload:
         import gstex_b200 as G
 
         def backward(outs, d):
-            gt = d["gt"].to(self.torch.float32) / 255.0  # get_gt_img, NS/models/gstex.py:1260-1275
-            _, main, l1, ssim = G.photometric_loss(outs[0], outs[4], outs[3], self.background, gt, 0.2)
+            # the uint8 image goes in as it is: the loss kernels convert it as get_gt_img does (NS/models/gstex.py:1238-1247)
+            _, main, l1, ssim = G.photometric_loss(outs[0], outs[4], outs[3], self.background, d["gt"], 0.2)
             main.backward()
             return self.torch.stack([main.detach(), l1, ssim])
 

@@ -76,6 +76,8 @@ _SIGNATURES = {
     "gstex_photometric_loss_scratch_bytes": (SZ, [I, I]),
     "gstex_photometric_loss_forward": (I, [I, I, I, P, P, P, P, P, P, F, I, F, P, P, P, P, SZ, P]),
     "gstex_photometric_loss_backward": (I, [I, I, I, P, P, P, P, P, P, F, I, F, P, P, P, P, P, P]),
+    "gstex_photometric_loss_forward_u8": (I, [I, I, I, P, P, P, P, P, P, F, I, F, P, P, P, P, SZ, P]),
+    "gstex_photometric_loss_backward_u8": (I, [I, I, I, P, P, P, P, P, P, F, I, F, P, P, P, P, P, P]),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)

@@ -56,6 +56,15 @@ struct LossDims {
 
 __device__ __forceinline__ float clamp_unit(float v) { return fminf(fmaxf(v, 0.f), 1.f); }
 
+// Ground truth as the trainer holds it: fp32 in [0, 1], or the uint8 image of the data manager
+// (NS/data/datamanagers/full_images_datamanager.py:316-333) converted the way `get_gt_img` does it
+// (NS/models/gstex.py:1238-1247: `image.float() / 255.0`, which eager torch evaluates as a multiplication by the
+// fp32 reciprocal of 255) -- same bits, without the two elementwise passes and the fp32 copy per view.
+__device__ __forceinline__ float load_gt(const float* gt, size_t i) { return __ldg(gt + i); }
+__device__ __forceinline__ float load_gt(const uint8_t* gt, size_t i) {
+    return __fmul_rn((float)__ldg(gt + i), 1.f / 255.f);
+}
+
 __device__ __forceinline__ float block_sum_256(float v, float* red) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -108,11 +117,12 @@ static_assert(sizeof(float2) * kHaloH * kPitch >= sizeof(float) * 3 * kTileH * k
 // so that four of the five multiply-adds per tap are two packed FFMA2 (each half an IEEE fma: the same bits as five
 // scalar ones), no integer division in the load loop, and the three derivative maps staged through shared memory so
 // that they leave as whole rows.  Pixels stay channel-interleaved in shared memory, as in HBM.
+template <typename GT>
 __global__ void __launch_bounds__(kLossThreads) loss_forward_kernel(LossDims d, LossWindow win, const float* __restrict__ out_img,
                                                            const float* __restrict__ out_texture,
                                                            const float* __restrict__ out_alpha,
                                                            const float* __restrict__ background,
-                                                           const float* __restrict__ gt, const float* __restrict__ mask,
+                                                           const GT* __restrict__ gt, const float* __restrict__ mask,
                                                            float* __restrict__ rgb, float* __restrict__ maps,
                                                            float2* __restrict__ partials) {
     extern __shared__ __align__(16) unsigned char loss_smem[];
@@ -138,11 +148,11 @@ __global__ void __launch_bounds__(kLossThreads) loss_forward_kernel(LossDims d, 
                                                 __fmul_rn(om, k == 0 ? bg[0] : k == 1 ? bg[1] : bg[2]));
                     const float v = clamp_unit(pre);
                     const float m = mask ? __ldg(mask + pix) : 1.f;
-                    x = __fmul_rn(__ldg(gt + pix * 3 + k), m);  // gstex.py:1297-1298 (gt_img * mask, pred_img * mask)
+                    x = __fmul_rn(load_gt(gt, pix * 3 + k), m);  // gstex.py:1297-1298 (gt_img * mask, pred_img * mask)
                     y = __fmul_rn(v, m);
                     if (r < kTileH && c < kTileW) {
                         rgb[pix * 3 + k] = v;
-                        l1 += fabsf(x - y);
+                        l1 += fabsf(__fsub_rn(x, y));
                     }
                 }
                 sh.sxy[r][e] = make_float2(x, y);
@@ -207,19 +217,24 @@ __global__ void __launch_bounds__(kLossThreads) loss_forward_kernel(LossDims d, 
         for (int o = 0; o < kOut2; ++o) {
             const int gj = j0 + kOut2 * cg + o;
             const bool valid = gi < d.Hv && gj < d.Wv;
+            // every operation rounded on its own, left to right (what the C oracle's -ffp-contract=off build does): the
+            // compiler is free to contract plain C differently in the fp32 and the uint8 instantiation of this kernel
             const float mu1 = a01[o].x, mu2 = a01[o].y;
-            const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
-            const float s1 = a23[o].x - mu1_sq, s2 = a23[o].y - mu2_sq, s12 = a4[o] - mu12;
-            const float A1 = 2.f * mu12 + C1, A2 = 2.f * s12 + C2, B1 = mu1_sq + mu2_sq + C1, B2 = s1 + s2 + C2;
-            const float rB1 = 1.f / B1, rB2 = 1.f / B2;
-            const float cs = A2 * rB2, lum = A1 * rB1;
-            if (valid) ssim += lum * cs;
+            const float mu1_sq = __fmul_rn(mu1, mu1), mu2_sq = __fmul_rn(mu2, mu2), mu12 = __fmul_rn(mu1, mu2);
+            const float s1 = __fsub_rn(a23[o].x, mu1_sq), s2 = __fsub_rn(a23[o].y, mu2_sq), s12 = __fsub_rn(a4[o], mu12);
+            const float A1 = __fadd_rn(__fmul_rn(2.f, mu12), C1), A2 = __fadd_rn(__fmul_rn(2.f, s12), C2);
+            const float B1 = __fadd_rn(__fadd_rn(mu1_sq, mu2_sq), C1), B2 = __fadd_rn(__fadd_rn(s1, s2), C2);
+            const float rB1 = __fdiv_rn(1.f, B1), rB2 = __fdiv_rn(1.f, B2);
+            const float cs = __fmul_rn(A2, rB2), lum = __fmul_rn(A1, rB1);
+            if (valid) ssim = __fadd_rn(ssim, __fmul_rn(lum, cs));
             // partial derivatives of lum*cs with E[y], E[y^2], E[xy] as the independent moments of the prediction y
             float dmu = 0.f, dyy = 0.f, dxy = 0.f;
             if (valid) {
-                dyy = -lum * cs * rB2;
-                dxy = 2.f * lum * rB2;
-                dmu = 2.f * rB1 * (mu1 * cs - mu2 * lum * cs) - 2.f * mu2 * dyy - mu1 * dxy;
+                dyy = __fmul_rn(__fmul_rn(-lum, cs), rB2);
+                dxy = __fmul_rn(__fmul_rn(2.f, lum), rB2);
+                const float t = __fsub_rn(__fmul_rn(mu1, cs), __fmul_rn(__fmul_rn(mu2, lum), cs));
+                dmu = __fsub_rn(__fsub_rn(__fmul_rn(__fmul_rn(2.f, rB1), t), __fmul_rn(__fmul_rn(2.f, mu2), dyy)),
+                                __fmul_rn(mu1, dxy));
             }
             const int se = r * kOwnE + (kOut2 * cg + o) * 3 + k;
             stage[se] = dmu; stage[kTileH * kOwnE + se] = dyy; stage[2 * kTileH * kOwnE + se] = dxy;
@@ -267,13 +282,14 @@ static_assert(sizeof(float2) * kHaloH * kPitch >= sizeof(float) * kTileH * kOwnE
 // One block = 16x32 owned pixels; the window positions that cover them start up to 10 rows/columns earlier.
 // Same tiling as the forward; the transpose of pass 2 then of pass 1 (the window is symmetric, so the adjoint is the
 // same filter read from 10 positions earlier).
+template <typename GT>
 __global__ void __launch_bounds__(kLossThreads) loss_backward_kernel(LossDims d, LossWindow win, float ssim_lambda,
                                                             const float* __restrict__ v_main,
                                                             const float* __restrict__ out_img,
                                                             const float* __restrict__ out_texture,
                                                             const float* __restrict__ out_alpha,
                                                             const float* __restrict__ background,
-                                                            const float* __restrict__ gt, const float* __restrict__ mask,
+                                                            const GT* __restrict__ gt, const float* __restrict__ mask,
                                                             const float* __restrict__ maps, float* __restrict__ v_out_img,
                                                             float* __restrict__ v_out_texture,
                                                             float* __restrict__ v_out_alpha) {
@@ -348,8 +364,8 @@ __global__ void __launch_bounds__(kLossThreads) loss_backward_kernel(LossDims d,
             }
         }
         const float up = v_main ? __ldg(v_main) : 1.f;
-        const float w_l1 = up * (1.f - ssim_lambda) / (3.f * (float)d.H * (float)d.W);
-        const float w_ss = -up * ssim_lambda / (3.f * (float)d.Hv * (float)d.Wv);
+        const float w_l1 = __fdiv_rn(__fmul_rn(up, __fsub_rn(1.f, ssim_lambda)), __fmul_rn(__fmul_rn(3.f, (float)d.H), (float)d.W));
+        const float w_ss = __fdiv_rn(__fmul_rn(-up, ssim_lambda), __fmul_rn(__fmul_rn(3.f, (float)d.Hv), (float)d.Wv));
         const float bgk = __ldg(background + k);
         const int gi = i0 + r;
 #pragma unroll
@@ -362,13 +378,15 @@ __global__ void __launch_bounds__(kLossThreads) loss_backward_kernel(LossDims d,
                 const float pre = __fadd_rn(__fadd_rn(__ldg(out_img + pix * 3 + k), __ldg(out_texture + pix * d.C + k)),
                                             __fmul_rn(om, bgk));
                 const float m = mask ? __ldg(mask + pix) : 1.f;
-                const float x = __fmul_rn(__ldg(gt + pix * 3 + k), m), y = __fmul_rn(clamp_unit(pre), m);
-                const float diff = x - y;  // Ll1 = mean |gt - pred|: d/dpred = -sign(gt - pred)
+                const float x = __fmul_rn(load_gt(gt, pix * 3 + k), m), y = __fmul_rn(clamp_unit(pre), m);
+                const float diff = __fsub_rn(x, y);  // Ll1 = mean |gt - pred|: d/dpred = -sign(gt - pred)
                 const float sgn = diff > 0.f ? -1.f : (diff < 0.f ? 1.f : 0.f);
-                g = w_l1 * sgn + w_ss * (aab[o].x + 2.f * y * aab[o].y + x * af[o]);
-                g *= m;                                    // pred_img * mask
+                // explicit roundings, left to right: see the forward's SSIM algebra
+                const float inner = __fadd_rn(__fadd_rn(aab[o].x, __fmul_rn(__fmul_rn(2.f, y), aab[o].y)), __fmul_rn(x, af[o]));
+                g = __fadd_rn(__fmul_rn(w_l1, sgn), __fmul_rn(w_ss, inner));
+                g = __fmul_rn(g, m);                       // pred_img * mask
                 if (!(pre >= 0.f && pre <= 1.f)) g = 0.f;  // torch.clamp passes the gradient on [min, max] only
-                gb = g * bgk;  // d/d out_alpha of (1 - out_alpha) * background, summed over the channels below
+                gb = __fmul_rn(g, bgk);  // d/d out_alpha of (1 - out_alpha) * background, summed over the channels below
             }
             const int se = (kOut2 * cg + o) * 3 + k;
             stage[r * kOwnE + se] = g;
@@ -421,11 +439,11 @@ extern "C" size_t gstex_photometric_loss_scratch_bytes(int img_height, int img_w
     return (size_t)div_up(img_height, kTileH) * div_up(img_width, kTileW) * sizeof(float2);
 }
 
-extern "C" int gstex_photometric_loss_forward(int img_height, int img_width, int channels, const float* out_img,
-                                              const float* out_texture, const float* out_alpha, const float* background,
-                                              const float* gt_img, const float* mask, float ssim_lambda, int win_size,
-                                              float win_sigma, float* rgb, float* losses, float* ssim_maps, void* scratch,
-                                              size_t scratch_bytes, void* stream) {
+template <typename GT>
+static int loss_forward_impl(int img_height, int img_width, int channels, const float* out_img, const float* out_texture,
+                             const float* out_alpha, const float* background, const GT* gt_img, const float* mask,
+                             float ssim_lambda, int win_size, float win_sigma, float* rgb, float* losses, float* ssim_maps,
+                             void* scratch, size_t scratch_bytes, void* stream) {
     if (img_height < kWin || img_width < kWin || channels < 3 || win_size != kWin || !(win_sigma > 0.f)) return GSTEX_E_BADARG;
     if (!out_img || !out_texture || !out_alpha || !background || !gt_img || !rgb || !losses || !scratch) return GSTEX_E_BADARG;
     if (scratch_bytes < gstex_photometric_loss_scratch_bytes(img_height, img_width)) return GSTEX_E_WORKSPACE;
@@ -433,10 +451,11 @@ extern "C" int gstex_photometric_loss_forward(int img_height, int img_width, int
     const dim3 grid(div_up(img_width, kTileW), div_up(img_height, kTileH));
     cudaStream_t st = (cudaStream_t)stream;
     // > 48 KB of shared memory: opt in (per device, cheap: done at every launch)
-    GSTEX_CUDA_TRY(cudaFuncSetAttribute(loss_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    GSTEX_CUDA_TRY(cudaFuncSetAttribute(loss_forward_kernel<GT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)sizeof(LossFwdShared)));
-    loss_forward_kernel<<<grid, kLossThreads, sizeof(LossFwdShared), st>>>(d, make_window(win_sigma), out_img, out_texture, out_alpha, background, gt_img,
-                                              mask, rgb, ssim_maps, reinterpret_cast<float2*>(scratch));
+    loss_forward_kernel<GT><<<grid, kLossThreads, sizeof(LossFwdShared), st>>>(d, make_window(win_sigma), out_img, out_texture,
+                                                                              out_alpha, background, gt_img, mask, rgb, ssim_maps,
+                                                                              reinterpret_cast<float2*>(scratch));
     GSTEX_LAUNCH_CHECK();
     loss_finalize_kernel<<<1, 256, 0, st>>>(reinterpret_cast<const float2*>(scratch), (int)(grid.x * grid.y), d, ssim_lambda,
                                             losses);
@@ -444,22 +463,63 @@ extern "C" int gstex_photometric_loss_forward(int img_height, int img_width, int
     return GSTEX_OK;
 }
 
-extern "C" int gstex_photometric_loss_backward(int img_height, int img_width, int channels, const float* out_img,
-                                               const float* out_texture, const float* out_alpha, const float* background,
-                                               const float* gt_img, const float* mask, float ssim_lambda, int win_size,
-                                               float win_sigma, const float* ssim_maps, const float* v_main_loss,
-                                               float* v_out_img, float* v_out_texture, float* v_out_alpha, void* stream) {
+template <typename GT>
+static int loss_backward_impl(int img_height, int img_width, int channels, const float* out_img, const float* out_texture,
+                              const float* out_alpha, const float* background, const GT* gt_img, const float* mask,
+                              float ssim_lambda, int win_size, float win_sigma, const float* ssim_maps,
+                              const float* v_main_loss, float* v_out_img, float* v_out_texture, float* v_out_alpha,
+                              void* stream) {
     if (img_height < kWin || img_width < kWin || channels < 3 || win_size != kWin || !(win_sigma > 0.f)) return GSTEX_E_BADARG;
     if (!out_img || !out_texture || !out_alpha || !background || !gt_img || !ssim_maps || !v_out_img || !v_out_texture ||
         !v_out_alpha)
         return GSTEX_E_BADARG;
     const LossDims d{img_height, img_width, channels, img_height - (kWin - 1), img_width - (kWin - 1)};
     const dim3 grid(div_up(img_width, kTileW), div_up(img_height, kTileH));
-    GSTEX_CUDA_TRY(cudaFuncSetAttribute(loss_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    GSTEX_CUDA_TRY(cudaFuncSetAttribute(loss_backward_kernel<GT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)sizeof(LossBwdShared)));
-    loss_backward_kernel<<<grid, kLossThreads, sizeof(LossBwdShared), (cudaStream_t)stream>>>(d, make_window(win_sigma), ssim_lambda, v_main_loss, out_img,
-                                                                 out_texture, out_alpha, background, gt_img, mask, ssim_maps,
-                                                                 v_out_img, v_out_texture, v_out_alpha);
+    loss_backward_kernel<GT><<<grid, kLossThreads, sizeof(LossBwdShared), (cudaStream_t)stream>>>(
+        d, make_window(win_sigma), ssim_lambda, v_main_loss, out_img, out_texture, out_alpha, background, gt_img, mask, ssim_maps,
+        v_out_img, v_out_texture, v_out_alpha);
     GSTEX_LAUNCH_CHECK();
     return GSTEX_OK;
+}
+
+#define GSTEX_LOSS_FWD_ARGS                                                                                              \
+    img_height, img_width, channels, out_img, out_texture, out_alpha, background, gt_img, mask, ssim_lambda, win_size,   \
+        win_sigma, rgb, losses, ssim_maps, scratch, scratch_bytes, stream
+#define GSTEX_LOSS_BWD_ARGS                                                                                              \
+    img_height, img_width, channels, out_img, out_texture, out_alpha, background, gt_img, mask, ssim_lambda, win_size,   \
+        win_sigma, ssim_maps, v_main_loss, v_out_img, v_out_texture, v_out_alpha, stream
+
+extern "C" int gstex_photometric_loss_forward(int img_height, int img_width, int channels, const float* out_img,
+                                              const float* out_texture, const float* out_alpha, const float* background,
+                                              const float* gt_img, const float* mask, float ssim_lambda, int win_size,
+                                              float win_sigma, float* rgb, float* losses, float* ssim_maps, void* scratch,
+                                              size_t scratch_bytes, void* stream) {
+    return loss_forward_impl<float>(GSTEX_LOSS_FWD_ARGS);
+}
+
+extern "C" int gstex_photometric_loss_backward(int img_height, int img_width, int channels, const float* out_img,
+                                               const float* out_texture, const float* out_alpha, const float* background,
+                                               const float* gt_img, const float* mask, float ssim_lambda, int win_size,
+                                               float win_sigma, const float* ssim_maps, const float* v_main_loss,
+                                               float* v_out_img, float* v_out_texture, float* v_out_alpha, void* stream) {
+    return loss_backward_impl<float>(GSTEX_LOSS_BWD_ARGS);
+}
+
+// The same two calls with the ground truth as the uint8 image the data manager holds (value / 255, see load_gt).
+extern "C" int gstex_photometric_loss_forward_u8(int img_height, int img_width, int channels, const float* out_img,
+                                                 const float* out_texture, const float* out_alpha, const float* background,
+                                                 const uint8_t* gt_img, const float* mask, float ssim_lambda, int win_size,
+                                                 float win_sigma, float* rgb, float* losses, float* ssim_maps, void* scratch,
+                                                 size_t scratch_bytes, void* stream) {
+    return loss_forward_impl<uint8_t>(GSTEX_LOSS_FWD_ARGS);
+}
+
+extern "C" int gstex_photometric_loss_backward_u8(int img_height, int img_width, int channels, const float* out_img,
+                                                  const float* out_texture, const float* out_alpha, const float* background,
+                                                  const uint8_t* gt_img, const float* mask, float ssim_lambda, int win_size,
+                                                  float win_sigma, const float* ssim_maps, const float* v_main_loss,
+                                                  float* v_out_img, float* v_out_texture, float* v_out_alpha, void* stream) {
+    return loss_backward_impl<uint8_t>(GSTEX_LOSS_BWD_ARGS);
 }

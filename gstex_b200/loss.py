@@ -31,7 +31,9 @@ def photometric_loss(out_img: Tensor, out_texture: Tensor, out_alpha: Tensor, ba
     """Returns `(rgb, main_loss, Ll1, ssim)`.
 
     `out_img` (H,W,3), `out_texture` (H,W,C>=3), `out_alpha` (H,W) are `texture_gaussians`' outputs; `background` (3,);
-    `gt_img` (H,W,3) is the ground truth already composited with the background (gstex.py:1286); `mask` (H,W) or
+    `gt_img` (H,W,3) is the ground truth already composited with the background (gstex.py:1286) -- fp32, or the uint8
+    image as the data manager holds it, which the kernels convert as `get_gt_img` does (`image.float() / 255.0`,
+    gstex.py:1244-1245; same bits, no fp32 copy); `mask` (H,W) or
     (H,W,1) multiplies both images before the two loss terms (gstex.py:1292-1298).  `main_loss` (0-dim) carries the
     gradient to the three rendered layers; `rgb` (H,W,3, clamped, unmasked), `Ll1` and `ssim` are detached values
     for logging/metrics (gstex.py:1384-1388)."""
@@ -47,7 +49,10 @@ class _PhotometricLoss(Function):
         tensors = [out_img, out_texture, out_alpha, background, gt_img] + ([mask] if mask is not None else [])
         dev = _lib.require_cuda(*tensors)
         for t, nm in zip(tensors, ["out_img", "out_texture", "out_alpha", "background", "gt_img", "mask"]):
+            if nm == "gt_img" and t.dtype == torch.uint8:
+                continue
             _lib.require_dtype(t, torch.float32, nm)
+        u8 = gt_img.dtype == torch.uint8
         if out_img.dim() != 3 or out_img.shape[2] != 3:
             raise RuntimeError("out_img must be (H, W, 3)")
         H, W = int(out_img.shape[0]), int(out_img.shape[1])
@@ -68,9 +73,10 @@ class _PhotometricLoss(Function):
         scratch = torch.empty((int(lib.gstex_photometric_loss_scratch_bytes(H, W)),), dtype=torch.uint8, device=dev)
         p = _lib.ptr
         with torch.cuda.device(dev):
-            rc = lib.gstex_photometric_loss_forward(H, W, C, p(out_img), p(out_texture), p(out_alpha), p(background),
-                                                    p(gt_img), p(mask), ssim_lambda, WIN_SIZE, WIN_SIGMA, p(rgb), p(losses),
-                                                    p(maps), p(scratch), scratch.numel(), _lib.stream_ptr(dev))
+            fwd = lib.gstex_photometric_loss_forward_u8 if u8 else lib.gstex_photometric_loss_forward
+            rc = fwd(H, W, C, p(out_img), p(out_texture), p(out_alpha), p(background),
+                     p(gt_img), p(mask), ssim_lambda, WIN_SIZE, WIN_SIGMA, p(rgb), p(losses),
+                     p(maps), p(scratch), scratch.numel(), _lib.stream_ptr(dev))
         _lib.check(rc, "gstex_photometric_loss_forward")
         ctx.ssim_lambda = ssim_lambda
         ctx.has_mask = mask is not None
@@ -96,7 +102,9 @@ class _PhotometricLoss(Function):
         v_main = v_main.to(torch.float32).contiguous()
         p = _lib.ptr
         with torch.cuda.device(dev):
-            rc = _lib.load().gstex_photometric_loss_backward(
+            lib = _lib.load()
+            bwd = lib.gstex_photometric_loss_backward_u8 if gt_img.dtype == torch.uint8 else lib.gstex_photometric_loss_backward
+            rc = bwd(
                 int(H), int(W), int(C), p(out_img), p(out_texture), p(out_alpha), p(background), p(gt_img), p(mask),
                 ctx.ssim_lambda, WIN_SIZE, WIN_SIGMA, p(maps), p(v_main), p(v_out_img), p(v_out_texture), p(v_out_alpha),
                 _lib.stream_ptr(dev))

@@ -410,6 +410,20 @@ int gstex_photometric_loss_backward(int img_height, int img_width, int channels,
                                     const float* gt_img, const float* mask, float ssim_lambda, int win_size,
                                     float win_sigma, const float* ssim_maps, const float* v_main_loss, float* v_out_img,
                                     float* v_out_texture, float* v_out_alpha, void* stream);
+/* The same two calls with `gt_img` as the uint8 (H,W,3) image the reference's data manager holds
+ * (NS/data/datamanagers/full_images_datamanager.py:316-333): every value is converted as `get_gt_img` does
+ * (NS/models/gstex.py:1238-1247, `image.float() / 255.0` = a multiplication by the fp32 reciprocal of 255), so the
+ * results are bit-identical to converting first, without the two elementwise passes and the fp32 copy per view. */
+int gstex_photometric_loss_forward_u8(int img_height, int img_width, int channels, const float* out_img,
+                                      const float* out_texture, const float* out_alpha, const float* background,
+                                      const uint8_t* gt_img, const float* mask, float ssim_lambda, int win_size,
+                                      float win_sigma, float* rgb, float* losses, float* ssim_maps, void* scratch,
+                                      size_t scratch_bytes, void* stream);
+int gstex_photometric_loss_backward_u8(int img_height, int img_width, int channels, const float* out_img,
+                                       const float* out_texture, const float* out_alpha, const float* background,
+                                       const uint8_t* gt_img, const float* mask, float ssim_lambda, int win_size,
+                                       float win_sigma, const float* ssim_maps, const float* v_main_loss, float* v_out_img,
+                                       float* v_out_texture, float* v_out_alpha, void* stream);
 
 /* ---- multi-GPU: the gradient sum of a view-sharded step over NVLink peer memory ----
  * Replaces the NCCL all-reduce torch DDP issues for the reference (NS/pipelines/base_pipeline.py:282) over the flat

@@ -166,3 +166,32 @@ def test_loss_argument_errors():
     z = torch.zeros(12, 12, 3)
     with pytest.raises(RuntimeError):
         G.photometric_loss(z, z, z[..., 0], torch.zeros(3), z)  # CPU tensors: there is no CPU path
+
+
+@pytest.mark.parametrize("size", [(97, 130), (256, 320)])
+def test_loss_takes_the_uint8_ground_truth_as_it_is(size):
+    """`gt_img` as the uint8 image the data manager holds == `get_gt_img`'s `image.float() / 255.0` first
+    (NS/models/gstex.py:1244-1245), bit for bit: values, losses and all three gradients."""
+    from gstex_b200.loss import photometric_loss
+
+    H, W = size
+    g = torch.Generator().manual_seed(H * 1000 + W)
+    dev = torch.device("cuda")
+    gt_u8 = torch.randint(0, 256, (H, W, 3), generator=g, dtype=torch.uint8).to(dev)
+    gt_f = gt_u8.float() / 255.0
+    base = [torch.rand(H, W, 3, generator=g).to(dev) * 0.6, torch.rand(H, W, 3, generator=g).to(dev) * 0.5,
+            torch.rand(H, W, generator=g).to(dev)]
+    bg = torch.tensor([0.2, 0.7, 0.4], device=dev)
+    mask = (torch.rand(H, W, generator=g) > 0.2).float().to(dev)
+
+    def run(gt, m):
+        ins = [t.clone().requires_grad_(True) for t in base]
+        rgb, main, l1, ssim = photometric_loss(ins[0], ins[1], ins[2], bg, gt, 0.2, mask=m)
+        (main * 1.7).backward()
+        return [rgb, main.detach(), l1, ssim] + [t.grad for t in ins]
+
+    for m in (None, mask):
+        for a, b in zip(run(gt_f, m), run(gt_u8, m)):
+            assert torch.equal(a, b)
+    with pytest.raises(RuntimeError):
+        photometric_loss(base[0], base[1], base[2], bg, gt_u8.to(torch.int32), 0.2)
