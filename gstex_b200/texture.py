@@ -254,7 +254,8 @@ class PackedRecords:
     typically by `BinningStream.finish(pre, pack=...)` on the binning stream, beside the compositing kernels of the
     view before.  Holds the workspace and the identity (address, shape, version counter) of every tensor it was
     computed from; the forward uses it only if it is handed exactly those tensors, unchanged, and packs again
-    otherwise."""
+    otherwise.  "Unchanged" is judged by torch's version counters: an in-place write through `.data` (which bypasses
+    them) between the pack and the forward goes unnoticed -- pack after such writes, not before."""
 
     __slots__ = ("workspace", "signature")
 
