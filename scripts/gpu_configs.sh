@@ -2,7 +2,7 @@
 # The other BASELINE.json configurations at full size (single GPU): our path + the reference CUDA kernels beside it.
 # Usage: bash scripts/gpu_configs.sh <tag>
 TAG=${1:-cfgs}; OUT=gpurun_out; mkdir -p $OUT
-for c in cfg2 cfg2_2dgs cfg3 cfg4; do
+for c in ${CFGS:-cfg2 cfg2_2dgs cfg3 cfg4}; do
   V=4; [ $c = cfg4 ] && V=8
   timeout 900 python bench.py --config $c --steps 3 --warmup 3 --views-per-gpu $V --no-cpu-baseline > $OUT/bench_${TAG}_$c.json 2> $OUT/bench_${TAG}_$c.err; echo "$c rc=$?"
   python - <<PY
